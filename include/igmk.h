@@ -1,0 +1,190 @@
+/*
+ * igmk.h -- C ABI of the B200-native IGM optimisation kernel ("igmk").
+ *
+ * This is the drop-in boundary for IGM's A/M hot path.  Every entry point is
+ * extern "C", takes plain pointers / sizes / PODs and returns an int status
+ * (0 = ok, non-zero = failure; the text is available from igmk_last_error()).
+ * Nothing throws across the ABI.  Paths cited below are relative to the
+ * alberlab/igm reference tree.
+ *
+ * M-step (replaces igm/model/kernel/lammps.py:361 `optimize(model, cfg)`,
+ * i.e. the create_lammps_data / create_lammps_script / Popen(lmp_serial) /
+ * get_info_from_log / get_last_frame sequence at lammps.py:429-465):
+ *     igmk_create -> igmk_submit (once per structure) -> igmk_run
+ *     -> igmk_fetch (once per structure) -> igmk_clear / igmk_destroy
+ *
+ * A-step (replaces igm/steps/ActivationDistanceStep.py:319 `get_actdist`,
+ * the row formatting/parsing at :39,:219-222,:241 and the contact-assignment
+ * predicate of igm/restraints/inter_hic.py:49-64 / intra_hic.py:50-65):
+ *     igmk_pop_create -> igmk_pop_upload -> igmk_pop_actdist
+ *     -> igmk_pop_assign -> (igmk_pop_mstep) -> igmk_pop_download
+ */
+#ifndef IGMK_H
+#define IGMK_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGMK_MAX_STAGES     32
+#define IGMK_MAX_ENVELOPES  8
+
+/* Particle kinds, igm/model/particle.py:10-12 */
+#define IGMK_KIND_BEAD      0   /* Particle.NORMAL        */
+#define IGMK_KIND_STATIC    1   /* Particle.DUMMY_STATIC  (frozen, no sterics) */
+#define IGMK_KIND_CENTROID  2   /* Particle.DUMMY_DYNAMIC (moves, no sterics)  */
+
+/* Bond styles, igm/model/kernel/lammps_model.py:8-9 */
+#define IGMK_BOND_UPPER     0   /* harmonic_upper_bound: active iff r > r0 */
+#define IGMK_BOND_LOWER     1   /* harmonic_lower_bound: active iff r < r0 */
+
+/* why the minimiser stopped (igmk_result_t.cg_stop) */
+#define IGMK_CG_MAXITER   0
+#define IGMK_CG_MAXEVAL   1
+#define IGMK_CG_ETOL      2
+#define IGMK_CG_FTOL      3
+#define IGMK_CG_DOWNHILL  4
+#define IGMK_CG_ZEROFORCE 5
+#define IGMK_CG_ZEROALPHA 6
+#define IGMK_CG_ZEROQUAD  7
+
+/*
+ * One structure = one igm.model.Model after all restraints were applied
+ * (what LammpsModel.from_model, lammps_model.py:253-301, walks).
+ * All pointers are HOST pointers, borrowed for the duration of the call only.
+ */
+typedef struct igmk_system {
+    int32_t        n_atoms;      /* len(model.particles)                               */
+    const float*   xyz;          /* [n_atoms][3]  Particle.pos (float32, particle.py:4) */
+    const float*   radius;       /* [n_atoms]     Particle.r                            */
+    const uint8_t* kind;         /* [n_atoms]     IGMK_KIND_*                           */
+    int32_t        n_bonds;      /* HarmonicUpperBound / HarmonicLowerBound forces      */
+    const int32_t* bond_i;       /* [n_bonds] particle index i (forces.py:113)          */
+    const int32_t* bond_j;       /* [n_bonds] particle index j                          */
+    const double*  bond_k;       /* [n_bonds] spring constant f.k                       */
+    const double*  bond_r0;      /* [n_bonds] bound distance  f.d                       */
+    const uint8_t* bond_style;   /* [n_bonds] IGMK_BOND_*                               */
+    int32_t        n_env;        /* EllipticEnvelope forces (forces.py:187), <= IGMK_MAX_ENVELOPES */
+    const double*  env_abck;     /* [n_env][4]  semi-axes a,b,c and k (k<0: DamID, damid.py:133) */
+    const int32_t* env_off;      /* [n_env+1]   CSR offsets into env_members            */
+    const int32_t* env_members;  /* particle ids of each envelope group                 */
+    double         evfactor;     /* ExcludedVolume.k (lammps_model.py:282-283); <0 = no Steric restraint */
+    int64_t        seed;         /* script seed, lammps.py:159-165                      */
+    int64_t        struct_id;    /* model.id (error messages only)                      */
+} igmk_system_t;
+
+/*
+ * The optimisation protocol = the part of create_lammps_script
+ * (lammps.py:263-356) that does not depend on the structure.
+ */
+typedef struct igmk_protocol {
+    int32_t n_stage;                         /* custom_annealing_protocol.num_steps */
+    int32_t mdsteps[IGMK_MAX_STAGES];
+    double  tstart[IGMK_MAX_STAGES];
+    double  tstop[IGMK_MAX_STAGES];
+    double  evfactor[IGMK_MAX_STAGES];       /* fix adapt ... scale yes, lammps.py:287-290 */
+    double  envfactor[IGMK_MAX_STAGES];      /* envelope_factors,        lammps.py:298-299 */
+    int32_t relax_mdsteps;                   /* 0: no relax sub-run (lammps.py:315-332)    */
+    double  relax_temperature;
+    double  relax_max_velocity;
+    double  timestep;                        /* lammps.py:242 */
+    double  max_velocity;                    /* nve/limit xmax, lammps.py:227 */
+    double  etol, ftol;                      /* minimize, lammps.py:355 */
+    int32_t max_cg_iter, max_cg_eval;
+    double  bond_prefactor;                  /* E = bond_prefactor*k*(r-r0)^2; 1.0 = LAMMPS harmonic convention */
+    int32_t skip_minimize;                   /* 1: stop after the last MD stage (diagnostics) */
+} igmk_protocol_t;
+
+/* What get_info_from_log (lammps_io.py:6-37) extracts from the LAMMPS log. */
+typedef struct igmk_result {
+    double  final_energy;                    /* 'final-energy'  */
+    double  pair_energy;                     /* 'pair-energy'   */
+    double  bond_energy;                     /* 'bond-energy'   */
+    double  temperature;                     /* thermo 'Temp'   */
+    double  env_energy[IGMK_MAX_ENVELOPES];  /* thermo 'f_envelope<j>' */
+    int32_t n_env;
+    int32_t cg_iters, cg_evals, cg_stop;
+    int32_t n_rebuilds;                      /* neighbour-list rebuilds during MD */
+    int32_t status;                          /* 0 ok, 1 non-finite coordinates/energy */
+    double  md_seconds;                      /* device time of the launch that ran this structure */
+} igmk_result_t;
+
+typedef struct igmk_handle igmk_handle_t;    /* M-step batch (one device)            */
+typedef struct igmk_pop    igmk_pop_t;       /* device-resident population (A-step)  */
+
+const char* igmk_last_error(void);
+int  igmk_version(void);
+int  igmk_device_count(void);
+
+/* ---- M-step: per-structure submit / run / fetch -------------------------------- */
+int igmk_create(int device, igmk_handle_t** out);
+int igmk_destroy(igmk_handle_t* h);
+int igmk_clear(igmk_handle_t* h);
+/* copies the structure into the batch; *slot_out indexes it in fetch calls */
+int igmk_submit(igmk_handle_t* h, const igmk_system_t* sys, int32_t* slot_out);
+/* ONE launch sequence for everything submitted: annealing MD + CG minimisation
+ * (lammps.py:285-356).  Coordinates are updated in the batch. */
+int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot);
+/* `run 0` equivalent: energies + forces at the submitted coordinates, double
+ * precision, with the pair prefactor scaled by ev_scale and the envelope
+ * semi-axes by env_scale. */
+int igmk_single_point(igmk_handle_t* h, double ev_scale, double env_scale,
+                      double bond_prefactor);
+/* same single point through the float32 force routine the MD loop uses */
+int igmk_single_point_f32(igmk_handle_t* h, double ev_scale, double env_scale,
+                          double bond_prefactor);
+int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out /* [n_atoms][3] */,
+               igmk_result_t* res);
+int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out /* [n_atoms][3] */);
+
+/* ---- A-step: device-resident population ------------------------------------------ */
+/*
+ * Population geometry.  `crd` uses the .hss layout coordinates[bead][struct][3]
+ * float32 (ModelingStep.py:441,517).  copy_off/copy_beads are Index.copy_index
+ * flattened (haploid bin -> bead ids); chrom_hap[i] = index.chrom[i] for the
+ * haploid bin i (ActivationDistanceStep.py:366-370).
+ */
+int igmk_pop_create(int device, int32_t n_bead, int32_t n_struct, int32_t n_hap,
+                    const float* radii /* [n_bead] */,
+                    const int32_t* chrom_bead /* [n_bead] index.chrom */,
+                    const int32_t* copy_off /* [n_hap+1] */,
+                    const int32_t* copy_beads,
+                    igmk_pop_t** out);
+int igmk_pop_destroy(igmk_pop_t* p);
+int igmk_pop_upload(igmk_pop_t* p, const float* crd /* [n_bead][n_struct][3] */);
+int igmk_pop_download(igmk_pop_t* p, float* crd);
+/* device pointer to the coordinate slab (for callers that keep data resident) */
+int igmk_pop_coords_devptr(igmk_pop_t* p, void** dptr);
+
+/*
+ * get_actdist (ActivationDistanceStep.py:319-459) for a batch of haploid pairs,
+ * including the "%6d %6d %10.4f %.4f" text round trip and float32 parse of
+ * :39/:241.  Inputs: pair_i/pair_j haploid indices, pwish/plast as float64
+ * (what the .in.npy batches hold, :179).  Outputs, sized for the worst case
+ * n_pairs*max_copies^2 rows: row/col bead ids, dist/prob float32 exactly as
+ * they would land in actdist.hdf5.  *n_rows_out = rows produced; rows appear
+ * in pair order, copy pairs in the reference's emission order.
+ */
+int igmk_pop_actdist(igmk_pop_t* p, int64_t n_pairs,
+                     const int32_t* pair_i, const int32_t* pair_j,
+                     const double* pwish, const double* plast,
+                     double contact_range,
+                     int64_t max_rows, int32_t* row, int32_t* col,
+                     float* dist, float* prob, int64_t* n_rows_out);
+
+/*
+ * Contact assignment: for every actdist row r and every structure s decide
+ * `np.linalg.norm(x_i - x_j) <= dist[r]` with the reference arithmetic
+ * (inter_hic.py:53, intra_hic.py:54, particle.py:35-36).  Output is a bit
+ * matrix bits[r][ceil(n_struct/32)] (bit s%32 of word s/32), host memory.
+ */
+int igmk_pop_assign(igmk_pop_t* p, int64_t n_rows,
+                    const int32_t* row, const int32_t* col, const float* dist,
+                    uint32_t* bits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGMK_H */
