@@ -178,6 +178,8 @@ _SIGNATURES = {
     "igmk_destroy": (C.c_int, [_vp]),
     "igmk_clear": (C.c_int, [_vp]),
     "igmk_submit": (C.c_int, [_vp, C.POINTER(System), c_i32p]),
+    "igmk_upload": (C.c_int, [_vp]),
+    "igmk_reset_coordinates": (C.c_int, [_vp]),
     "igmk_run": (C.c_int, [_vp, C.POINTER(Protocol)]),
     "igmk_single_point": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double]),
     "igmk_single_point_f32": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double]),
@@ -192,6 +194,14 @@ _SIGNATURES = {
     "igmk_pop_actdist": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f64p, c_f64p, C.c_double,
                                    C.c_int64, c_i32p, c_i32p, c_f32p, c_f32p, c_i64p]),
     "igmk_pop_assign": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p, c_u32p]),
+    "igmk_pop_attach_coords": (C.c_int, [_vp, _vp]),
+    "igmk_pop_last_kernel_ms": (C.c_double, [_vp]),
+    "igmk_pop_set_pairs": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f64p, c_f64p]),
+    "igmk_pop_actdist_launch": (C.c_int, [_vp, C.c_double]),
+    "igmk_pop_actdist_collect": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p, c_f32p, c_i64p]),
+    "igmk_pop_set_rows": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p]),
+    "igmk_pop_assign_launch": (C.c_int, [_vp]),
+    "igmk_pop_assign_collect": (C.c_int, [_vp, c_u32p]),
 }
 
 

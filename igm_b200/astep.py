@@ -1,0 +1,158 @@
+"""A-step host side: a device-resident population and the two Hi-C A-step operations.
+
+``Population.actdist`` is ``ActivationDistanceStep.task`` + the parse in ``reduce``
+(igm/steps/ActivationDistanceStep.py:192-222, :238-249) for one batch of haploid pairs;
+``Population.assign`` evaluates the contact-assignment predicate of
+``interHiC._apply`` / ``intraHiC._apply`` (igm/restraints/inter_hic.py:49-64,
+intra_hic.py:50-65) for every (actdist row, structure).  Both run on the GPU through the C ABI
+and fail loudly without it.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+
+
+def copy_index_to_csr(copy_index, n_hap=None):
+    """Index.copy_index (dict haploid bin -> list of bead ids) -> (copy_off, copy_beads)."""
+    if n_hap is None:
+        n_hap = len(copy_index)
+    off = np.zeros(n_hap + 1, dtype=np.int32)
+    beads = []
+    for h in range(n_hap):
+        ids = copy_index[h] if h in copy_index else copy_index[str(h)]
+        beads.extend(int(b) for b in ids)
+        off[h + 1] = len(beads)
+    return off, np.array(beads, dtype=np.int32)
+
+
+class Population(object):
+    """coordinates[bead][struct][3] float32 (the .hss layout) resident on one GPU."""
+
+    def __init__(self, n_struct, radii, chrom, copy_off, copy_beads, device=0):
+        self._lib = _abi.load()
+        self.radii = np.ascontiguousarray(radii, dtype=np.float32)
+        self.chrom = np.ascontiguousarray(chrom, dtype=np.int32)
+        self.copy_off = np.ascontiguousarray(copy_off, dtype=np.int32)
+        self.copy_beads = np.ascontiguousarray(copy_beads, dtype=np.int32)
+        self.n_bead = int(self.radii.size)
+        self.n_struct = int(n_struct)
+        self.n_hap = int(self.copy_off.size - 1)
+        self.max_copies = int(np.diff(self.copy_off).max())
+        self._keep = None
+        self._p = C.c_void_p()
+        _abi.check(self._lib.igmk_pop_create(
+            int(device), self.n_bead, self.n_struct, self.n_hap,
+            self.radii.ctypes.data_as(_abi.c_f32p), self.chrom.ctypes.data_as(_abi.c_i32p),
+            self.copy_off.ctypes.data_as(_abi.c_i32p), self.copy_beads.ctypes.data_as(_abi.c_i32p),
+            C.byref(self._p)), "igmk_pop_create")
+
+    def close(self):
+        if self._p:
+            self._lib.igmk_pop_destroy(self._p)
+            self._p = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+        return False
+
+    # ---- coordinates ------------------------------------------------------------------
+    def _check_crd(self, crd):
+        if crd.dtype != np.float32 or crd.shape != (self.n_bead, self.n_struct, 3) or not crd.flags.c_contiguous:
+            raise ValueError("coordinates must be C-contiguous float32 [%d][%d][3]" % (self.n_bead, self.n_struct))
+
+    def upload(self, crd):
+        self._check_crd(crd)
+        _abi.check(self._lib.igmk_pop_upload(self._p, crd.ctypes.data_as(_abi.c_f32p)), "igmk_pop_upload")
+
+    def download(self):
+        crd = np.empty((self.n_bead, self.n_struct, 3), dtype=np.float32)
+        _abi.check(self._lib.igmk_pop_download(self._p, crd.ctypes.data_as(_abi.c_f32p)), "igmk_pop_download")
+        return crd
+
+    def attach(self, tensor):
+        """Use a caller-owned CUDA tensor (float32 [n_bead][n_struct][3], contiguous) as the slab."""
+        if tuple(tensor.shape) != (self.n_bead, self.n_struct, 3) or not tensor.is_contiguous() \
+                or str(tensor.dtype) != "torch.float32" or not tensor.is_cuda:
+            raise ValueError("attach() needs a contiguous CUDA float32 tensor [%d][%d][3]" % (self.n_bead, self.n_struct))
+        _abi.check(self._lib.igmk_pop_attach_coords(self._p, C.c_void_p(tensor.data_ptr())), "igmk_pop_attach_coords")
+        self._keep = tensor
+
+    def last_kernel_ms(self):
+        return float(self._lib.igmk_pop_last_kernel_ms(self._p))
+
+    # ---- activation distances -----------------------------------------------------------
+    def set_pairs(self, pair_i, pair_j, pwish, plast):
+        pi = np.ascontiguousarray(pair_i, dtype=np.int32)
+        pj = np.ascontiguousarray(pair_j, dtype=np.int32)
+        pw = np.ascontiguousarray(pwish, dtype=np.float64)
+        pl = np.ascontiguousarray(plast, dtype=np.float64)
+        if not (pi.size == pj.size == pw.size == pl.size):
+            raise ValueError("pair arrays differ in length")
+        self._n_pairs = int(pi.size)
+        _abi.check(self._lib.igmk_pop_set_pairs(
+            self._p, pi.size, pi.ctypes.data_as(_abi.c_i32p), pj.ctypes.data_as(_abi.c_i32p),
+            pw.ctypes.data_as(_abi.c_f64p), pl.ctypes.data_as(_abi.c_f64p)), "igmk_pop_set_pairs")
+
+    def actdist_launch(self, contact_range=2.0):
+        _abi.check(self._lib.igmk_pop_actdist_launch(self._p, float(contact_range)), "igmk_pop_actdist_launch")
+
+    def actdist_collect(self):
+        cap = max(1, self._n_pairs * self.max_copies * self.max_copies)
+        row = np.empty(cap, dtype=np.int32)
+        col = np.empty(cap, dtype=np.int32)
+        dist = np.empty(cap, dtype=np.float32)
+        prob = np.empty(cap, dtype=np.float32)
+        n = C.c_int64(0)
+        _abi.check(self._lib.igmk_pop_actdist_collect(
+            self._p, cap, row.ctypes.data_as(_abi.c_i32p), col.ctypes.data_as(_abi.c_i32p),
+            dist.ctypes.data_as(_abi.c_f32p), prob.ctypes.data_as(_abi.c_f32p), C.byref(n)), "igmk_pop_actdist_collect")
+        k = n.value
+        return row[:k], col[:k], dist[:k], prob[:k]
+
+    def actdist(self, pair_i, pair_j, pwish, plast, contact_range=2.0):
+        """-> (row i4, col i4, dist f4, prob f4): the rows this batch contributes to
+        actdist.hdf5 (ActivationDistanceStep.py:277-281), bit for bit."""
+        self.set_pairs(pair_i, pair_j, pwish, plast)
+        self.actdist_launch(contact_range)
+        return self.actdist_collect()
+
+    # ---- contact assignment ---------------------------------------------------------------
+    def set_rows(self, row, col, dist):
+        r = np.ascontiguousarray(row, dtype=np.int32)
+        c = np.ascontiguousarray(col, dtype=np.int32)
+        d = np.ascontiguousarray(dist, dtype=np.float32)
+        if not (r.size == c.size == d.size):
+            raise ValueError("row arrays differ in length")
+        self._n_rows = int(r.size)
+        _abi.check(self._lib.igmk_pop_set_rows(self._p, r.size, r.ctypes.data_as(_abi.c_i32p),
+                                               c.ctypes.data_as(_abi.c_i32p), d.ctypes.data_as(_abi.c_f32p)),
+                   "igmk_pop_set_rows")
+
+    def assign_launch(self):
+        _abi.check(self._lib.igmk_pop_assign_launch(self._p), "igmk_pop_assign_launch")
+
+    def assign_collect(self):
+        nw = (self.n_struct + 31) // 32
+        bits = np.zeros((self._n_rows, nw), dtype=np.uint32)
+        _abi.check(self._lib.igmk_pop_assign_collect(self._p, bits.ctypes.data_as(_abi.c_u32p)), "igmk_pop_assign_collect")
+        return bits
+
+    def assign(self, row, col, dist):
+        """-> uint32 [n_rows][ceil(n_struct/32)]; bit s%32 of word s//32 set <=> structure s
+        gets a HarmonicUpperBound for that row (inter_hic.py:53-62, intra_hic.py:54-63)."""
+        self.set_rows(row, col, dist)
+        self.assign_launch()
+        return self.assign_collect()
+
+
+def unpack_bits(bits, n_struct):
+    """uint32 [n_rows][nw] -> bool [n_rows][n_struct]"""
+    b = (bits[:, :, None] >> np.arange(32, dtype=np.uint32)) & np.uint32(1)
+    return b.reshape(bits.shape[0], -1)[:, :n_struct].astype(bool)

@@ -1,0 +1,187 @@
+// astep.cuh -- A-step device code (Hi-C activation distances + contact assignment).
+//
+// k_actdist restates get_actdist (igm/steps/ActivationDistanceStep.py:319-459) bit for bit:
+// float32 squared distances with the association ((dx^2+dy^2)+dz^2) and no FMA contraction,
+// float64 probability correction (cleanProbability, :306-315), an exact order statistic in
+// place of np.sort (:425,:446), float64 sqrt, and the "%10.4f"/"%.4f" text round trip + float32
+// parse of :39/:241 done arithmetically.
+// k_assign restates the predicate of inter_hic.py:53 / intra_hic.py:54 with the arithmetic of
+// np.linalg.norm on a float32 3-vector (OpenBLAS sdot: float32 products, double accumulator).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace igmk {
+
+constexpr int AD_THREADS = 256;
+constexpr int AD_MAX_COPIES = 4;          // copies per haploid bin (diploid = 2)
+
+struct PopView {
+    int32_t n_bead, n_struct, n_hap;
+    const float*   crd;        // [n_bead][n_struct][3]
+    const float*   radii;      // [n_bead]
+    const int32_t* chrom;      // [n_bead]
+    const int32_t* copy_off;   // [n_hap+1]
+    const int32_t* copy_beads;
+};
+
+// "%.{4}f" % x followed by float(str): the decimal string is the exact value of x rounded
+// half-to-even to 4 decimals (glibc printf is exact), and parsing it gives the double nearest to
+// r / 10^4 -- which is what IEEE division of the two exactly representable numbers returns.
+// Then np.genfromtxt casts that double to float32.
+__device__ __forceinline__ float text_roundtrip4(double x)
+{
+    const double p = x * 1.0e4;                       // rounded product
+    const double err = fma(x, 1.0e4, -p);             // exact residual: x*1e4 = p + err
+    double r = rint(p);                               // half-to-even on p
+    const double fl = floor(p);
+    if (p - fl == 0.5) {                              // p is an exact tie: the residual decides
+        if (err > 0.0) r = fl + 1.0;
+        else if (err < 0.0) r = fl;
+    }
+    return (float)(r / 1.0e4);
+}
+
+// order-preserving key for non-negative floats is the bit pattern itself
+__device__ __forceinline__ uint32_t fkey(float v) { return __float_as_uint(v); }
+
+// One CTA per haploid pair.  Shared memory holds the n_comb * n_struct squared distances.
+// Per-pair outputs: valid flag, activation distance and corrected probability (both already
+// through the text round trip), number of copy combinations emitted.
+__global__ void __launch_bounds__(AD_THREADS)
+k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const int32_t* __restrict__ pair_j,
+          const double* __restrict__ pwish, const double* __restrict__ plast, float contact_range_f32,
+          float* __restrict__ out_dist, float* __restrict__ out_prob, uint8_t* __restrict__ out_valid)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* dsq = (float*)smem_raw;
+    __shared__ int s_red[2][AD_THREADS / 32];
+    __shared__ uint32_t s_mm[2][AD_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int S = P.n_struct;
+
+    for (int64_t pidx = blockIdx.x; pidx < n_pairs; pidx += gridDim.x) {
+        const int hi = pair_i[pidx], hj = pair_j[pidx];
+        if (hi == hj) {                                   // :351-352
+            if (tid == 0) out_valid[pidx] = 0;
+            continue;
+        }
+        const int io = P.copy_off[hi], jo = P.copy_off[hj];
+        const int ni = P.copy_off[hi + 1] - io, nj = P.copy_off[hj + 1] - jo;
+        const bool intra = P.chrom[hi] == P.chrom[hj];
+        const int ncomb = intra ? min(ni, nj) : ni * nj;  // n_possible_contacts, :384-385,:400-401
+        const float ri = P.radii[P.copy_beads[io]], rj = P.radii[P.copy_beads[jo]];
+        const float rc = __fmul_rn(contact_range_f32, __fadd_rn(ri, rj));
+        const float rcutsq = __fmul_rn(rc, rc);           // :368, float32 under numpy >= 2
+        const int total = ncomb * S;
+
+        // ---- squared distances (A1) + contact count (A2) + min/max key ----
+        int cnt = 0;
+        uint32_t kmin = 0xffffffffu, kmax = 0u;
+        for (int c = 0; c < ncomb; c++) {
+            const int bi = P.copy_beads[io + (intra ? c : c / nj)];
+            const int bj = P.copy_beads[jo + (intra ? c : c % nj)];
+            const float* xi = P.crd + (size_t)bi * S * 3;
+            const float* xj = P.crd + (size_t)bj * S * 3;
+            for (int s = tid; s < S; s += AD_THREADS) {
+                const float dx = __fsub_rn(xi[3 * s], xj[3 * s]);
+                const float dy = __fsub_rn(xi[3 * s + 1], xj[3 * s + 1]);
+                const float dz = __fsub_rn(xi[3 * s + 2], xj[3 * s + 2]);
+                const float v = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                dsq[c * S + s] = v;
+                cnt += (v <= rcutsq);
+                const uint32_t k = fkey(v);
+                kmin = min(kmin, k); kmax = max(kmax, k);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+            kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+            kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+        }
+        if (lane == 0) { s_red[0][warp] = cnt; s_mm[0][warp] = kmin; s_mm[1][warp] = kmax; }
+        __syncthreads();
+        cnt = 0; kmin = 0xffffffffu; kmax = 0u;
+#pragma unroll
+        for (int w = 0; w < AD_THREADS / 32; w++) { cnt += s_red[0][w]; kmin = min(kmin, s_mm[0][w]); kmax = max(kmax, s_mm[1][w]); }
+
+        // ---- probability correction (A4), float64 exactly as the host does it ----
+        const double pnow = (double)cnt / (double)(ncomb * S);                  // :422
+        const double pl = plast[pidx], pw = pwish[pidx];
+        double t = pl < 1.0 ? (pnow - pl) / (1.0 - pl) : pnow; t = t > 0.0 ? t : 0.0;   // :430
+        double p = t < 1.0 ? (pw - t) / (1.0 - t) : pw; p = p > 0.0 ? p : 0.0;          // :434
+        if (!(p > 0.0)) {
+            if (tid == 0) out_valid[pidx] = 0;
+            __syncthreads();
+            continue;
+        }
+        // o = min(n*S-1, int(round(n*p*S))), product left to right, round half to even  (:443-444)
+        const double prod = ((double)ncomb * p) * (double)S;
+        long long o = (long long)rint(prod);
+        if (o > (long long)total - 1) o = total - 1;
+
+        // ---- exact o-th smallest (A3): MSB-first descent over the float bit patterns.
+        //      All keys share the bits above the highest bit in which min and max differ.
+        uint32_t prefix, k = (uint32_t)o;
+        int bit;
+        if (kmin == kmax) { prefix = kmin; bit = -1; }
+        else { bit = 31 - __clz(kmin ^ kmax); prefix = (bit == 31) ? 0u : (kmin >> (bit + 1)) << (bit + 1); }
+        int par = 1;
+        for (; bit >= 0; bit--) {
+            const uint32_t hmask = (bit == 31) ? 0u : (0xffffffffu << (bit + 1));
+            int c0 = 0;                                   // keys matching the prefix with this bit clear
+            for (int q = tid; q < total; q += AD_THREADS) {
+                const uint32_t key = fkey(dsq[q]);
+                c0 += ((key & hmask) == prefix) && !((key >> bit) & 1u);
+            }
+#pragma unroll
+            for (int o2 = 16; o2 > 0; o2 >>= 1) c0 += __shfl_xor_sync(0xffffffffu, c0, o2);
+            if (lane == 0) s_red[par][warp] = c0;
+            __syncthreads();
+            c0 = 0;
+#pragma unroll
+            for (int w = 0; w < AD_THREADS / 32; w++) c0 += s_red[par][w];
+            par ^= 1;
+            if (k >= (uint32_t)c0) { k -= (uint32_t)c0; prefix |= (1u << bit); }
+        }
+        if (tid == 0) {
+            const double ad = sqrt((double)__uint_as_float(prefix));            // :446
+            out_dist[pidx] = text_roundtrip4(ad);
+            out_prob[pidx] = text_roundtrip4(p);
+            out_valid[pidx] = 1;
+        }
+        __syncthreads();
+    }
+}
+
+// Contact assignment.  One warp per actdist row, lanes over structures; 32 rows per CTA.
+// bits[r][w] bit l  <=>  structure 32*w+l gets a bond for row r.
+__global__ void __launch_bounds__(1024)
+k_assign(PopView P, int64_t n_rows, const int32_t* __restrict__ row, const int32_t* __restrict__ col,
+         const float* __restrict__ dist, uint32_t* __restrict__ bits)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int S = P.n_struct, nw = (S + 31) >> 5;
+    for (int64_t r = (int64_t)blockIdx.x * 32 + warp; r < n_rows; r += (int64_t)gridDim.x * 32) {
+        const float* xi = P.crd + (size_t)row[r] * S * 3;
+        const float* xj = P.crd + (size_t)col[r] * S * 3;
+        const float d = dist[r];
+        for (int w = 0; w < nw; w++) {
+            const int s = w * 32 + lane;
+            bool hit = false;
+            if (s < S) {
+                const float dx = __fsub_rn(xi[3 * s], xj[3 * s]);
+                const float dy = __fsub_rn(xi[3 * s + 1], xj[3 * s + 1]);
+                const float dz = __fsub_rn(xi[3 * s + 2], xj[3 * s + 2]);
+                const double acc = __dadd_rn(__dadd_rn((double)__fmul_rn(dx, dx), (double)__fmul_rn(dy, dy)),
+                                             (double)__fmul_rn(dz, dz));
+                hit = __fsqrt_rn(__double2float_rn(acc)) <= d;
+            }
+            const uint32_t b = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) bits[r * nw + w] = b;
+        }
+    }
+}
+
+}  // namespace igmk

@@ -1,0 +1,717 @@
+// igmk.cu -- host side of the C ABI declared in include/igmk.h.
+// Owns device memory, packs submitted structures into the flat batch layout of mstep.cuh,
+// launches the kernels and copies results back.  No exceptions cross the ABI.
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <map>
+#include <tuple>
+#include <algorithm>
+#include <cuda_runtime.h>
+
+#include "../../include/igmk.h"
+#include "mstep.cuh"
+#include "astep.cuh"
+
+using namespace igmk;
+
+static thread_local std::string g_err;
+
+static int fail(const std::string& s) { g_err = s; return 1; }
+static const int IGMK_NL_OVERFLOW = 100;   // internal: retry with a wider neighbour table
+
+#define CU(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            char b_[512];                                                                     \
+            snprintf(b_, sizeof b_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            return fail(b_);                                                                  \
+        }                                                                                     \
+    } while (0)
+
+template <typename T>
+static cudaError_t dev_alloc_copy(T** dptr, const std::vector<T>& h)
+{
+    size_t bytes = std::max<size_t>(h.size(), 1) * sizeof(T);
+    cudaError_t e = cudaMalloc((void**)dptr, bytes);
+    if (e != cudaSuccess) return e;
+    if (!h.empty()) e = cudaMemcpy(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+    return e;
+}
+
+struct igmk_handle {
+    int device = 0;
+    int smem_optin = 0;
+    // host staging
+    std::vector<StructDesc> desc;
+    std::vector<float4>   xyzr;         // current coordinates (results land here)
+    std::vector<float4>   xyzr0;        // coordinates as submitted
+    std::vector<uint8_t>  kind;
+    std::vector<uint32_t> envmask;
+    std::vector<int32_t>  bond_ptr;
+    std::vector<uint32_t> bond_items;
+    std::vector<float2>   btype_f;
+    std::vector<double2>  btype_d;
+    std::vector<int64_t>  struct_id;
+    int max_atoms = 0;
+    int nl_width = NL_WIDTH0;
+    bool dirty = true;
+    // device
+    StructDesc* d_desc = nullptr; float4* d_xyzr = nullptr; uint8_t* d_kind = nullptr; uint32_t* d_envmask = nullptr;
+    int32_t* d_bond_ptr = nullptr; uint32_t* d_bond_items = nullptr; float2* d_btype_f = nullptr; double2* d_btype_d = nullptr;
+    uint16_t* d_nl = nullptr; uint16_t* d_nl_cnt = nullptr; double* d_xd = nullptr; double* d_fd = nullptr; double* d_work = nullptr;
+    igmk_result_t* d_res = nullptr; int32_t* d_flags = nullptr;
+    // results
+    std::vector<igmk_result_t> res;
+    std::vector<int32_t> flags;
+    std::vector<double> forces;
+    bool have_forces = false;
+
+    void free_device()
+    {
+        cudaFree(d_desc); cudaFree(d_xyzr); cudaFree(d_kind); cudaFree(d_envmask); cudaFree(d_bond_ptr);
+        cudaFree(d_bond_items); cudaFree(d_btype_f); cudaFree(d_btype_d); cudaFree(d_nl); cudaFree(d_nl_cnt);
+        cudaFree(d_xd); cudaFree(d_fd); cudaFree(d_work); cudaFree(d_res); cudaFree(d_flags);
+        d_desc = nullptr; d_xyzr = nullptr; d_kind = nullptr; d_envmask = nullptr; d_bond_ptr = nullptr;
+        d_bond_items = nullptr; d_btype_f = nullptr; d_btype_d = nullptr; d_nl = nullptr; d_nl_cnt = nullptr;
+        d_xd = nullptr; d_fd = nullptr; d_work = nullptr; d_res = nullptr; d_flags = nullptr;
+    }
+};
+
+extern "C" const char* igmk_last_error(void) { return g_err.c_str(); }
+extern "C" int igmk_version(void) { return 100; }
+extern "C" int igmk_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" int igmk_create(int device, igmk_handle_t** out)
+{
+    if (!out) return fail("igmk_create: out is NULL");
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail("igmk_create: no such CUDA device");
+    CU(cudaSetDevice(device));
+    igmk_handle* h = new igmk_handle();
+    h->device = device;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    h->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    *out = h;
+    return 0;
+}
+
+extern "C" int igmk_destroy(igmk_handle_t* h)
+{
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    h->free_device();
+    delete h;
+    return 0;
+}
+
+extern "C" int igmk_clear(igmk_handle_t* h)
+{
+    if (!h) return fail("igmk_clear: NULL handle");
+    cudaSetDevice(h->device);
+    h->free_device();
+    h->desc.clear(); h->xyzr.clear(); h->xyzr0.clear(); h->kind.clear(); h->envmask.clear(); h->bond_ptr.clear();
+    h->bond_items.clear(); h->btype_f.clear(); h->btype_d.clear(); h->struct_id.clear();
+    h->res.clear(); h->flags.clear(); h->forces.clear();
+    h->max_atoms = 0; h->dirty = true; h->have_forces = false;
+    return 0;
+}
+
+extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* slot_out)
+{
+    if (!h || !s) return fail("igmk_submit: NULL argument");
+    char msg[256];
+    const int n = s->n_atoms;
+    if (n <= 0 || n > 65535) {
+        snprintf(msg, sizeof msg, "igmk_submit: structure %lld has %d atoms (supported: 1..65535)", (long long)s->struct_id, n);
+        return fail(msg);
+    }
+    if (s->n_env < 0 || s->n_env > IGMK_MAX_ENVELOPES) return fail("igmk_submit: too many envelopes");
+    const size_t need = std::max(ctx_smem_bytes<float>(n, true), ctx_smem_bytes<double>(n, false));
+    if ((long long)need > (long long)h->smem_optin) {
+        snprintf(msg, sizeof msg, "igmk_submit: structure %lld with %d atoms needs %zu B of shared memory per CTA, "
+                 "device offers %d B (single-CTA path; larger structures need the cluster path)",
+                 (long long)s->struct_id, n, need, h->smem_optin);
+        return fail(msg);
+    }
+    StructDesc d;
+    memset(&d, 0, sizeof d);
+    d.atom_off = (int32_t)h->xyzr.size();
+    d.n_atoms = n;
+    d.bond_ptr_off = (int32_t)h->bond_ptr.size();
+    d.bond_item_off = (int64_t)h->bond_items.size();
+    d.btype_off = (int32_t)h->btype_f.size();
+    d.n_env = s->n_env;
+    d.evfactor = s->evfactor;
+    d.seed = s->seed;
+    float maxrad = 0.f;
+    int nonfixed = 0;
+    for (int i = 0; i < n; i++) {
+        if (s->kind[i] > 2) return fail("igmk_submit: unknown particle kind");
+        h->xyzr.push_back(make_float4(s->xyz[3 * i], s->xyz[3 * i + 1], s->xyz[3 * i + 2], s->radius[i]));
+        h->xyzr0.push_back(h->xyzr.back());
+        h->kind.push_back(s->kind[i]);
+        if (s->kind[i] == IGMK_KIND_BEAD) maxrad = std::max(maxrad, s->radius[i]);
+        if (s->kind[i] != IGMK_KIND_STATIC) nonfixed++;
+    }
+    d.maxrad = maxrad;
+    d.n_nonfixed = nonfixed;
+    // envelopes -> per-atom membership mask
+    std::vector<uint32_t> mask(n, 0u);
+    for (int e = 0; e < s->n_env; e++) {
+        for (int k = 0; k < 4; k++) d.env[e][k] = s->env_abck[4 * e + k];
+        for (int q = s->env_off[e]; q < s->env_off[e + 1]; q++) {
+            int i = s->env_members[q];
+            if (i < 0 || i >= n) return fail("igmk_submit: envelope member out of range");
+            mask[i] |= 1u << e;
+        }
+    }
+    h->envmask.insert(h->envmask.end(), mask.begin(), mask.end());
+    // bonds -> directional CSR by atom, bond types de-duplicated like LammpsModel.add_bond
+    // (lammps_model.py:314-329) so that the type table stays cache resident
+    std::map<std::tuple<double, double, int>, int> types;
+    std::vector<int32_t> cnt(n + 1, 0);
+    for (int b = 0; b < s->n_bonds; b++) {
+        int i = s->bond_i[b], j = s->bond_j[b];
+        if (i < 0 || i >= n || j < 0 || j >= n) return fail("igmk_submit: bond index out of range");
+        if (s->bond_style[b] > 1) return fail("igmk_submit: unknown bond style");
+        if (!(s->bond_k[b] >= 0.0)) return fail("igmk_submit: bond spring constants must be >= 0");
+        cnt[i + 1]++; cnt[j + 1]++;
+    }
+    for (int i = 0; i < n; i++) cnt[i + 1] += cnt[i];
+    std::vector<uint32_t> items((size_t)cnt[n]);
+    std::vector<int32_t> cur(cnt.begin(), cnt.end() - 1);
+    for (int b = 0; b < s->n_bonds; b++) {
+        auto key = std::make_tuple(s->bond_r0[b], s->bond_k[b], (int)s->bond_style[b]);
+        auto it = types.find(key);
+        int t;
+        if (it == types.end()) {
+            t = (int)types.size();
+            if (t > 65535) return fail("igmk_submit: more than 65536 distinct bond types in one structure");
+            types[key] = t;
+            const double ks = s->bond_style[b] == IGMK_BOND_LOWER ? -s->bond_k[b] : s->bond_k[b];
+            h->btype_f.push_back(make_float2((float)s->bond_r0[b], (float)ks));
+            h->btype_d.push_back(make_double2(s->bond_r0[b], ks));
+        } else t = it->second;
+        const int i = s->bond_i[b], j = s->bond_j[b];
+        items[cur[i]++] = (uint32_t)j | ((uint32_t)t << 16);
+        items[cur[j]++] = (uint32_t)i | ((uint32_t)t << 16);
+    }
+    h->bond_ptr.insert(h->bond_ptr.end(), cnt.begin(), cnt.end());
+    h->bond_items.insert(h->bond_items.end(), items.begin(), items.end());
+    h->desc.push_back(d);
+    h->struct_id.push_back(s->struct_id);
+    h->max_atoms = std::max(h->max_atoms, n);
+    h->dirty = true;
+    if (slot_out) *slot_out = (int32_t)h->desc.size() - 1;
+    return 0;
+}
+
+static int upload(igmk_handle* h)
+{
+    if (!h->dirty) return 0;
+    h->free_device();
+    const size_t na = h->xyzr.size(), ns = h->desc.size();
+    CU(dev_alloc_copy(&h->d_desc, h->desc));
+    CU(dev_alloc_copy(&h->d_xyzr, h->xyzr));
+    CU(dev_alloc_copy(&h->d_kind, h->kind));
+    CU(dev_alloc_copy(&h->d_envmask, h->envmask));
+    CU(dev_alloc_copy(&h->d_bond_ptr, h->bond_ptr));
+    CU(dev_alloc_copy(&h->d_bond_items, h->bond_items));
+    CU(dev_alloc_copy(&h->d_btype_f, h->btype_f));
+    CU(dev_alloc_copy(&h->d_btype_d, h->btype_d));
+    CU(cudaMalloc((void**)&h->d_nl, std::max<size_t>(na, 1) * h->nl_width * sizeof(uint16_t)));
+    CU(cudaMalloc((void**)&h->d_nl_cnt, std::max<size_t>(na, 1) * sizeof(uint16_t)));
+    CU(cudaMalloc((void**)&h->d_xd, std::max<size_t>(na, 1) * 3 * sizeof(double)));
+    CU(cudaMalloc((void**)&h->d_fd, std::max<size_t>(na, 1) * 3 * sizeof(double)));
+    CU(cudaMalloc((void**)&h->d_work, std::max<size_t>(na, 1) * 12 * sizeof(double)));
+    CU(cudaMalloc((void**)&h->d_res, std::max<size_t>(ns, 1) * sizeof(igmk_result_t)));
+    CU(cudaMalloc((void**)&h->d_flags, std::max<size_t>(ns, 1) * sizeof(int32_t)));
+    CU(cudaMemset(h->d_res, 0, std::max<size_t>(ns, 1) * sizeof(igmk_result_t)));
+    CU(cudaMemset(h->d_flags, 0, std::max<size_t>(ns, 1) * sizeof(int32_t)));
+    h->dirty = false;
+    return 0;
+}
+
+extern "C" int igmk_upload(igmk_handle_t* h)
+{
+    if (!h) return fail("igmk_upload: NULL handle");
+    if (h->desc.empty()) return fail("igmk_upload: nothing submitted");
+    CU(cudaSetDevice(h->device));
+    return upload(h);
+}
+
+extern "C" int igmk_reset_coordinates(igmk_handle_t* h)
+{
+    if (!h) return fail("igmk_reset_coordinates: NULL handle");
+    h->xyzr = h->xyzr0;
+    if (!h->dirty && h->d_xyzr) {
+        CU(cudaSetDevice(h->device));
+        CU(cudaMemcpy(h->d_xyzr, h->xyzr0.data(), h->xyzr0.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    }
+    return 0;
+}
+
+static Batch make_batch(igmk_handle* h)
+{
+    Batch B;
+    B.n_struct = (int32_t)h->desc.size(); B.max_atoms = h->max_atoms;
+    B.desc = h->d_desc; B.xyzr = h->d_xyzr; B.kind = h->d_kind; B.envmask = h->d_envmask;
+    B.bond_ptr = h->d_bond_ptr; B.bond_items = h->d_bond_items; B.btype_f = h->d_btype_f; B.btype_d = h->d_btype_d;
+    B.nl = h->d_nl; B.nl_width = h->nl_width; B.nl_cnt = h->d_nl_cnt; B.xd = h->d_xd; B.fd = h->d_fd; B.work = h->d_work;
+    B.res = h->d_res; B.flags = h->d_flags;
+    return B;
+}
+
+static int collect(igmk_handle* h, const char* what)
+{
+    const size_t ns = h->desc.size();
+    h->res.resize(ns); h->flags.resize(ns);
+    CU(cudaMemcpy(h->flags.data(), h->d_flags, ns * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    for (size_t s = 0; s < ns; s++) {
+        if (h->flags[s] & 1) {
+            char msg[256];
+            snprintf(msg, sizeof msg, "%s: neighbour list overflow (> %d neighbours per bead) in structure %lld",
+                     what, h->nl_width, (long long)h->struct_id[s]);
+            fail(msg);
+            return IGMK_NL_OVERFLOW;      // host staging still holds the submitted coordinates
+        }
+    }
+    CU(cudaMemcpy(h->res.data(), h->d_res, ns * sizeof(igmk_result_t), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(h->xyzr.data(), h->d_xyzr, h->xyzr.size() * sizeof(float4), cudaMemcpyDeviceToHost));
+    for (size_t s = 0; s < ns; s++) h->res[s].status = (h->flags[s] & 2) ? 1 : 0;
+    return 0;
+}
+
+// widen the neighbour table after an overflow; false when it already holds every atom
+static bool widen_neighbour_table(igmk_handle* h)
+{
+    if (h->nl_width >= h->max_atoms) return false;
+    h->nl_width = std::min(h->nl_width * 2, (h->max_atoms + 7) / 8 * 8);
+    h->dirty = true;
+    return true;
+}
+
+extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
+{
+    if (!h || !prot) return fail("igmk_run: NULL argument");
+    if (h->desc.empty()) return fail("igmk_run: nothing submitted");
+    if (prot->n_stage < 0 || prot->n_stage > IGMK_MAX_STAGES) return fail("igmk_run: bad n_stage");
+    if (!(prot->timestep > 0.0)) return fail("igmk_run: timestep must be > 0");
+    CU(cudaSetDevice(h->device));
+    const int ns = (int)h->desc.size();
+    const size_t sm_md = ctx_smem_bytes<float>(h->max_atoms, true);
+    const size_t sm_cg = ctx_smem_bytes<double>(h->max_atoms, false);
+    CU(cudaFuncSetAttribute(k_md, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_md));
+    CU(cudaFuncSetAttribute(k_cg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_cg));
+    float ms = 0.f;
+    for (;;) {
+        if (int rc = upload(h)) return rc;
+        Batch B = make_batch(h);
+        CU(cudaMemset(h->d_flags, 0, ns * sizeof(int32_t)));
+        cudaEvent_t e0, e1;
+        CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+        CU(cudaEventRecord(e0));
+        MdParams P; P.prot = *prot;
+        k_md<<<ns, MD_THREADS, sm_md>>>(B, P);
+        CU(cudaGetLastError());
+        k_cg<<<ns, MD_THREADS, sm_cg>>>(B, *prot);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(e1));
+        CU(cudaEventSynchronize(e1));
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        const int rc = collect(h, "igmk_run");
+        if (rc == IGMK_NL_OVERFLOW && widen_neighbour_table(h)) continue;
+        if (rc) return 1;
+        break;
+    }
+    for (auto& r : h->res) r.md_seconds = ms * 1e-3;
+    h->forces.resize(h->xyzr.size() * 3);
+    CU(cudaMemcpy(h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    h->have_forces = true;
+    return 0;
+}
+
+template <typename T>
+static int single_point_impl(igmk_handle* h, double ev_scale, double env_scale, double bond_prefactor)
+{
+    if (!h) return fail("igmk_single_point: NULL handle");
+    if (h->desc.empty()) return fail("igmk_single_point: nothing submitted");
+    CU(cudaSetDevice(h->device));
+    const size_t sm = ctx_smem_bytes<T>(h->max_atoms, false);
+    CU(cudaFuncSetAttribute(k_single_point<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    for (;;) {
+        if (int rc = upload(h)) return rc;
+        Batch B = make_batch(h);
+        CU(cudaMemset(h->d_flags, 0, h->desc.size() * sizeof(int32_t)));
+        k_single_point<T><<<(int)h->desc.size(), MD_THREADS, sm>>>(B, ev_scale, env_scale, bond_prefactor);
+        CU(cudaGetLastError());
+        CU(cudaDeviceSynchronize());
+        const int rc = collect(h, "igmk_single_point");
+        if (rc == IGMK_NL_OVERFLOW && widen_neighbour_table(h)) continue;
+        if (rc) return 1;
+        break;
+    }
+    h->forces.resize(h->xyzr.size() * 3);
+    CU(cudaMemcpy(h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    h->have_forces = true;
+    return 0;
+}
+
+extern "C" int igmk_single_point(igmk_handle_t* h, double ev_scale, double env_scale, double bond_prefactor)
+{
+    return single_point_impl<double>(h, ev_scale, env_scale, bond_prefactor);
+}
+extern "C" int igmk_single_point_f32(igmk_handle_t* h, double ev_scale, double env_scale, double bond_prefactor)
+{
+    return single_point_impl<float>(h, ev_scale, env_scale, bond_prefactor);
+}
+
+extern "C" int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out, igmk_result_t* res)
+{
+    if (!h) return fail("igmk_fetch: NULL handle");
+    if (slot < 0 || slot >= (int)h->desc.size()) return fail("igmk_fetch: bad slot");
+    if (h->res.size() != h->desc.size()) return fail("igmk_fetch: nothing has been run");
+    const StructDesc& d = h->desc[slot];
+    if (xyz_out)
+        for (int i = 0; i < d.n_atoms; i++) {
+            const float4 p = h->xyzr[d.atom_off + i];
+            xyz_out[3 * i] = p.x; xyz_out[3 * i + 1] = p.y; xyz_out[3 * i + 2] = p.z;
+        }
+    if (res) *res = h->res[slot];
+    return 0;
+}
+
+extern "C" int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out)
+{
+    if (!h || !f_out) return fail("igmk_fetch_forces: NULL argument");
+    if (slot < 0 || slot >= (int)h->desc.size()) return fail("igmk_fetch_forces: bad slot");
+    if (!h->have_forces) return fail("igmk_fetch_forces: no forces available");
+    const StructDesc& d = h->desc[slot];
+    memcpy(f_out, h->forces.data() + (size_t)d.atom_off * 3, (size_t)d.n_atoms * 3 * sizeof(double));
+    return 0;
+}
+
+// =========================================================================================
+// A-step
+template <typename T>
+struct DevBuf {
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t reserve(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc((void**)&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct igmk_pop {
+    int device = 0;
+    int smem_optin = 0;
+    int sm_count = 0;
+    int32_t n_bead = 0, n_struct = 0, n_hap = 0;
+    int max_copies = 1;
+    float* d_crd = nullptr; bool own_crd = false;
+    float* d_radii = nullptr; int32_t* d_chrom = nullptr;
+    int32_t* d_copy_off = nullptr; int32_t* d_copy_beads = nullptr;
+    std::vector<int32_t> copy_off, copy_beads, chrom;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+    // staged pair batch (activation distances)
+    int64_t n_pairs = 0;
+    std::vector<int32_t> h_pi, h_pj;
+    DevBuf<int32_t> d_pi, d_pj; DevBuf<double> d_pw, d_pl;
+    DevBuf<float> d_dist, d_prob; DevBuf<uint8_t> d_valid;
+    bool actdist_done = false;
+    // staged actdist rows (assignment)
+    int64_t n_rows = 0;
+    DevBuf<int32_t> d_row, d_col; DevBuf<float> d_rdist; DevBuf<uint32_t> d_bits;
+    bool assign_done = false;
+
+    PopView view() const
+    {
+        PopView v;
+        v.n_bead = n_bead; v.n_struct = n_struct; v.n_hap = n_hap;
+        v.crd = d_crd; v.radii = d_radii; v.chrom = d_chrom; v.copy_off = d_copy_off; v.copy_beads = d_copy_beads;
+        return v;
+    }
+    void free_all()
+    {
+        if (own_crd) cudaFree(d_crd);
+        cudaFree(d_radii); cudaFree(d_chrom); cudaFree(d_copy_off); cudaFree(d_copy_beads);
+        d_pi.release(); d_pj.release(); d_pw.release(); d_pl.release(); d_dist.release(); d_prob.release();
+        d_valid.release(); d_row.release(); d_col.release(); d_rdist.release(); d_bits.release();
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+        if (stream) cudaStreamDestroy(stream);
+    }
+};
+
+extern "C" int igmk_pop_create(int device, int32_t n_bead, int32_t n_struct, int32_t n_hap,
+                               const float* radii, const int32_t* chrom_bead,
+                               const int32_t* copy_off, const int32_t* copy_beads, igmk_pop_t** out)
+{
+    if (!out || !radii || !chrom_bead || !copy_off || !copy_beads) return fail("igmk_pop_create: NULL argument");
+    if (n_bead <= 0 || n_struct <= 0 || n_hap <= 0 || n_hap > n_bead) return fail("igmk_pop_create: bad sizes");
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail("igmk_pop_create: no such CUDA device");
+    CU(cudaSetDevice(device));
+    if (copy_off[0] != 0) return fail("igmk_pop_create: copy_off[0] must be 0");
+    int max_copies = 1;
+    for (int i = 0; i < n_hap; i++) {
+        int c = copy_off[i + 1] - copy_off[i];
+        if (c < 1 || c > AD_MAX_COPIES) return fail("igmk_pop_create: every haploid bin needs 1..4 copies");
+        max_copies = std::max(max_copies, c);
+    }
+    for (int q = 0; q < copy_off[n_hap]; q++)
+        if (copy_beads[q] < 0 || copy_beads[q] >= n_bead) return fail("igmk_pop_create: copy bead out of range");
+    igmk_pop* p = new igmk_pop();
+    p->device = device; p->n_bead = n_bead; p->n_struct = n_struct; p->n_hap = n_hap; p->max_copies = max_copies;
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    p->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    p->sm_count = prop.multiProcessorCount;
+    p->copy_off.assign(copy_off, copy_off + n_hap + 1);
+    p->copy_beads.assign(copy_beads, copy_beads + copy_off[n_hap]);
+    p->chrom.assign(chrom_bead, chrom_bead + n_bead);
+    CU(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&p->ev0)); CU(cudaEventCreate(&p->ev1));
+    CU(cudaMalloc((void**)&p->d_crd, (size_t)n_bead * n_struct * 3 * sizeof(float)));
+    p->own_crd = true;
+    CU(cudaMalloc((void**)&p->d_radii, (size_t)n_bead * sizeof(float)));
+    CU(cudaMalloc((void**)&p->d_chrom, (size_t)n_bead * sizeof(int32_t)));
+    CU(cudaMalloc((void**)&p->d_copy_off, (size_t)(n_hap + 1) * sizeof(int32_t)));
+    CU(cudaMalloc((void**)&p->d_copy_beads, p->copy_beads.size() * sizeof(int32_t)));
+    CU(cudaMemcpy(p->d_radii, radii, (size_t)n_bead * sizeof(float), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p->d_chrom, chrom_bead, (size_t)n_bead * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p->d_copy_off, copy_off, (size_t)(n_hap + 1) * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(p->d_copy_beads, p->copy_beads.data(), p->copy_beads.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    *out = p;
+    return 0;
+}
+
+extern "C" int igmk_pop_destroy(igmk_pop_t* p)
+{
+    if (!p) return 0;
+    cudaSetDevice(p->device);
+    p->free_all();
+    delete p;
+    return 0;
+}
+
+extern "C" int igmk_pop_upload(igmk_pop_t* p, const float* crd)
+{
+    if (!p || !crd) return fail("igmk_pop_upload: NULL argument");
+    CU(cudaSetDevice(p->device));
+    CU(cudaMemcpyAsync(p->d_crd, crd, (size_t)p->n_bead * p->n_struct * 3 * sizeof(float), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
+extern "C" int igmk_pop_download(igmk_pop_t* p, float* crd)
+{
+    if (!p || !crd) return fail("igmk_pop_download: NULL argument");
+    CU(cudaSetDevice(p->device));
+    CU(cudaMemcpyAsync(crd, p->d_crd, (size_t)p->n_bead * p->n_struct * 3 * sizeof(float), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
+extern "C" int igmk_pop_coords_devptr(igmk_pop_t* p, void** dptr)
+{
+    if (!p || !dptr) return fail("igmk_pop_coords_devptr: NULL argument");
+    *dptr = p->d_crd;
+    return 0;
+}
+
+extern "C" int igmk_pop_attach_coords(igmk_pop_t* p, void* dptr)
+{
+    if (!p || !dptr) return fail("igmk_pop_attach_coords: NULL argument");
+    CU(cudaSetDevice(p->device));
+    cudaPointerAttributes a;
+    CU(cudaPointerGetAttributes(&a, dptr));
+    if (a.type != cudaMemoryTypeDevice || a.device != p->device)
+        return fail("igmk_pop_attach_coords: not a device pointer of this population's GPU");
+    if (p->own_crd) cudaFree(p->d_crd);
+    p->d_crd = (float*)dptr; p->own_crd = false;
+    return 0;
+}
+
+extern "C" double igmk_pop_last_kernel_ms(igmk_pop_t* p) { return p ? (double)p->last_ms : 0.0; }
+
+extern "C" int igmk_pop_set_pairs(igmk_pop_t* p, int64_t n_pairs, const int32_t* pair_i, const int32_t* pair_j,
+                                  const double* pwish, const double* plast)
+{
+    if (!p) return fail("igmk_pop_set_pairs: NULL handle");
+    if (n_pairs < 0) return fail("igmk_pop_set_pairs: negative pair count");
+    p->n_pairs = 0; p->actdist_done = false;
+    if (n_pairs == 0) return 0;
+    if (!pair_i || !pair_j || !pwish || !plast) return fail("igmk_pop_set_pairs: NULL argument");
+    for (int64_t k = 0; k < n_pairs; k++)
+        if (pair_i[k] < 0 || pair_i[k] >= p->n_hap || pair_j[k] < 0 || pair_j[k] >= p->n_hap)
+            return fail("igmk_pop_set_pairs: haploid index out of range");
+    CU(cudaSetDevice(p->device));
+    CU(p->d_pi.reserve(n_pairs)); CU(p->d_pj.reserve(n_pairs)); CU(p->d_pw.reserve(n_pairs)); CU(p->d_pl.reserve(n_pairs));
+    CU(p->d_dist.reserve(n_pairs)); CU(p->d_prob.reserve(n_pairs)); CU(p->d_valid.reserve(n_pairs));
+    CU(cudaMemcpyAsync(p->d_pi.p, pair_i, n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_pj.p, pair_j, n_pairs * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_pw.p, pwish, n_pairs * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_pl.p, plast, n_pairs * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+    p->h_pi.assign(pair_i, pair_i + n_pairs); p->h_pj.assign(pair_j, pair_j + n_pairs);
+    CU(cudaStreamSynchronize(p->stream));
+    p->n_pairs = n_pairs;
+    return 0;
+}
+
+extern "C" int igmk_pop_actdist_launch(igmk_pop_t* p, double contact_range)
+{
+    if (!p) return fail("igmk_pop_actdist_launch: NULL handle");
+    p->last_ms = 0.f;
+    if (p->n_pairs == 0) { p->actdist_done = true; return 0; }
+    CU(cudaSetDevice(p->device));
+    const size_t smem = (size_t)p->max_copies * p->max_copies * p->n_struct * sizeof(float);
+    if ((long long)smem + 1024 > (long long)p->smem_optin) {
+        char msg[256];
+        snprintf(msg, sizeof msg, "igmk_pop_actdist: %d copy pairs x %d structures need %zu B of shared memory per CTA (limit %d)",
+                 p->max_copies * p->max_copies, p->n_struct, smem, p->smem_optin);
+        return fail(msg);
+    }
+    CU(cudaFuncSetAttribute(k_actdist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_actdist, AD_THREADS, smem));
+    if (per_sm < 1) per_sm = 1;
+    const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * per_sm);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_actdist<<<(int)grid, AD_THREADS, smem, p->stream>>>(p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, p->d_pw.p, p->d_pl.p,
+                                                          (float)contact_range, p->d_dist.p, p->d_prob.p, p->d_valid.p);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(p->ev1, p->stream));
+    CU(cudaEventSynchronize(p->ev1));
+    CU(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+    p->actdist_done = true;
+    return 0;
+}
+
+extern "C" int igmk_pop_actdist_collect(igmk_pop_t* p, int64_t max_rows, int32_t* row, int32_t* col, float* dist,
+                                        float* prob, int64_t* n_rows_out)
+{
+    if (!p || !n_rows_out) return fail("igmk_pop_actdist_collect: NULL argument");
+    *n_rows_out = 0;
+    if (!p->actdist_done) return fail("igmk_pop_actdist_collect: no launch to collect");
+    const int64_t n_pairs = p->n_pairs;
+    if (n_pairs == 0) return 0;
+    if (!row || !col || !dist || !prob) return fail("igmk_pop_actdist_collect: NULL argument");
+    CU(cudaSetDevice(p->device));
+    std::vector<float> hd(n_pairs), hp(n_pairs);
+    std::vector<uint8_t> hv(n_pairs);
+    CU(cudaMemcpyAsync(hd.data(), p->d_dist.p, n_pairs * sizeof(float), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaMemcpyAsync(hp.data(), p->d_prob.p, n_pairs * sizeof(float), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaMemcpyAsync(hv.data(), p->d_valid.p, n_pairs * sizeof(uint8_t), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    // expand to rows in the reference's emission order (ActivationDistanceStep.py:450-456)
+    int64_t nr = 0;
+    for (int64_t k = 0; k < n_pairs; k++) {
+        if (!hv[k]) continue;
+        const int hi = p->h_pi[k], hj = p->h_pj[k];
+        const int io = p->copy_off[hi], jo = p->copy_off[hj];
+        const int ni = p->copy_off[hi + 1] - io, nj = p->copy_off[hj + 1] - jo;
+        const bool intra = p->chrom[hi] == p->chrom[hj];
+        const int ne = intra ? std::min(ni, nj) : ni * nj;
+        if (nr + ne > max_rows) return fail("igmk_pop_actdist_collect: output buffers too small");
+        for (int c = 0; c < ne; c++) {
+            row[nr] = p->copy_beads[io + (intra ? c : c / nj)];
+            col[nr] = p->copy_beads[jo + (intra ? c : c % nj)];
+            dist[nr] = hd[k]; prob[nr] = hp[k];
+            nr++;
+        }
+    }
+    *n_rows_out = nr;
+    return 0;
+}
+
+extern "C" int igmk_pop_actdist(igmk_pop_t* p, int64_t n_pairs, const int32_t* pair_i, const int32_t* pair_j,
+                                const double* pwish, const double* plast, double contact_range,
+                                int64_t max_rows, int32_t* row, int32_t* col, float* dist, float* prob,
+                                int64_t* n_rows_out)
+{
+    if (int rc = igmk_pop_set_pairs(p, n_pairs, pair_i, pair_j, pwish, plast)) return rc;
+    if (int rc = igmk_pop_actdist_launch(p, contact_range)) return rc;
+    return igmk_pop_actdist_collect(p, max_rows, row, col, dist, prob, n_rows_out);
+}
+
+extern "C" int igmk_pop_set_rows(igmk_pop_t* p, int64_t n_rows, const int32_t* row, const int32_t* col, const float* dist)
+{
+    if (!p) return fail("igmk_pop_set_rows: NULL handle");
+    if (n_rows < 0) return fail("igmk_pop_set_rows: negative row count");
+    p->n_rows = 0; p->assign_done = false;
+    if (n_rows == 0) return 0;
+    if (!row || !col || !dist) return fail("igmk_pop_set_rows: NULL argument");
+    for (int64_t r = 0; r < n_rows; r++)
+        if (row[r] < 0 || row[r] >= p->n_bead || col[r] < 0 || col[r] >= p->n_bead)
+            return fail("igmk_pop_set_rows: bead index out of range");
+    CU(cudaSetDevice(p->device));
+    const int nw = (p->n_struct + 31) / 32;
+    CU(p->d_row.reserve(n_rows)); CU(p->d_col.reserve(n_rows)); CU(p->d_rdist.reserve(n_rows));
+    CU(p->d_bits.reserve((size_t)n_rows * nw));
+    CU(cudaMemcpyAsync(p->d_row.p, row, n_rows * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_col.p, col, n_rows * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_rdist.p, dist, n_rows * sizeof(float), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    p->n_rows = n_rows;
+    return 0;
+}
+
+extern "C" int igmk_pop_assign_launch(igmk_pop_t* p)
+{
+    if (!p) return fail("igmk_pop_assign_launch: NULL handle");
+    p->last_ms = 0.f;
+    if (p->n_rows == 0) { p->assign_done = true; return 0; }
+    CU(cudaSetDevice(p->device));
+    const int64_t grid = std::min<int64_t>((p->n_rows + 31) / 32, (int64_t)p->sm_count * 2);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_assign<<<(int)grid, 1024, 0, p->stream>>>(p->view(), p->n_rows, p->d_row.p, p->d_col.p, p->d_rdist.p, p->d_bits.p);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(p->ev1, p->stream));
+    CU(cudaEventSynchronize(p->ev1));
+    CU(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+    p->assign_done = true;
+    return 0;
+}
+
+extern "C" int igmk_pop_assign_collect(igmk_pop_t* p, uint32_t* bits)
+{
+    if (!p) return fail("igmk_pop_assign_collect: NULL handle");
+    if (!p->assign_done) return fail("igmk_pop_assign_collect: no launch to collect");
+    if (p->n_rows == 0) return 0;
+    if (!bits) return fail("igmk_pop_assign_collect: NULL argument");
+    CU(cudaSetDevice(p->device));
+    const int nw = (p->n_struct + 31) / 32;
+    CU(cudaMemcpyAsync(bits, p->d_bits.p, (size_t)p->n_rows * nw * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
+extern "C" int igmk_pop_assign(igmk_pop_t* p, int64_t n_rows, const int32_t* row, const int32_t* col,
+                               const float* dist, uint32_t* bits)
+{
+    if (int rc = igmk_pop_set_rows(p, n_rows, row, col, dist)) return rc;
+    if (int rc = igmk_pop_assign_launch(p)) return rc;
+    return igmk_pop_assign_collect(p, bits);
+}

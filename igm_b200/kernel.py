@@ -1,0 +1,152 @@
+"""The ``optimization/kernel = "b200"`` plugin: same contract as the reference's
+``igm.model.kernel.lammps.optimize(model, cfg)`` (igm/model/kernel/lammps.py:361-489).
+
+* reads ``cfg['optimization']['optimizer_options']`` (+ ``kernel_opts/b200``),
+  ``cfg['runtime']['step_no']`` for the seed (lammps.py:435, :159-165);
+* mutates ``model.particles[i].pos`` in place for EVERY particle (lammps.py:464-465);
+* returns the ``info`` dict of ``get_info_from_log`` (lammps_io.py:6-37):
+  ``final-energy``, ``pair-energy``, ``bond-energy``, ``thermo`` {Temp, E_pair, E_bond,
+  f_envelope<j>}, ``md-time``;
+* raises ``RuntimeError`` naming the model id when the kernel fails (lammps.py:450-454).
+
+``optimize_population`` is the same thing for many models in ONE launch sequence (a CTA per
+structure); ``optimize`` is the batch-of-one case.  No temp files, no subprocess.  There is no
+CPU fallback: without the CUDA library or a GPU these functions raise.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from .pack import pack_model, script_seed
+
+KERNEL_NAME = "b200"          # value of cfg['optimization']['kernel'] that selects this module
+
+_DEFAULT_KERNEL_OPTS = {
+    "device": 0,              # CUDA device ordinal
+    "bond_prefactor": 1.0,    # E = bond_prefactor * k * (r - r0)^2 (LAMMPS `harmonic` convention)
+}
+
+
+def _cfg_get(cfg, path, default=None):
+    """cfg may be an igm.core.Config (slash paths, config.py:98-113) or a plain dict."""
+    node = cfg
+    for key in path.split("/"):
+        try:
+            node = node[key]
+        except (KeyError, TypeError, IndexError):
+            return default
+    return node
+
+
+def kernel_opts(cfg):
+    opts = dict(_DEFAULT_KERNEL_OPTS)
+    opts.update(_cfg_get(cfg, "optimization/kernel_opts/" + KERNEL_NAME, {}) or {})
+    return opts
+
+
+class MStepBatch(object):
+    """Thin owner of one ``igmk_handle_t`` (one device)."""
+
+    def __init__(self, device=0):
+        self._lib = _abi.load()
+        self._h = C.c_void_p()
+        _abi.check(self._lib.igmk_create(int(device), C.byref(self._h)), "igmk_create")
+        self._packed = []
+
+    def close(self):
+        if self._h:
+            self._lib.igmk_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+        return False
+
+    def __len__(self):
+        return len(self._packed)
+
+    def clear(self):
+        _abi.check(self._lib.igmk_clear(self._h), "igmk_clear")
+        self._packed = []
+
+    def submit(self, packed):
+        slot = C.c_int32(-1)
+        _abi.check(self._lib.igmk_submit(self._h, C.byref(packed.c), C.byref(slot)),
+                   "igmk_submit (modelid: %d)" % packed.struct_id)
+        self._packed.append(packed)
+        return slot.value
+
+    def upload(self):
+        _abi.check(self._lib.igmk_upload(self._h), "igmk_upload")
+
+    def reset_coordinates(self):
+        _abi.check(self._lib.igmk_reset_coordinates(self._h), "igmk_reset_coordinates")
+
+    def run(self, protocol):
+        _abi.check(self._lib.igmk_run(self._h, C.byref(protocol)), "igmk_run")
+
+    def single_point(self, ev_scale=1.0, env_scale=1.0, bond_prefactor=1.0, f32=False):
+        fn = self._lib.igmk_single_point_f32 if f32 else self._lib.igmk_single_point
+        _abi.check(fn(self._h, float(ev_scale), float(env_scale), float(bond_prefactor)), "igmk_single_point")
+
+    def fetch(self, slot):
+        n = self._packed[slot].n_atoms
+        xyz = np.empty((n, 3), dtype=np.float32)
+        res = _abi.Result()
+        _abi.check(self._lib.igmk_fetch(self._h, slot, xyz.ctypes.data_as(_abi.c_f32p), C.byref(res)), "igmk_fetch")
+        return xyz, res
+
+    def fetch_forces(self, slot):
+        n = self._packed[slot].n_atoms
+        f = np.empty((n, 3), dtype=np.float64)
+        _abi.check(self._lib.igmk_fetch_forces(self._h, slot, f.ctypes.data_as(_abi.c_f64p)), "igmk_fetch_forces")
+        return f
+
+
+def info_from_result(res):
+    """igmk_result_t -> the dict get_info_from_log builds (lammps_io.py:6-37)."""
+    thermo = {"Temp": res.temperature, "E_pair": res.pair_energy, "E_bond": res.bond_energy}
+    for j in range(res.n_env):
+        thermo["f_envelope%d" % j] = res.env_energy[j]        # fix ids, lammps.py:296
+    return {
+        "final-energy": res.final_energy,
+        "pair-energy": res.pair_energy,
+        "bond-energy": res.bond_energy,
+        "thermo": thermo,
+        "md-time": res.md_seconds,
+    }
+
+
+def optimize_population(models, cfg, device=None):
+    """Optimise every model of ``models`` in one launch sequence; returns the list of info dicts."""
+    models = list(models)
+    if not models:
+        return []
+    kopts = kernel_opts(cfg)
+    run_opts = dict(_cfg_get(cfg, "optimization/optimizer_options"))
+    run_opts.update(kopts)                                                        # lammps.py:433 (carries `seed`)
+    step_no = (_cfg_get(cfg, "runtime/step_no", 1) or 0) + 2                     # lammps.py:435
+    protocol = _abi.make_protocol(run_opts, bond_prefactor=kopts["bond_prefactor"])
+    with MStepBatch(kopts["device"] if device is None else device) as batch:
+        slots = [batch.submit(pack_model(m, seed=script_seed(run_opts, m.id, step_no))) for m in models]
+        batch.run(protocol)
+        infos = []
+        for m, slot in zip(models, slots):
+            xyz, res = batch.fetch(slot)
+            if res.status != 0 or not np.isfinite(res.final_energy):
+                raise RuntimeError("b200 kernel produced non-finite coordinates or energy (modelid: %d)" % m.id)
+            for i, p in enumerate(m.particles):
+                p.pos = xyz[i]                                                    # lammps.py:464-465
+            infos.append(info_from_result(res))
+    return infos
+
+
+def optimize(model, cfg):
+    """Drop-in for ``igm.model.kernel.lammps.optimize`` (lammps.py:361)."""
+    return optimize_population([model], cfg)[0]

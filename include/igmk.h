@@ -124,6 +124,11 @@ int igmk_destroy(igmk_handle_t* h);
 int igmk_clear(igmk_handle_t* h);
 /* copies the structure into the batch; *slot_out indexes it in fetch calls */
 int igmk_submit(igmk_handle_t* h, const igmk_system_t* sys, int32_t* slot_out);
+/* host -> device copy of everything submitted (what writing + re-reading the .data
+ * file is in the reference, lammps.py:430-431); igmk_run does it implicitly if needed */
+int igmk_upload(igmk_handle_t* h);
+/* put the coordinates back to what was submitted (repeat a run on the same batch) */
+int igmk_reset_coordinates(igmk_handle_t* h);
 /* ONE launch sequence for everything submitted: annealing MD + CG minimisation
  * (lammps.py:285-356).  Coordinates are updated in the batch. */
 int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot);
@@ -157,6 +162,11 @@ int igmk_pop_upload(igmk_pop_t* p, const float* crd /* [n_bead][n_struct][3] */)
 int igmk_pop_download(igmk_pop_t* p, float* crd);
 /* device pointer to the coordinate slab (for callers that keep data resident) */
 int igmk_pop_coords_devptr(igmk_pop_t* p, void** dptr);
+/* use a caller-owned device slab [n_bead][n_struct][3] float32 instead (e.g. a torch
+ * tensor that NCCL all-gathers into); the caller keeps it alive */
+int igmk_pop_attach_coords(igmk_pop_t* p, void* dptr);
+/* device time (ms, CUDA events on the population's stream) of the last *_launch */
+double igmk_pop_last_kernel_ms(igmk_pop_t* p);
 
 /*
  * get_actdist (ActivationDistanceStep.py:319-459) for a batch of haploid pairs,
@@ -174,6 +184,15 @@ int igmk_pop_actdist(igmk_pop_t* p, int64_t n_pairs,
                      int64_t max_rows, int32_t* row, int32_t* col,
                      float* dist, float* prob, int64_t* n_rows_out);
 
+/* The same in three phases, so that a caller can keep the batch resident and time the
+ * kernel alone: stage the pair batch on the device, launch, copy back + expand to rows. */
+int igmk_pop_set_pairs(igmk_pop_t* p, int64_t n_pairs,
+                       const int32_t* pair_i, const int32_t* pair_j,
+                       const double* pwish, const double* plast);
+int igmk_pop_actdist_launch(igmk_pop_t* p, double contact_range);
+int igmk_pop_actdist_collect(igmk_pop_t* p, int64_t max_rows, int32_t* row, int32_t* col,
+                             float* dist, float* prob, int64_t* n_rows_out);
+
 /*
  * Contact assignment: for every actdist row r and every structure s decide
  * `np.linalg.norm(x_i - x_j) <= dist[r]` with the reference arithmetic
@@ -183,6 +202,10 @@ int igmk_pop_actdist(igmk_pop_t* p, int64_t n_pairs,
 int igmk_pop_assign(igmk_pop_t* p, int64_t n_rows,
                     const int32_t* row, const int32_t* col, const float* dist,
                     uint32_t* bits);
+int igmk_pop_set_rows(igmk_pop_t* p, int64_t n_rows,
+                      const int32_t* row, const int32_t* col, const float* dist);
+int igmk_pop_assign_launch(igmk_pop_t* p);
+int igmk_pop_assign_collect(igmk_pop_t* p, uint32_t* bits);
 
 #ifdef __cplusplus
 }

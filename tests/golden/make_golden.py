@@ -5,7 +5,7 @@ the known-answer data out of the demo output the reference ships.
 
 Run in the build container only:   python tests/golden/make_golden.py
 Outputs:
-  ff_golden.npz      6 full demo structures + the per-structure energies lmp_serial
+  ff_golden.npz      10 full demo structures + the per-structure energies lmp_serial
                      reported for them (demo/demo_sample_outputs/igm-model.hss.T)
   astep_golden.npz   a mini genome (chr1, chr2, chr21, chr22, X, Y; 100 structures) cut
                      from the demo population, a set of haploid pairs with real pwish
@@ -52,7 +52,7 @@ def main():
     summ = json.loads(hss["summary"].read())["bystructure"]
 
     # ---------------- force-field known answers -------------------------------------
-    sel = [0, 1, 5, 6, 7, 37]
+    sel = [0, 1, 5, 6, 7, 37, 80, 38, 9, 69]      # incl. the largest envelope and pair energies
     np.savez_compressed(
         os.path.join(HERE, "ff_golden.npz"),
         struct_ids=np.array(sel, dtype=np.int32),

@@ -1,0 +1,187 @@
+"""M-step protocol on the GPU: annealing MD (float32) + CG (float64) against the CPU oracle.
+Trajectories are chaotic, so agreement is statistical (north_star criterion 3) except where the
+arithmetic is deterministic: a run repeated on the GPU must reproduce itself bit for bit."""
+import numpy as np
+import pytest
+
+from igm_b200 import synth, _abi
+from igm_b200.kernel import MStepBatch, optimize, optimize_population
+from oracle import ff
+from helpers import small_system, short_protocol, demo_structure
+
+pytestmark = pytest.mark.gpu
+
+
+def _violations(ps, xyz, tol=0.05):
+    """HarmonicUpperBound.getViolationRatio (forces.py:128-136) over the structure's bonds"""
+    d = np.linalg.norm(xyz[ps.bond_i] - xyz[ps.bond_j], axis=1)
+    ratio = np.where(ps.bond_r0 > 0, np.maximum(0.0, d - ps.bond_r0) / np.maximum(ps.bond_r0, 1e-30), 0.0)
+    return int((ratio > tol).sum())
+
+
+def test_cg_only_matches_oracle_minimiser():
+    """no MD stages: the double-precision CG alone is deterministic and follows the oracle's
+    path step for step (same iteration / evaluation counts, energies to 1e-9)"""
+    g, rad, systems = small_system(seed=4, n_struct=3)
+    prot = short_protocol()
+    prot.n_stage = 0
+    with MStepBatch(0) as b:
+        slots = [b.submit(ps) for ps in systems]
+        b.run(prot)
+        for ps, slot in zip(systems, slots):
+            x_ref, r_ref = ff.optimize(ps, prot)
+            xyz, res = b.fetch(slot)
+            assert (res.cg_iters, res.cg_evals, res.cg_stop) == (r_ref.cg_iters, r_ref.cg_evals, r_ref.cg_stop)
+            assert res.final_energy == pytest.approx(r_ref.final_energy, rel=1e-8, abs=1e-10)
+            assert np.abs(xyz - x_ref).max() <= 1e-3      # float32 write-back of ~1e3-sized coordinates
+
+
+def test_full_protocol_statistics_match_oracle():
+    g, rad, systems = small_system(seed=5, n_struct=8)
+    prot = short_protocol(md=600, relax=100)
+    e_gpu, e_cpu, v_gpu, v_cpu, t_gpu = [], [], 0, 0, []
+    with MStepBatch(0) as b:
+        slots = [b.submit(ps) for ps in systems]
+        b.run(prot)
+        for ps, slot in zip(systems, slots):
+            xyz, res = b.fetch(slot)
+            assert res.status == 0 and np.isfinite(xyz).all()
+            assert res.final_energy == pytest.approx(res.pair_energy + res.bond_energy + res.env_energy[0], rel=1e-9, abs=1e-9)
+            assert np.all(xyz[len(g)] == 0.0)                          # static dummy untouched
+            assert (np.linalg.norm(xyz[:len(g)], axis=1) + rad <= 1400.0 * 1.02).all()
+            # the reported energies are those of the returned coordinates (float32 write-back)
+            ps2 = synth.pack_structure(xyz[:len(g)], rad, g, ps.bond_i[len(g) - 4:], ps.bond_j[len(g) - 4:],
+                                       ps.bond_r0[len(g) - 4:], nucleus_radius=1400.0)
+            e_gpu.append(res.final_energy); v_gpu += _violations(ps, xyz); t_gpu.append(res.temperature)
+            x_ref, r_ref = ff.optimize(ps, prot)
+            e_cpu.append(r_ref.final_energy); v_cpu += _violations(ps, x_ref)
+            del ps2
+    n_restr = sum(ps.bond_i.size for ps in systems)
+    # both implementations relax the same systems to (nearly) restraint-free states
+    assert v_gpu <= 0.01 * n_restr and v_cpu <= 0.01 * n_restr
+    assert abs(v_gpu - v_cpu) <= 0.01 * n_restr
+    assert np.median(e_gpu) <= 10.0 * np.median(e_cpu) + 1.0 and np.median(e_cpu) <= 10.0 * np.median(e_gpu) + 1.0
+    assert max(t_gpu) < 0.2                                            # annealed to T -> 0
+
+
+def test_run_is_bitwise_reproducible():
+    g, rad, systems = small_system(seed=6, n_struct=4)
+    prot = short_protocol(md=300, relax=50)
+    out = []
+    for rep in range(2):
+        with MStepBatch(0) as b:
+            slots = [b.submit(ps) for ps in systems]
+            b.run(prot)
+            out.append([b.fetch(s)[0] for s in slots])
+    for a, c in zip(*out):
+        assert np.array_equal(a.view(np.uint32), c.view(np.uint32))
+
+
+def test_reset_coordinates_repeats_the_run():
+    g, rad, systems = small_system(seed=7, n_struct=2)
+    prot = short_protocol(md=100, relax=20)
+    with MStepBatch(0) as b:
+        slots = [b.submit(ps) for ps in systems]
+        b.run(prot)
+        first = [b.fetch(s)[0] for s in slots]
+        b.reset_coordinates()
+        b.run(prot)
+        second = [b.fetch(s)[0] for s in slots]
+    for a, c in zip(first, second):
+        assert np.array_equal(a, c)
+
+
+def test_thermostat_holds_the_target_temperature():
+    """skip_minimize + a flat T=50 stage: the thermo temperature at the end is the target
+    (temp/rescale window 0.1, fraction 1)"""
+    g, rad, systems = small_system(seed=8)
+    prot = short_protocol(md=300, relax=0)
+    prot.n_stage = 1
+    prot.tstart[0] = 50.0; prot.tstop[0] = 50.0
+    prot.skip_minimize = 1
+    with MStepBatch(0) as b:
+        slot = b.submit(systems[0])
+        b.run(prot)
+        _, res = b.fetch(slot)
+    n = systems[0].n_atoms
+    want = 50.0 * (3.0 * (n - 1) - 3.0) / (3.0 * n - 3.0)    # thermo `temp` is over group all
+    assert res.temperature == pytest.approx(want, abs=0.11)
+
+
+def test_demo_size_structure_runs(ff_golden):
+    """a 3008-bead structure with ~7k bonds through a shortened protocol"""
+    ps = demo_structure(ff_golden, 0, n_extra_bonds=0, with_damid=False, with_centroid=False)
+    prot = short_protocol(md=200, relax=50)
+    with MStepBatch(0) as b:
+        slot = b.submit(ps)
+        b.run(prot)
+        xyz, res = b.fetch(slot)
+    assert res.status == 0 and np.isfinite(res.final_energy)
+    assert res.final_energy < 168097.0                      # lower than where it started
+    assert res.n_rebuilds > 1
+
+
+class _P(object):
+    def __init__(self, pos, r, ptype):
+        self.pos = np.array(pos, dtype=np.float32); self.r = np.float32(r); self.ptype = ptype
+
+
+class _F(object):
+    def __init__(self, ftype, **kw):
+        self.ftype = ftype
+        self.__dict__.update(kw)
+
+
+class _Model(object):
+    def __init__(self, uid):
+        self.id = uid; self.particles = []; self.forces = []
+
+
+def _toy_model(uid, seed):
+    """what ModelingStep.task builds (ModelingStep.py:184-264), with duck-typed igm classes"""
+    g, rad, systems = small_system(seed=seed)
+    ps = systems[0]
+    m = _Model(uid)
+    n = len(g)
+    for i in range(n):
+        m.particles.append(_P(ps.xyz[i], rad[i], 0))
+    m.forces.append(_F(0, k=1.0))                                              # Steric
+    m.particles.append(_P([0, 0, 0], 0.0, 1))                                  # Envelope's dummy
+    m.forces.append(_F(3, shape="ellipsoid", semiaxes=np.array([1400.0] * 3), particle_ids=list(range(n)), k=1.0))
+    for i, j, d, k in zip(ps.bond_i, ps.bond_j, ps.bond_r0, ps.bond_k):
+        m.forces.append(_F(1, i=int(i), j=int(j), d=float(d), k=float(k)))
+    return m, ps
+
+
+def test_optimize_plugin_contract():
+    """igm.model.kernel.lammps.optimize's contract (lammps.py:361-489): in-place positions, info keys"""
+    m, ps = _toy_model(3, seed=9)
+    opts = synth.demo_protocol_options()
+    opts["custom_annealing_protocol"]["mdsteps"] = [100, 100, 100, 100]
+    opts["custom_annealing_protocol"]["relax"]["mdsteps"] = 20
+    cfg = {"optimization": {"kernel": "b200", "optimizer_options": opts, "kernel_opts": {"b200": {"seed": 6535}}},
+           "runtime": {"step_no": 3}}
+    before = np.array([p.pos for p in m.particles])
+    info = optimize(m, cfg)
+    after = np.array([p.pos for p in m.particles])
+    assert set(info) == {"final-energy", "pair-energy", "bond-energy", "thermo", "md-time"}
+    assert set(info["thermo"]) == {"Temp", "E_pair", "E_bond", "f_envelope0"}
+    assert after.dtype == np.float32 and after.shape == before.shape and not np.array_equal(after, before)
+    assert np.all(after[-1] == 0.0)
+    assert info["final-energy"] == pytest.approx(info["pair-energy"] + info["bond-energy"] + info["thermo"]["f_envelope0"], abs=1e-6)
+    assert info["md-time"] > 0
+    # a population call gives the same answer for the same model / seed as the single call
+    m2, _ = _toy_model(3, seed=9)
+    m3, _ = _toy_model(4, seed=10)
+    infos = optimize_population([m2, m3], cfg)
+    assert np.array_equal(np.array([p.pos for p in m2.particles]), after)
+    assert infos[0]["final-energy"] == info["final-energy"]
+
+
+def test_optimize_raises_runtime_error_with_model_id():
+    m, _ = _toy_model(12, seed=11)
+    m.forces.append(_F(1, i=0, j=10 ** 6, d=1.0, k=1.0))
+    cfg = {"optimization": {"kernel": "b200", "optimizer_options": synth.demo_protocol_options(), "kernel_opts": {}},
+           "runtime": {"step_no": 0}}
+    with pytest.raises(RuntimeError, match="modelid: 12"):
+        optimize(m, cfg)
