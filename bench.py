@@ -1,0 +1,407 @@
+#!/usr/bin/env python
+"""Benchmark of the A/M hot path on B200 (contract: see DESIGN.md "Measurement").
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+Workload (BASELINE.json configs[1]): 2 Mb diploid genome (3008 beads + the envelope's dummy),
+1000 structures PER GPU (weak scaling), spherical envelope, Hi-C restraints assigned at one
+sigma, the demo's full annealing protocol (4 x [relax 500 + 5k/15k/15k/10k MD steps] + CG).
+A "step" = one M-step over the rank's structures.  `value` = structures/s with everything
+resident in HBM; `e2e` = the same through the C ABI with host buffers (submit -> upload -> run
+-> fetch).  The A-step (activation distances + assignment over all structures x pairs) is
+timed in the same run and reported under "astep".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from igm_b200 import _abi, synth          # noqa: E402
+
+NUCLEUS_R = 5500.0
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # non-tensor FP32 FMA peak at max clock (derived)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--structures", type=int, default=1000, help="structures per GPU")
+    ap.add_argument("--pairs", type=int, default=614140,
+                    help="haploid pairs kept by the sigma threshold (default: what sigma=0.01 keeps of the demo matrix)")
+    ap.add_argument("--md-scale", type=float, default=1.0, help="scale every mdsteps entry (diagnostics only)")
+    ap.add_argument("--relax-md-scale", type=float, default=None, help="mdsteps scale of the untimed RelaxInit pass (profiling aid)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="structures in the CPU baseline sample (0: one per core)")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        super(ClockSampler, self).__init__(daemon=True)
+        self.device, self.rows, self._halt = device, [], threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.check_output(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                               "--format=csv,noheader,nounits"], timeout=10).decode()
+                self.rows.append([v.strip() for v in out.strip().split(",")])
+            except Exception:
+                pass
+            self._halt.wait(0.5)
+
+    def finish(self):
+        self._halt.set()
+        self.join(timeout=15)
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def protocol(md_scale):
+    opts = synth.demo_protocol_options()
+    if md_scale != 1.0:
+        cap = opts["custom_annealing_protocol"]
+        cap["mdsteps"] = [max(1, int(v * md_scale)) for v in cap["mdsteps"]]
+        cap["relax"]["mdsteps"] = max(1, int(cap["relax"]["mdsteps"] * md_scale))
+    return opts, _abi.make_protocol(opts)
+
+
+def md_force_evals(prot):
+    """force evaluations of the MD launch per structure: every run = setup + nsteps"""
+    n = 0
+    for k in range(prot.n_stage):
+        if prot.relax_mdsteps > 0:
+            n += prot.relax_mdsteps + 1
+        n += prot.mdsteps[k] + 1
+    return n
+
+
+def flops_per_eval(systems, coords, sample=6):
+    """F_eval = 8 P_cand + 21 P_act + 20 B + 9 N_env + 36 N, with the pair counts
+    measured on the optimised coordinates of a few structures (full neighbour rows as the kernel
+    walks them: cutoff ri+rj+skin, skin = max radius)."""
+    from scipy.spatial import cKDTree
+    tot = []
+    for ps, xyz in list(zip(systems, coords))[:sample]:
+        n = ps.n_atoms - 1
+        r = float(ps.radius[0])
+        t = cKDTree(xyz[:n].astype(np.float64))
+        p_cand = t.count_neighbors(t, 3.0 * r) - n          # ordered pairs within cutoff + skin (each visited by its owner)
+        p_act = t.count_neighbors(t, 2.0 * r) - n
+        b = 2 * ps.bond_i.size                              # every bond is evaluated from both ends
+        tot.append(8.0 * p_cand + 21.0 * p_act + 20.0 * b + 9.0 * n + 36.0 * n)
+    return float(np.mean(tot))
+
+
+# --------------------------------------------------------------------------------------
+def build_workload(args, rank, world, device, log):
+    """-> dict(genome, radii, systems (local PackedSystems), crd_local, pairs, rows, timings of the A-step)"""
+    import torch
+    import torch.distributed as dist
+    from igm_b200.kernel import MStepBatch
+    from igm_b200.astep import Population, unpack_bits
+
+    S = args.structures
+    g = synth.genome_2mb()
+    n = len(g)
+    rad = synth.bead_radii(n, NUCLEUS_R, 0.4)
+    opts, prot = protocol(args.md_scale)
+    t0 = time.time()
+    start = np.empty((n, S, 3), dtype=np.float32)
+    for s in range(S):
+        start[:, s, :] = synth.territories(g, NUCLEUS_R, np.random.default_rng(1234 + rank * S + s))
+    # RelaxInit-equivalent pass (igm/steps/RelaxInit.py:86-177: polymer + steric + envelope only)
+    relax_sys = [synth.pack_structure(start[:, s, :], rad, g, nucleus_radius=NUCLEUS_R, seed=1 + rank * S + s,
+                                      struct_id=rank * S + s) for s in range(S)]
+    crd = np.empty((n, S, 3), dtype=np.float32)
+    relax_prot = prot if args.relax_md_scale is None else protocol(args.relax_md_scale)[1]
+    with MStepBatch(device) as b:
+        slots = [b.submit(ps) for ps in relax_sys]
+        b.run(relax_prot)
+        for s, slot in enumerate(slots):
+            crd[:, s, :] = b.fetch(slot)[0][:n]
+        relax_ms = sum(b.last_timings()[:2])
+    log("setup: territories + RelaxInit pass of %d structures: %.1f s (kernels %.0f ms)" % (S, time.time() - t0, relax_ms))
+
+    # ---- A-step: all-gather the slab on the struct axis, shard the pairs ----
+    local = torch.from_numpy(crd).to("cuda:%d" % device)
+    if world > 1:
+        parts = [torch.empty_like(local) for _ in range(world)]
+        dist.all_gather(parts, local)
+        slab = torch.cat(parts, dim=1).contiguous()
+    else:
+        slab = local
+    S_tot = S * world
+    sl = slice(rank, None, world)                   # interleaved pair shard: equal intra/inter mix per rank
+    astep = {}
+    with Population(S_tot, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop:
+        pop.attach(slab)
+        # Synthetic Hi-C matrix that is geometrically consistent with the population (a random matrix
+        # collapses the genome into a globule): the contact frequency of every haploid pair in the relaxed
+        # population is the "experiment"; the iteration wishes 10 % more contacts than are present
+        # (pwish = 1.1 f) and the previous iteration is taken to have imposed f (plast).
+        iu, ju = np.triu_indices(g.n_hap, 1)
+        freq = pop.contact_freq(iu.astype(np.int32), ju.astype(np.int32), 2.0)
+        pw_all = np.minimum(np.float32(1.0), np.float32(1.1) * freq).astype(np.float32)
+        sigma = float(np.partition(pw_all, pw_all.size - args.pairs)[pw_all.size - args.pairs]) if args.pairs < pw_all.size else 0.0
+        keep = pw_all >= np.float32(sigma)
+        log("synthetic Hi-C matrix: pairs with pwish >= sigma: " + ", ".join(
+            "%g: %d" % (sg, int((pw_all >= np.float32(sg)).sum())) for sg in (0.05, 0.02, 0.01, 0.005, 0.003, 0.002, 0.001)))
+        pi, pj = iu[keep].astype(np.int32), ju[keep].astype(np.int32)
+        pw = pw_all[keep].astype(np.float64)
+        pl = np.round(freq[keep].astype(np.float64), 4).astype(np.float32).astype(np.float64)
+        kt, et = [], []
+        rows = None
+        for rep in range(3):
+            torch.cuda.synchronize(device)
+            t1 = time.perf_counter()
+            rows = pop.actdist(pi[sl], pj[sl], pw[sl], pl[sl], 2.0)
+            et.append(time.perf_counter() - t1)
+            kt.append(pop.last_kernel_ms())
+        astep["actdist_kernel_ms"] = min(kt)
+        astep["actdist_e2e_ms"] = min(et) * 1e3
+        astep["pairs_local"] = int(pi[sl].size)
+        n_copies = np.diff(g.copy_off)
+        astep["actdist_bytes"] = float(12.0 * S_tot * (n_copies[pi[sl]] + n_copies[pj[sl]]).sum() + 32.0 * pi[sl].size)
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, rows)
+        # restore the global pair order: rank r holds pairs r, r+world, ... -> merge by pair ordinal
+        rows = tuple(np.concatenate([gg[k] for gg in gathered]) for k in range(4))
+    row, col, dst, prb = rows
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop:
+        pop.attach(local)
+        kt, et = [], []
+        for rep in range(3):
+            t1 = time.perf_counter()
+            bits = pop.assign(row, col, dst)
+            et.append(time.perf_counter() - t1)
+            kt.append(pop.last_kernel_ms())
+        astep["assign_kernel_ms"] = min(kt)
+        astep["assign_e2e_ms"] = min(et) * 1e3
+        astep["rows"] = int(row.size)
+        astep["assign_bytes"] = float(row.size) * (24.0 * S + 12.0 + 4.0 * ((S + 31) // 32))
+    # bits -> per-structure Hi-C bonds (HarmonicUpperBound(i, j, contact_range*(ri+rj), k), inter_hic.py:55-62)
+    t1 = time.time()
+    r0_all = (2.0 * (rad[row] + rad[col])).astype(np.float64)
+    systems = []
+    nb = []
+    for s in range(S):
+        m = ((bits[:, s >> 5] >> np.uint32(s & 31)) & np.uint32(1)).astype(bool)
+        systems.append(synth.pack_structure(crd[:, s, :], rad, g, row[m], col[m], r0_all[m], nucleus_radius=NUCLEUS_R,
+                                            seed=7 + rank * S + s, struct_id=rank * S + s))
+        nb.append(int(m.sum()))
+    log("A-step: %d pairs -> %d rows; actdist %.2f ms, assign %.2f ms (kernels); %.0f Hi-C bonds/structure; "
+        "host bond build %.1f s" % (pi.size, row.size, astep["actdist_kernel_ms"], astep["assign_kernel_ms"],
+                                    np.mean(nb), time.time() - t1))
+    cnts = np.sort(np.bincount(np.concatenate([systems[0].bond_i, systems[0].bond_j]), minlength=3072))[::-1]
+    cnts = np.concatenate([cnts, np.zeros((-cnts.size) % 32, dtype=cnts.dtype)]).reshape(-1, 32)
+    log("bond items of structure 0: %d real, %d after sliced-ELL padding, longest row %d"
+        % (cnts.sum(), 32 * cnts.max(axis=1).sum(), cnts.max()))
+    astep["pairs_total"] = int(pi.size)
+    astep["sigma"] = sigma
+    astep["hic_bonds_per_structure"] = float(np.mean(nb))
+    return {"genome": g, "radii": rad, "systems": systems, "crd": crd, "astep": astep, "prot": prot, "opts": opts}
+
+
+def cpu_mstep_baseline(systems, prot, n_sample, threads):
+    """the oracle's C port of the whole protocol, one structure per host thread (ctypes drops the GIL)"""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import ff
+    ff.lib()
+    sample = systems[:n_sample]
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        res = list(ex.map(lambda ps: ff.optimize(ps, prot)[1].final_energy, sample))
+    dt = time.perf_counter() - t0
+    return len(sample) / dt, dt, res
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU restatement of the reference path (lmp_serial itself is not
+    installable here) on all host cores, same config / metric."""
+    if rank != 0:
+        return
+    g = synth.genome_2mb()
+    n = len(g)
+    rad = synth.bead_radii(n, NUCLEUS_R, 0.4)
+    opts, prot = protocol(args.md_scale)
+    cores = os.cpu_count() or 1
+    n_sample = args.cpu_sample or cores
+    systems = []
+    for s in range(n_sample):
+        xyz = synth.territories(g, NUCLEUS_R, np.random.default_rng(1234 + s))
+        systems.append(synth.pack_structure(xyz, rad, g, nucleus_radius=NUCLEUS_R, seed=1 + s, struct_id=s))
+    times = []
+    for it in range(args.warmup + args.steps):
+        v, dt, _ = cpu_mstep_baseline(systems, prot, n_sample, cores)
+        if it >= args.warmup:
+            times.append(dt)
+    ms = 1e3 * float(np.mean(times))
+    value = n_sample / (ms / 1e3)
+    sample = "%d structures per step (one per host thread), polymer+steric+envelope restraints, full protocol" % n_sample
+    print(json.dumps({
+        "impl": "reference", "metric": "optimised structures/sec at 2Mb diploid", "value": value, "unit": "structures/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "2Mb diploid (3008 beads), CPU restatement of the lammpgen script (oracle/ff_oracle.c); "
+                               "lmp_serial itself is not installable offline", "structures_per_step": n_sample},
+        "cpu_baseline": {"value": value, "unit": "structures/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "structures/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    import torch
+    import torch.distributed as dist
+    from igm_b200.kernel import MStepBatch
+
+    def log(msg):
+        if rank == 0:
+            print("[bench] " + msg, file=sys.stderr, flush=True)
+
+    device = local_rank
+    torch.cuda.set_device(device)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % device))
+    wl = build_workload(args, rank, world, device, log)
+    systems, prot = wl["systems"], wl["prot"]
+    S = len(systems)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(device)
+
+    # ---- value: batch resident in HBM, K steps inside ONE timed region --------------------
+    batch = MStepBatch(device)
+    for ps in systems:
+        batch.submit(ps)
+    batch.upload()
+    md_ms, cg_ms = [], []
+    for _ in range(args.warmup):
+        batch.reset_coordinates()
+        batch.run(prot)
+    sampler = ClockSampler(device)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        batch.reset_coordinates()
+        batch.run(prot)
+        t = batch.last_timings()
+        md_ms.append(t[0]); cg_ms.append(t[1])
+    e1.record()
+    barrier()
+    clocks = sampler.finish()
+    ms_step = e0.elapsed_time(e1) / args.steps
+    coords = [batch.fetch(k)[0] for k in range(min(S, 6))]
+    cg_evals = float(np.mean([batch.fetch(k)[1].cg_evals for k in range(S)]))
+    h2d = batch.last_timings()[2]
+    # ---- e2e: host buffers through the C ABI every step -------------------------------------
+    d2h = sum(ps.n_atoms for ps in systems) * 16 + S * 136
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        batch.clear()
+        for ps in systems:
+            batch.submit(ps)
+        batch.run(prot)
+        out = [batch.fetch(k) for k in range(S)]
+    torch.cuda.synchronize(device)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    del out
+    batch.close()
+
+    tt = torch.tensor([ms_step, e2e_ms, wl["astep"]["actdist_kernel_ms"], wl["astep"]["actdist_e2e_ms"],
+                       wl["astep"]["assign_kernel_ms"], wl["astep"]["assign_e2e_ms"]], dtype=torch.float64, device="cuda:%d" % device)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_step, e2e_ms, ad_k, ad_e, as_k, as_e = [float(v) for v in tt.tolist()]
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm = peaks.get("hbm_gbs", 6650.0)
+        which = "measured" if "hbm_gbs" in peaks else "fallback"
+        feval = flops_per_eval(systems, coords)
+        evals = md_force_evals(prot)
+        md_t = float(np.mean(md_ms)) * 1e-3
+        md_tflops = feval * evals * S / md_t / 1e12
+        a = wl["astep"]
+        ad_gbs = a["actdist_bytes"] / (a["actdist_kernel_ms"] * 1e-3) / 1e9
+        as_gbs = a["assign_bytes"] / (a["assign_kernel_ms"] * 1e-3) / 1e9
+        line = {
+            "metric": "optimised structures/sec at 2Mb diploid", "value": S * world / (ms_step * 1e-3), "unit": "structures/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32 (MD) + f64 (CG)", "data": "synthetic",
+            "config": {"workload": "configs[1]: 2 Mb diploid Hi-C, %d structures per GPU, spherical envelope, full demo annealing "
+                                   "protocol + CG; Hi-C matrix = contact frequencies of the relaxed synthetic population, sigma=%.4g "
+                                   "keeps %d haploid pairs (the demo matrix keeps 614140 at its last sigma, 0.01)"
+                                   % (S, a["sigma"], a["pairs_total"]),
+                       "beads": 3008, "structures_per_gpu": S, "hic_bonds_per_structure": a["hic_bonds_per_structure"],
+                       "md_force_evals": evals, "cg_evals_mean": cg_evals, "md_scale": args.md_scale,
+                       "l2_policy": "working set per step (bond lists + neighbour tables, >400 MB) exceeds L2; A-step slab is "
+                                    "L2 resident at S=1000 (36 MB), noted in roofline_astep"},
+            "e2e": {"value": S * world / (e2e_ms * 1e-3), "unit": "structures/s", "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": 2 * args.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "fp32", "kernel": "k_md", "achieved": md_tflops, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
+                         "frac": md_tflops / FP32_PEAK_TFLOPS, "traffic": None, "flops_per_force_eval": feval,
+                         "kernel_ms": md_t * 1e3, "cg_kernel_ms": float(np.mean(cg_ms)),
+                         "peak_source": "derived: 148 SM x 128 lanes x 2 x 1.965 GHz (non-tensor FP32; not in MEASURED_PEAKS.json)"},
+            "astep": {"metric": "A-step haploid pairs/sec", "pairs": a["pairs_total"], "rows": a["rows"],
+                      "structures": S * world,
+                      "value": a["pairs_total"] / (ad_k * 1e-3), "e2e": a["pairs_total"] / (ad_e * 1e-3), "unit": "pairs/s",
+                      "actdist_kernel_ms": ad_k, "actdist_e2e_ms": ad_e, "assign_kernel_ms": as_k, "assign_e2e_ms": as_e,
+                      "assign_rows_x_structures_per_s": a["rows"] * float(S) / (as_k * 1e-3)},
+            "roofline_astep": {"bound": "hbm", "kernel": "k_actdist", "achieved": ad_gbs, "peak": hbm, "unit": "GB/s",
+                               "frac": ad_gbs / hbm, "traffic": None, "peak_source": which + " copy bandwidth",
+                               "assign_achieved": as_gbs, "assign_frac": as_gbs / hbm},
+        }
+        if not args.no_cpu_baseline and world == 1:
+            cores = os.cpu_count() or 1
+            n_sample = args.cpu_sample or cores
+            v, dt, _ = cpu_mstep_baseline(systems, prot, n_sample, cores)
+            line["cpu_baseline"] = {"value": v, "unit": "structures/s", "cores": cores, "kind": "port",
+                                    "sample": "%d of the %d structures (same restraints, full protocol), one per host "
+                                              "thread, %.1f s" % (n_sample, S, dt)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -185,6 +185,7 @@ _SIGNATURES = {
     "igmk_single_point_f32": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double]),
     "igmk_fetch": (C.c_int, [_vp, C.c_int32, c_f32p, C.POINTER(Result)]),
     "igmk_fetch_forces": (C.c_int, [_vp, C.c_int32, c_f64p]),
+    "igmk_last_timings": (C.c_int, [_vp, c_f64p, c_f64p, c_i64p]),
     "igmk_pop_create": (C.c_int, [C.c_int, C.c_int32, C.c_int32, C.c_int32, c_f32p, c_i32p, c_i32p, c_i32p,
                                   C.POINTER(_vp)]),
     "igmk_pop_destroy": (C.c_int, [_vp]),
@@ -199,6 +200,7 @@ _SIGNATURES = {
     "igmk_pop_set_pairs": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f64p, c_f64p]),
     "igmk_pop_actdist_launch": (C.c_int, [_vp, C.c_double]),
     "igmk_pop_actdist_collect": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p, c_f32p, c_i64p]),
+    "igmk_pop_contact_freq": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, C.c_double, c_f32p]),
     "igmk_pop_set_rows": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p]),
     "igmk_pop_assign_launch": (C.c_int, [_vp]),
     "igmk_pop_assign_collect": (C.c_int, [_vp, c_u32p]),

@@ -123,6 +123,19 @@ class Population(object):
         self.actdist_launch(contact_range)
         return self.actdist_collect()
 
+    def contact_freq(self, pair_i, pair_j, contact_range=2.0):
+        """-> float32 [n_pairs]: fraction of (copy pair, structure) combinations in contact, the
+        ``pnow`` of get_actdist (ActivationDistanceStep.py:419-422)."""
+        pi = np.ascontiguousarray(pair_i, dtype=np.int32)
+        pj = np.ascontiguousarray(pair_j, dtype=np.int32)
+        if pi.size != pj.size:
+            raise ValueError("pair arrays differ in length")
+        out = np.empty(pi.size, dtype=np.float32)
+        _abi.check(self._lib.igmk_pop_contact_freq(self._p, pi.size, pi.ctypes.data_as(_abi.c_i32p),
+                                                   pj.ctypes.data_as(_abi.c_i32p), float(contact_range),
+                                                   out.ctypes.data_as(_abi.c_f32p)), "igmk_pop_contact_freq")
+        return out
+
     # ---- contact assignment ---------------------------------------------------------------
     def set_rows(self, row, col, dist):
         r = np.ascontiguousarray(row, dtype=np.int32)

@@ -155,6 +155,41 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
     }
 }
 
+// Contact frequency of haploid pairs in the population: the `pnow` of get_actdist
+// (ActivationDistanceStep.py:419-422) = count(d_sq <= rcutsq) / (n_comb * n_struct), as float32.
+// One warp per pair.  Used to derive geometrically consistent synthetic Hi-C matrices and as the
+// population-side half of a Hi-C evaluation.
+__global__ void __launch_bounds__(256)
+k_contact_freq(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const int32_t* __restrict__ pair_j,
+               float contact_range_f32, float* __restrict__ freq)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int S = P.n_struct;
+    for (int64_t pidx = (int64_t)blockIdx.x * 8 + warp; pidx < n_pairs; pidx += (int64_t)gridDim.x * 8) {
+        const int hi = pair_i[pidx], hj = pair_j[pidx];
+        const int io = P.copy_off[hi], jo = P.copy_off[hj];
+        const int ni = P.copy_off[hi + 1] - io, nj = P.copy_off[hj + 1] - jo;
+        const bool intra = P.chrom[hi] == P.chrom[hj];
+        const int ncomb = intra ? min(ni, nj) : ni * nj;
+        const float rc = __fmul_rn(contact_range_f32, __fadd_rn(P.radii[P.copy_beads[io]], P.radii[P.copy_beads[jo]]));
+        const float rcutsq = __fmul_rn(rc, rc);
+        int cnt = 0;
+        for (int c = 0; c < ncomb; c++) {
+            const float* xi = P.crd + (size_t)P.copy_beads[io + (intra ? c : c / nj)] * S * 3;
+            const float* xj = P.crd + (size_t)P.copy_beads[jo + (intra ? c : c % nj)] * S * 3;
+            for (int s = lane; s < S; s += 32) {
+                const float dx = __fsub_rn(xi[3 * s], xj[3 * s]);
+                const float dy = __fsub_rn(xi[3 * s + 1], xj[3 * s + 1]);
+                const float dz = __fsub_rn(xi[3 * s + 2], xj[3 * s + 2]);
+                cnt += (__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)) <= rcutsq);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0) freq[pidx] = hi == hj ? 1.0f : (float)((double)cnt / (double)(ncomb * S));
+    }
+}
+
 // Contact assignment.  One warp per actdist row, lanes over structures; 32 rows per CTA.
 // bits[r][w] bit l  <=>  structure 32*w+l gets a bond for row r.
 __global__ void __launch_bounds__(1024)

@@ -3,6 +3,7 @@
 // launches the kernels and copies results back.  No exceptions cross the ABI.
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <cmath>
 #include <string>
 #include <vector>
@@ -13,6 +14,7 @@
 
 #include "../../include/igmk.h"
 #include "mstep.cuh"
+#include "md2.cuh"
 #include "astep.cuh"
 
 using namespace igmk;
@@ -58,9 +60,18 @@ struct igmk_handle {
     std::vector<int64_t>  struct_id;
     int max_atoms = 0;
     int nl_width = NL_WIDTH0;
+    // thread-per-atom MD layout (md2.cuh), built at upload time
+    int md2_K = 0, md2_nlw = MD2_NLW0;
+    float skin_factor = 0.7f;   // measured optimum on the 2 Mb workload (profiles/)
+    std::vector<Md2Desc> md2_desc;
+    std::vector<uint16_t> md2_perm;
+    std::vector<int32_t>  md2_ell_off;
+    std::vector<uint32_t> md2_ell_items;
+    Md2Desc* d_md2_desc = nullptr; uint16_t* d_md2_perm = nullptr; int32_t* d_md2_ell_off = nullptr;
+    uint32_t* d_md2_ell_items = nullptr; uint16_t* d_md2_nl = nullptr;
     bool dirty = true;
     // device
-    StructDesc* d_desc = nullptr; float4* d_xyzr = nullptr; uint8_t* d_kind = nullptr; uint32_t* d_envmask = nullptr;
+    StructDesc* d_desc = nullptr; float4* d_xyzr = nullptr; float4* d_xyzr0 = nullptr; uint8_t* d_kind = nullptr; uint32_t* d_envmask = nullptr;
     int32_t* d_bond_ptr = nullptr; uint32_t* d_bond_items = nullptr; float2* d_btype_f = nullptr; double2* d_btype_d = nullptr;
     uint16_t* d_nl = nullptr; uint16_t* d_nl_cnt = nullptr; double* d_xd = nullptr; double* d_fd = nullptr; double* d_work = nullptr;
     igmk_result_t* d_res = nullptr; int32_t* d_flags = nullptr;
@@ -69,13 +80,17 @@ struct igmk_handle {
     std::vector<int32_t> flags;
     std::vector<double> forces;
     bool have_forces = false;
+    double md_ms = 0.0, cg_ms = 0.0;   // device time of the last igmk_run's two launches
+    size_t h2d_bytes = 0;              // bytes the last upload() moved to the device
 
     void free_device()
     {
-        cudaFree(d_desc); cudaFree(d_xyzr); cudaFree(d_kind); cudaFree(d_envmask); cudaFree(d_bond_ptr);
+        cudaFree(d_desc); cudaFree(d_xyzr); cudaFree(d_xyzr0); cudaFree(d_kind); cudaFree(d_envmask); cudaFree(d_bond_ptr);
         cudaFree(d_bond_items); cudaFree(d_btype_f); cudaFree(d_btype_d); cudaFree(d_nl); cudaFree(d_nl_cnt);
         cudaFree(d_xd); cudaFree(d_fd); cudaFree(d_work); cudaFree(d_res); cudaFree(d_flags);
-        d_desc = nullptr; d_xyzr = nullptr; d_kind = nullptr; d_envmask = nullptr; d_bond_ptr = nullptr;
+        cudaFree(d_md2_desc); cudaFree(d_md2_perm); cudaFree(d_md2_ell_off); cudaFree(d_md2_ell_items); cudaFree(d_md2_nl);
+        d_md2_desc = nullptr; d_md2_perm = nullptr; d_md2_ell_off = nullptr; d_md2_ell_items = nullptr; d_md2_nl = nullptr;
+        d_desc = nullptr; d_xyzr = nullptr; d_xyzr0 = nullptr; d_kind = nullptr; d_envmask = nullptr; d_bond_ptr = nullptr;
         d_bond_items = nullptr; d_btype_f = nullptr; d_btype_d = nullptr; d_nl = nullptr; d_nl_cnt = nullptr;
         d_xd = nullptr; d_fd = nullptr; d_work = nullptr; d_res = nullptr; d_flags = nullptr;
     }
@@ -102,6 +117,15 @@ extern "C" int igmk_create(int device, igmk_handle_t** out)
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     h->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if (const char* e = getenv("IGMK_NL_WIDTH")) {          // initial neighbour-table width (tuning / profiling aid)
+        const int w = atoi(e);
+        if (w >= 8 && w <= 65536) { h->md2_nlw = w; h->nl_width = w; }
+    }
+    if (const char* e = getenv("IGMK_SKIN")) {              // neighbour skin in units of the bead radius (results do not depend on it)
+        const float f = (float)atof(e);
+        if (f >= 0.05f && f <= 4.0f) h->skin_factor = f;
+    }
+
     *out = h;
     return 0;
 }
@@ -191,6 +215,11 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
     for (int i = 0; i < n; i++) cnt[i + 1] += cnt[i];
     std::vector<uint32_t> items((size_t)cnt[n]);
     std::vector<int32_t> cur(cnt.begin(), cnt.end() - 1);
+    // provisional type ids in first-seen order, then renumbered by use count so that the MD kernel
+    // can keep the two most frequent types in registers
+    std::vector<int32_t> btype_of((size_t)s->n_bonds);
+    std::vector<std::tuple<double, double, int>> tkeys;
+    std::vector<int64_t> tuse;
     for (int b = 0; b < s->n_bonds; b++) {
         auto key = std::make_tuple(s->bond_r0[b], s->bond_k[b], (int)s->bond_style[b]);
         auto it = types.find(key);
@@ -199,13 +228,30 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
             t = (int)types.size();
             if (t > 65535) return fail("igmk_submit: more than 65536 distinct bond types in one structure");
             types[key] = t;
-            const double ks = s->bond_style[b] == IGMK_BOND_LOWER ? -s->bond_k[b] : s->bond_k[b];
-            h->btype_f.push_back(make_float2((float)s->bond_r0[b], (float)ks));
-            h->btype_d.push_back(make_double2(s->bond_r0[b], ks));
+            tkeys.push_back(key); tuse.push_back(0);
         } else t = it->second;
+        tuse[t]++;
+        btype_of[b] = t;
+    }
+    std::vector<int32_t> torder(tkeys.size()), tnew(tkeys.size());
+    for (size_t t = 0; t < torder.size(); t++) torder[t] = (int32_t)t;
+    std::stable_sort(torder.begin(), torder.end(), [&](int32_t a, int32_t b) { return tuse[a] > tuse[b]; });
+    for (size_t r = 0; r < torder.size(); r++) {
+        tnew[torder[r]] = (int32_t)r;
+        const double r0 = std::get<0>(tkeys[torder[r]]), k = std::get<1>(tkeys[torder[r]]);
+        const double ks = std::get<2>(tkeys[torder[r]]) == IGMK_BOND_LOWER ? -k : k;
+        h->btype_f.push_back(make_float2((float)r0, (float)ks));
+        h->btype_d.push_back(make_double2(r0, ks));
+    }
+    for (size_t r = torder.size(); r < 2; r++) {           // the kernel reads entries 0 and 1 unconditionally
+        h->btype_f.push_back(make_float2(0.f, 0.f));
+        h->btype_d.push_back(make_double2(0.0, 0.0));
+    }
+    for (int b = 0; b < s->n_bonds; b++) {
+        const uint32_t t = (uint32_t)tnew[btype_of[b]];
         const int i = s->bond_i[b], j = s->bond_j[b];
-        items[cur[i]++] = (uint32_t)j | ((uint32_t)t << 16);
-        items[cur[j]++] = (uint32_t)i | ((uint32_t)t << 16);
+        items[cur[i]++] = (uint32_t)j | (t << 16);
+        items[cur[j]++] = (uint32_t)i | (t << 16);
     }
     h->bond_ptr.insert(h->bond_ptr.end(), cnt.begin(), cnt.end());
     h->bond_items.insert(h->bond_items.end(), items.begin(), items.end());
@@ -217,6 +263,76 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
     return 0;
 }
 
+// slots per thread the MD kernel is instantiated for
+static int md2_pick_K(int max_atoms)
+{
+    const int need = (max_atoms + MD2_T - 1) / MD2_T;
+    const int avail[] = {1, 2, 3, 4, 6, 8};
+    for (int k : avail) if (k >= need) return k;
+    return 0;
+}
+
+// Atom ordering + sliced-ELL bond items for the thread-per-atom MD kernel: atoms sorted by bond
+// count, 32 at a time into warp-slots laid out boustrophedon over the warps so that every warp
+// gets a similar amount of bond work and the atoms of one warp-slot have similar row lengths.
+static void md2_build(igmk_handle* h)
+{
+    const int K = h->md2_K, np = K * MD2_T, G = K * 32;
+    const size_t ns = h->desc.size();
+    h->md2_desc.assign(ns, Md2Desc());
+    h->md2_perm.assign(ns * (size_t)np, MD2_NONE);
+    h->md2_ell_off.assign(ns * (size_t)(G + 1), 0);
+    h->md2_ell_items.clear();
+    std::vector<int> order, pos;
+    for (size_t s = 0; s < ns; s++) {
+        const StructDesc& d = h->desc[s];
+        const int n = d.n_atoms;
+        const int32_t* bp = h->bond_ptr.data() + d.bond_ptr_off;
+        const uint32_t* bi = h->bond_items.data() + d.bond_item_off;
+        order.resize(n); pos.assign(n, -1);
+        for (int a = 0; a < n; a++) order[a] = a;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return bp[a + 1] - bp[a] > bp[b + 1] - bp[b]; });
+        uint16_t* perm = h->md2_perm.data() + s * (size_t)np;
+        auto slot_of_group = [&](int g) { const int k = g / 32, r = g % 32; return k * 32 + ((k & 1) ? 31 - r : r); };
+        for (int g = 0; g < G; g++) {
+            const int gi = slot_of_group(g), k = gi / 32, w = gi % 32;
+            for (int l = 0; l < 32; l++) {
+                const int q = g * 32 + l;
+                if (q >= n) break;
+                const int p = k * MD2_T + w * 32 + l;
+                perm[p] = (uint16_t)order[q]; pos[order[q]] = p;
+            }
+        }
+        Md2Desc& m = h->md2_desc[s];
+        m.perm_off = (int32_t)(s * (size_t)np);
+        m.ell_desc_off = (int32_t)(s * (size_t)(G + 1));
+        m.ell_item_off = (int64_t)h->md2_ell_items.size();
+        m.K = K;
+        int32_t* eoff = h->md2_ell_off.data() + m.ell_desc_off;
+        size_t base = h->md2_ell_items.size();
+        for (int gi = 0; gi < G; gi++) {           // blocks in (slot, warp) order = the order the kernel indexes them
+            const int k = gi / 32, w = gi % 32;
+            int cols = 0;
+            for (int l = 0; l < 32; l++) {
+                const int a = perm[k * MD2_T + w * 32 + l];
+                if (a != MD2_NONE) cols = std::max(cols, bp[a + 1] - bp[a]);
+            }
+            eoff[gi] = (int32_t)(h->md2_ell_items.size() - base);
+            h->md2_ell_items.resize(h->md2_ell_items.size() + (size_t)cols * 32, MD2_PAD);
+            uint32_t* blk = h->md2_ell_items.data() + base + eoff[gi];
+            for (int l = 0; l < 32; l++) {
+                const int a = perm[k * MD2_T + w * 32 + l];
+                if (a == MD2_NONE) continue;
+                for (int c = 0; c < bp[a + 1] - bp[a]; c++) {
+                    const uint32_t it = bi[bp[a] + c];
+                    blk[c * 32 + l] = (uint32_t)pos[it & 0xffffu] | (it & 0xffff0000u);
+                }
+            }
+        }
+        eoff[G] = (int32_t)(h->md2_ell_items.size() - base);
+    }
+}
+
 static int upload(igmk_handle* h)
 {
     if (!h->dirty) return 0;
@@ -224,6 +340,7 @@ static int upload(igmk_handle* h)
     const size_t na = h->xyzr.size(), ns = h->desc.size();
     CU(dev_alloc_copy(&h->d_desc, h->desc));
     CU(dev_alloc_copy(&h->d_xyzr, h->xyzr));
+    CU(dev_alloc_copy(&h->d_xyzr0, h->xyzr0));
     CU(dev_alloc_copy(&h->d_kind, h->kind));
     CU(dev_alloc_copy(&h->d_envmask, h->envmask));
     CU(dev_alloc_copy(&h->d_bond_ptr, h->bond_ptr));
@@ -239,6 +356,20 @@ static int upload(igmk_handle* h)
     CU(cudaMalloc((void**)&h->d_flags, std::max<size_t>(ns, 1) * sizeof(int32_t)));
     CU(cudaMemset(h->d_res, 0, std::max<size_t>(ns, 1) * sizeof(igmk_result_t)));
     CU(cudaMemset(h->d_flags, 0, std::max<size_t>(ns, 1) * sizeof(int32_t)));
+    h->md2_K = md2_pick_K(h->max_atoms);
+    if (h->md2_K > 0) {
+        md2_build(h);
+        CU(dev_alloc_copy(&h->d_md2_desc, h->md2_desc));
+        CU(dev_alloc_copy(&h->d_md2_perm, h->md2_perm));
+        CU(dev_alloc_copy(&h->d_md2_ell_off, h->md2_ell_off));
+        CU(dev_alloc_copy(&h->d_md2_ell_items, h->md2_ell_items));
+        CU(cudaMalloc((void**)&h->d_md2_nl, h->md2_perm.size() * (size_t)h->md2_nlw * sizeof(uint16_t)));
+    }
+    h->h2d_bytes = ns * sizeof(StructDesc) + 2 * na * sizeof(float4) + na * (sizeof(uint8_t) + sizeof(uint32_t)) +
+                   h->bond_ptr.size() * sizeof(int32_t) + h->bond_items.size() * sizeof(uint32_t) +
+                   h->btype_f.size() * (sizeof(float2) + sizeof(double2)) +
+                   h->md2_desc.size() * sizeof(Md2Desc) + h->md2_perm.size() * sizeof(uint16_t) +
+                   h->md2_ell_off.size() * sizeof(int32_t) + h->md2_ell_items.size() * sizeof(uint32_t);
     h->dirty = false;
     return 0;
 }
@@ -251,13 +382,22 @@ extern "C" int igmk_upload(igmk_handle_t* h)
     return upload(h);
 }
 
+extern "C" int igmk_last_timings(igmk_handle_t* h, double* md_ms, double* cg_ms, int64_t* h2d_bytes)
+{
+    if (!h) return fail("igmk_last_timings: NULL handle");
+    if (md_ms) *md_ms = h->md_ms;
+    if (cg_ms) *cg_ms = h->cg_ms;
+    if (h2d_bytes) *h2d_bytes = (int64_t)h->h2d_bytes;
+    return 0;
+}
+
 extern "C" int igmk_reset_coordinates(igmk_handle_t* h)
 {
     if (!h) return fail("igmk_reset_coordinates: NULL handle");
     h->xyzr = h->xyzr0;
     if (!h->dirty && h->d_xyzr) {
         CU(cudaSetDevice(h->device));
-        CU(cudaMemcpy(h->d_xyzr, h->xyzr0.data(), h->xyzr0.size() * sizeof(float4), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(h->d_xyzr, h->d_xyzr0, h->xyzr0.size() * sizeof(float4), cudaMemcpyDeviceToDevice));
     }
     return 0;
 }
@@ -302,6 +442,32 @@ static bool widen_neighbour_table(igmk_handle* h)
     return true;
 }
 
+template <int K>
+static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
+{
+    const size_t sm = md2_smem_bytes(K);
+    CU(cudaFuncSetAttribute(k_md2<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    Md2View V;
+    V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
+    V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw;
+    k_md2<K><<<ns, MD2_T, sm>>>(B, V, h->d_md2_desc, P);
+    CU(cudaGetLastError());
+    return 0;
+}
+
+static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
+{
+    switch (h->md2_K) {
+        case 1: return launch_md2_k<1>(h, B, P, ns);
+        case 2: return launch_md2_k<2>(h, B, P, ns);
+        case 3: return launch_md2_k<3>(h, B, P, ns);
+        case 4: return launch_md2_k<4>(h, B, P, ns);
+        case 6: return launch_md2_k<6>(h, B, P, ns);
+        case 8: return launch_md2_k<8>(h, B, P, ns);
+    }
+    return fail("igmk_run: structures with more than 8192 atoms need the cluster path (not built yet)");
+}
+
 extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
 {
     if (!h || !prot) return fail("igmk_run: NULL argument");
@@ -310,35 +476,41 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
     if (!(prot->timestep > 0.0)) return fail("igmk_run: timestep must be > 0");
     CU(cudaSetDevice(h->device));
     const int ns = (int)h->desc.size();
-    const size_t sm_md = ctx_smem_bytes<float>(h->max_atoms, true);
     const size_t sm_cg = ctx_smem_bytes<double>(h->max_atoms, false);
-    CU(cudaFuncSetAttribute(k_md, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_md));
     CU(cudaFuncSetAttribute(k_cg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_cg));
     float ms = 0.f;
     for (;;) {
         if (int rc = upload(h)) return rc;
         Batch B = make_batch(h);
         CU(cudaMemset(h->d_flags, 0, ns * sizeof(int32_t)));
-        cudaEvent_t e0, e1;
-        CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+        cudaEvent_t e0, e1, e2;
+        CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
         CU(cudaEventRecord(e0));
-        MdParams P; P.prot = *prot;
-        k_md<<<ns, MD_THREADS, sm_md>>>(B, P);
-        CU(cudaGetLastError());
+        MdParams P; P.prot = *prot; P.skin_factor = h->skin_factor;
+        if (int rc = launch_md2(h, B, P, ns)) return rc;
+        CU(cudaEventRecord(e1));
         k_cg<<<ns, MD_THREADS, sm_cg>>>(B, *prot);
         CU(cudaGetLastError());
-        CU(cudaEventRecord(e1));
-        CU(cudaEventSynchronize(e1));
-        CU(cudaEventElapsedTime(&ms, e0, e1));
-        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        CU(cudaEventRecord(e2));
+        CU(cudaEventSynchronize(e2));
+        float ms_md = 0.f, ms_cg = 0.f;
+        CU(cudaEventElapsedTime(&ms_md, e0, e1));
+        CU(cudaEventElapsedTime(&ms_cg, e1, e2));
+        ms = ms_md + ms_cg; h->md_ms = ms_md; h->cg_ms = ms_cg;
+        cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
         const int rc = collect(h, "igmk_run");
-        if (rc == IGMK_NL_OVERFLOW && widen_neighbour_table(h)) continue;
+        if (rc == IGMK_NL_OVERFLOW) {                                  // either table may have overflowed
+            const int cap = (h->max_atoms + 7) / 8 * 8;
+            const bool w1 = widen_neighbour_table(h);
+            const bool w2 = h->md2_nlw < cap;
+            if (w2) { h->md2_nlw = std::min(h->md2_nlw * 2, cap); h->dirty = true; }
+            if (w1 || w2) continue;
+        }
         if (rc) return 1;
         break;
     }
     for (auto& r : h->res) r.md_seconds = ms * 1e-3;
-    h->forces.resize(h->xyzr.size() * 3);
-    CU(cudaMemcpy(h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    h->forces.clear();                 // copied on demand by igmk_fetch_forces
     h->have_forces = true;
     return 0;
 }
@@ -398,6 +570,11 @@ extern "C" int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out)
     if (!h || !f_out) return fail("igmk_fetch_forces: NULL argument");
     if (slot < 0 || slot >= (int)h->desc.size()) return fail("igmk_fetch_forces: bad slot");
     if (!h->have_forces) return fail("igmk_fetch_forces: no forces available");
+    if (h->forces.size() != h->xyzr.size() * 3) {
+        CU(cudaSetDevice(h->device));
+        h->forces.resize(h->xyzr.size() * 3);
+        CU(cudaMemcpy(h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    }
     const StructDesc& d = h->desc[slot];
     memcpy(f_out, h->forces.data() + (size_t)d.atom_off * 3, (size_t)d.n_atoms * 3 * sizeof(double));
     return 0;
@@ -654,6 +831,29 @@ extern "C" int igmk_pop_actdist(igmk_pop_t* p, int64_t n_pairs, const int32_t* p
     if (int rc = igmk_pop_set_pairs(p, n_pairs, pair_i, pair_j, pwish, plast)) return rc;
     if (int rc = igmk_pop_actdist_launch(p, contact_range)) return rc;
     return igmk_pop_actdist_collect(p, max_rows, row, col, dist, prob, n_rows_out);
+}
+
+extern "C" int igmk_pop_contact_freq(igmk_pop_t* p, int64_t n_pairs, const int32_t* pair_i, const int32_t* pair_j,
+                                     double contact_range, float* freq)
+{
+    if (!p) return fail("igmk_pop_contact_freq: NULL handle");
+    if (n_pairs == 0) return 0;
+    if (!freq) return fail("igmk_pop_contact_freq: NULL argument");
+    const double zero = 0.0;
+    (void)zero;
+    std::vector<double> dummy((size_t)n_pairs, 0.0);
+    if (int rc = igmk_pop_set_pairs(p, n_pairs, pair_i, pair_j, dummy.data(), dummy.data())) return rc;
+    CU(cudaSetDevice(p->device));
+    const int64_t grid = std::min<int64_t>((n_pairs + 7) / 8, (int64_t)p->sm_count * 32);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_contact_freq<<<(int)grid, 256, 0, p->stream>>>(p->view(), n_pairs, p->d_pi.p, p->d_pj.p, (float)contact_range, p->d_dist.p);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(p->ev1, p->stream));
+    CU(cudaMemcpyAsync(freq, p->d_dist.p, n_pairs * sizeof(float), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    CU(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+    p->n_pairs = 0; p->actdist_done = false;
+    return 0;
 }
 
 extern "C" int igmk_pop_set_rows(igmk_pop_t* p, int64_t n_rows, const int32_t* row, const int32_t* col, const float* dist)

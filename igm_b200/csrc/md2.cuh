@@ -1,0 +1,464 @@
+// md2.cuh -- the annealing-MD kernel of the M-step (lammps.py:285-351), one CTA per structure.
+//
+// Work decomposition: THREAD PER ATOM.  Thread t owns the atoms at positions t, t+1024, ...
+// (K slots per thread) of a host-chosen ordering in which the 32 atoms of a warp-slot have
+// similar bond counts.  Each thread gathers the complete force on its own atoms (no atomics, no
+// cross-lane reductions => bit-reproducible), and keeps their velocities and forces in registers.
+// Shared memory holds only what other threads read: the positions (float4 x,y,z,radius), plus the
+// coordinates of the last neighbour build and the cell grid used during a rebuild.
+// Lists are laid out so that a warp reads them with full 32-lane coalescing:
+//   * neighbour table   nl[c][p]   (uint16, column c of position p)  -- rebuilt in-kernel
+//   * bond items        ell[g][c][lane] (uint32 partner | type<<16) -- sliced ELL per warp-slot g
+// Both live in global memory and are streamed through L1/L2.
+#pragma once
+#include "mstep.cuh"
+
+namespace igmk {
+
+constexpr int MD2_T = 1024;           // threads per CTA
+constexpr int MD2_KMAX = 8;           // slots per thread supported (n_atoms <= 8192 on the 1-CTA path)
+constexpr int MD2_NLW0 = 256;         // initial neighbour-table width (columns)
+constexpr uint16_t MD2_NONE = 0xffffu;
+constexpr uint32_t MD2_PAD = 0xffffffffu;
+
+struct Md2View {
+    const uint16_t* perm;      // [sum np] position -> original atom (0xffff: empty position)
+    const int32_t*  ell_off;   // per structure: 32*K+1 offsets (in items) of each warp-slot block
+    const uint32_t* ell_items; // sliced-ELL bond items
+    uint16_t*       nl;        // [sum np * nl_width] column-major per structure
+    int32_t         nl_width;
+};
+
+struct Md2Desc {               // per structure
+    int64_t ell_item_off;
+    int32_t perm_off;          // offset into perm (== sum of np of the structures before)
+    int32_t ell_desc_off;      // offset into ell_off
+    int32_t K;
+    int32_t pad;
+};
+
+__host__ __device__ inline size_t md2_smem_bytes(int K)
+{
+    const size_t np = (size_t)K * MD2_T;
+    size_t b = np * 16;                       // x
+    b += np * 12;                             // build coordinates
+    b += ((size_t)MAX_CELLS + 1) * 4;         // cell_start
+    b += np * 2 * 2;                          // cell_atoms, cell_of
+    b += 2 * 32 * 8 * 4;                      // reduction scratch
+    b += IGMK_MAX_ENVELOPES * 4 * 4;          // envelope parameters
+    return (b + 255) / 256 * 256;
+}
+
+template <int K>
+__global__ void __launch_bounds__(MD2_T, 1)
+k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int np = K * MD2_T;
+    const StructDesc* d = B.desc + blockIdx.x;
+    const Md2Desc md = mdesc[blockIdx.x];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = d->n_atoms;
+
+    float4* x = (float4*)smem;
+    float* xbx = (float*)(x + np); float* xby = xbx + np; float* xbz = xby + np;
+    uint32_t* cell_start = (uint32_t*)(xbz + np);
+    uint16_t* cell_atoms = (uint16_t*)(cell_start + MAX_CELLS + 1);
+    uint16_t* cell_of = cell_atoms + np;
+    float* rbuf = (float*)(cell_of + np);
+    float* envp = rbuf + 2 * 256;
+    int rb_par = 0;
+
+    const igmk_protocol_t& pr = P.prot;
+    const uint16_t* perm = V.perm + md.perm_off;
+    const int32_t* eoff = V.ell_off + md.ell_desc_off;
+    const uint32_t* eitems = V.ell_items + md.ell_item_off;
+    uint16_t* nl = V.nl + (size_t)md.perm_off * V.nl_width;
+    const int nlw = V.nl_width;
+    const float2* btype = B.btype_f + d->btype_off;
+    float4* xg = B.xyzr + d->atom_off;
+
+    // ---- per-slot state in registers ----
+    int   kind[K];            // IGMK_KIND_*, 3 = empty position
+    uint32_t emask[K];
+    int   ncnt[K];            // neighbours in my row
+    int   boff[K], bcols[K];  // my warp-slot's block of bond items
+    float vx[K], vy[K], vz[K], fx[K], fy[K], fz[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const int p = k * MD2_T + tid;
+        const uint16_t a = perm[p];
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        kind[k] = 3; emask[k] = 0;
+        if (a != MD2_NONE) {
+            q = xg[a];
+            kind[k] = B.kind[d->atom_off + a];
+            emask[k] = B.envmask[d->atom_off + a];
+        }
+        x[p] = q;
+        const int g = k * 32 + warp;
+        boff[k] = eoff[g];
+        bcols[k] = (eoff[g + 1] - eoff[g]) >> 5;
+        vx[k] = vy[k] = vz[k] = 0.f; fx[k] = fy[k] = fz[k] = 0.f; ncnt[k] = 0;
+    }
+    // the two most frequent bond types stay in registers (the host orders the type table by use)
+    const float2 bt0 = btype[0], bt1 = btype[1];
+    const float skin = d->maxrad * P.skin_factor;
+    const float lim = 0.25f * skin * skin;
+    const float bond_pref2 = 2.f * (float)pr.bond_prefactor;
+    float ev_c = -1.f;                 // evfactor * stage scale / pi  (force prefactor / rc), < 0: no sterics
+    int n_rebuild = 0, overflow = 0;
+    __syncthreads();
+
+    // ------------------------------------------------------------------------------------
+    auto block_sum1 = [&](float v) -> float {
+        float* buf = rbuf + (rb_par ^= 1) * 256;
+        v = warp_sum(v);
+        if (lane == 0) buf[warp] = v;
+        __syncthreads();
+        return warp_sum(buf[lane]);          // MD2_T / 32 == 32 partials: one per lane, same tree in every warp
+    };
+
+    auto set_stage = [&](double ev_scale, double env_scale) {
+        ev_c = d->evfactor < 0 ? -1.f : (float)(d->evfactor * ev_scale / 3.14159265358979323846);
+        if (tid < IGMK_MAX_ENVELOPES * 4) {
+            const int e = tid >> 2, c = tid & 3;
+            envp[tid] = e < d->n_env ? (float)(c < 3 ? d->env[e][c] * env_scale : d->env[e][3]) : 0.f;
+        }
+        __syncthreads();
+    };
+
+    // ---- neighbour table: cell binning in shared memory, every thread fills its own rows ----
+    auto rebuild = [&]() {
+        float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2_T + tid;
+            const float4 q = x[p];
+            xbx[p] = q.x; xby[p] = q.y; xbz[p] = q.z;
+            if (kind[k] == IGMK_KIND_BEAD) {
+                lo[0] = fminf(lo[0], q.x); hi[0] = fmaxf(hi[0], q.x);
+                lo[1] = fminf(lo[1], q.y); hi[1] = fmaxf(hi[1], q.y);
+                lo[2] = fminf(lo[2], q.z); hi[2] = fmaxf(hi[2], q.z);
+            }
+        }
+        float* rb = rbuf + (rb_par ^= 1) * 256;
+#pragma unroll
+        for (int c = 0; c < 3; c++) { lo[c] = warp_min(lo[c]); hi[c] = warp_max(hi[c]); }
+        if (lane == 0) {
+#pragma unroll
+            for (int c = 0; c < 3; c++) { rb[warp * 6 + c] = lo[c]; rb[warp * 6 + 3 + c] = hi[c]; }
+        }
+        for (int c = tid; c <= MAX_CELLS; c += MD2_T) cell_start[c] = 0;
+        __syncthreads();
+#pragma unroll
+        for (int c = 0; c < 3; c++) { lo[c] = warp_min(rb[lane * 6 + c]); hi[c] = warp_max(rb[lane * 6 + 3 + c]); }
+        const float rlist = 2.f * d->maxrad + skin;
+        int dim[3]; float inv[3];
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            float ext = hi[c] - lo[c];
+            if (!(ext > 0.f)) ext = 0.f;
+            int m = (int)(ext / rlist) + 1;
+            if (m > MAX_CELL_DIM) m = MAX_CELL_DIM;
+            float cw = ext / (float)m;
+            if (cw < rlist) cw = rlist;
+            dim[c] = m; inv[c] = 1.f / cw;
+        }
+        const int ncell = dim[0] * dim[1] * dim[2];
+        // counts per cell (integer atomics: the counts do not depend on the order)
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2_T + tid;
+            int c = MD2_NONE;
+            if (kind[k] == IGMK_KIND_BEAD) {
+                const float4 q = x[p];
+                int cx = (int)((q.x - lo[0]) * inv[0]), cy = (int)((q.y - lo[1]) * inv[1]), cz = (int)((q.z - lo[2]) * inv[2]);
+                cx = min(max(cx, 0), dim[0] - 1); cy = min(max(cy, 0), dim[1] - 1); cz = min(max(cz, 0), dim[2] - 1);
+                c = (cz * dim[1] + cy) * dim[0] + cx;
+                atomicAdd(&cell_start[c + 1], 1u);
+            }
+            cell_of[p] = (uint16_t)c;
+        }
+        __syncthreads();
+        // inclusive scan of cell_start[1..ncell] (cell_start[c+1] held the count of cell c)
+        {
+            const int per = (ncell + MD2_T - 1) / MD2_T;
+            const int c0 = min(tid * per, ncell), c1 = min(c0 + per, ncell);
+            int s = 0;
+            for (int c = c0; c < c1; c++) s += cell_start[c + 1];
+            int incl = s;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+            int* ib = (int*)(rbuf + (rb_par ^= 1) * 256);
+            if (lane == 31) ib[warp] = incl;
+            __syncthreads();
+            int base = 0;
+            for (int w = 0; w < warp; w++) base += ib[w];
+            int run = base + incl - s;
+            for (int c = c0; c < c1; c++) { const int cnt = cell_start[c + 1]; run += cnt; cell_start[c + 1] = run; }
+        }
+        __syncthreads();
+        // scatter with a per-cell cursor kept in cell_of's upper half?  no: reuse the counts trick --
+        // drop atoms unordered behind the cell start, then sort each (tiny) cell by index so that the
+        // row order, and with it the floating-point summation order, is independent of the race.
+        uint32_t* cursor = (uint32_t*)xbx;          // aliases the build x, which is re-written below
+        for (int c = tid; c < ncell; c += MD2_T) cursor[c] = 0;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2_T + tid;
+            const int c = cell_of[p];
+            if (c != MD2_NONE) {
+                const uint32_t pos = atomicAdd(&cursor[c], 1u);
+                cell_atoms[cell_start[c] + pos] = (uint16_t)p;
+            }
+        }
+        __syncthreads();
+        for (int c = tid; c < ncell; c += MD2_T) {
+            const int b = cell_start[c], e = cell_start[c + 1];
+            for (int q = b + 1; q < e; q++) {
+                const uint16_t v = cell_atoms[q]; int r = q - 1;
+                while (r >= b && cell_atoms[r] > v) { cell_atoms[r + 1] = cell_atoms[r]; r--; }
+                cell_atoms[r + 1] = v;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < K; k++) xbx[k * MD2_T + tid] = x[k * MD2_T + tid].x;
+        // neighbour search: my rows
+        int ovf = 0;
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2_T + tid;
+            int cnt = 0;
+            const int c = cell_of[p];
+            if (c != MD2_NONE) {
+                const float4 q = x[p];
+                const int cx = c % dim[0], cy = (c / dim[0]) % dim[1], cz = c / (dim[0] * dim[1]);
+                const int ax0 = max(cx - 1, 0), ax1 = min(cx + 1, dim[0] - 1);
+                uint16_t* row = nl + p;
+                for (int dz = -1; dz <= 1; dz++) {
+                    const int az = cz + dz;
+                    if (az < 0 || az >= dim[2]) continue;
+                    for (int dy = -1; dy <= 1; dy++) {
+                        const int ay = cy + dy;
+                        if (ay < 0 || ay >= dim[1]) continue;
+                        const int cb = (az * dim[1] + ay) * dim[0];
+                        const int b = cell_start[cb + ax0], e = cell_start[cb + ax1 + 1];   // 3 cells, contiguous
+                        for (int s = b; s < e; s++) {
+                            const int j = cell_atoms[s];
+                            const float4 pj = x[j];
+                            const float ddx = q.x - pj.x, ddy = q.y - pj.y, ddz = q.z - pj.z;
+                            const float rl = q.w + pj.w + skin;
+                            if (j != p && ddx * ddx + ddy * ddy + ddz * ddz < rl * rl) {
+                                if (cnt < nlw) row[(size_t)cnt * np] = (uint16_t)j;
+                                cnt++;
+                            }
+                        }
+                    }
+                }
+                if (cnt > nlw) { ovf = 1; cnt = nlw; }
+            }
+            ncnt[k] = cnt;
+        }
+        overflow |= __syncthreads_or(ovf);
+        n_rebuild++;
+    };
+
+    // ---- forces on my atoms (gather) -------------------------------------------------------
+    auto forces = [&]() {
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2_T + tid;
+            const float4 pi = x[p];
+            float ax = 0.f, ay = 0.f, az = 0.f;
+            // pair_style soft: F = A pi/rc sin(pi r/rc) r_hat, A = rc^2 ev/pi^2  =>  F/r = ev_c rc sin(pi r/rc) / r
+            if (ev_c >= 0.f) {
+                const uint16_t* col = nl + p;
+                const int cnt = ncnt[k];
+                for (int q = 0; q < cnt; q += 4) {
+                    int j[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) j[u] = (q + u < cnt) ? (int)col[(size_t)(q + u) * np] : -1;
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        if (j[u] >= 0) {
+                            const float4 pj = x[j[u]];
+                            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                            const float rc = pi.w + pj.w;
+                            const float r2 = dx * dx + dy * dy + dz * dz;
+                            if (r2 < rc * rc && r2 > 0.f) {
+                                const float rinv = rsqrtf(r2);
+                                const float r = r2 * rinv;
+                                const float s = __sinf(3.14159265358979323846f * __fdividef(r, rc));
+                                const float fp = ev_c * rc * s * rinv;
+                                ax += dx * fp; ay += dy * fp; az += dz * fp;
+                            }
+                        }
+                    }
+                }
+            }
+            // harmonic upper / lower bounds: F = -2 pref k (r - r0) r_hat when violated
+            {
+                const uint32_t* it = eitems + boff[k] + lane;
+                const int nc = bcols[k];
+                for (int c = 0; c < nc; c += 4) {
+                    uint32_t v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) v[u] = (c + u < nc) ? it[(c + u) * 32] : MD2_PAD;
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        if (v[u] != MD2_PAD) {
+                            const uint32_t ti = v[u] >> 16;
+                            const float2 t = ti == 0 ? bt0 : (ti == 1 ? bt1 : btype[ti]);   // (r0, k); k < 0: lower bound
+                            const float4 pj = x[v[u] & 0xffffu];
+                            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                            const float r2 = dx * dx + dy * dy + dz * dz;
+                            const float r02 = t.x * t.x;
+                            const bool act = t.y > 0.f ? (r2 > r02) : (r2 < r02);
+                            if (act && r2 > 0.f) {
+                                const float rinv = rsqrtf(r2);
+                                const float fb = -bond_pref2 * fabsf(t.y) * (1.f - t.x * rinv);
+                                ax += dx * fb; ay += dy * fb; az += dz * fb;
+                            }
+                        }
+                    }
+                }
+            }
+            // fix ellipsoidalenvelope
+            uint32_t m = emask[k];
+            while (m) {
+                const int e = __ffs(m) - 1; m &= m - 1;
+                const float a = envp[4 * e] - pi.w, b = envp[4 * e + 1] - pi.w, c = envp[4 * e + 2] - pi.w, kk = envp[4 * e + 3];
+                const float k2 = pi.x * pi.x / (a * a) + pi.y * pi.y / (b * b) + pi.z * pi.z / (c * c);
+                const bool act = kk > 0.f ? (k2 > 1.f) : (kk < 0.f && k2 < 1.f);
+                if (act && k2 > 0.f) {
+                    const float g = fabsf(kk) * (1.f - rsqrtf(k2));
+                    ax -= g * pi.x; ay -= g * pi.y; az -= g * pi.z;
+                }
+            }
+            if (kind[k] != IGMK_KIND_BEAD && kind[k] != IGMK_KIND_CENTROID) { ax = 0.f; ay = 0.f; az = 0.f; }   // frozen / empty
+            fx[k] = ax; fy[k] = ay; fz[k] = az;
+        }
+    };
+
+    // ------------------------------------------------------------------------------------
+    rebuild();
+    const float dt = (float)pr.timestep, dtf = 0.5f * dt;
+    const float dof = 3.f * (float)d->n_nonfixed - 3.f;
+    float last_temp = 0.f;
+
+    for (int st = 0; st < pr.n_stage; st++) {
+        set_stage(pr.evfactor[st], pr.envfactor[st]);
+        for (int sub = (pr.relax_mdsteps > 0 ? 0 : 1); sub < 2; sub++) {
+            const int nsteps = sub == 0 ? pr.relax_mdsteps : pr.mdsteps[st];
+            const float t0 = sub == 0 ? (float)pr.relax_temperature : (float)pr.tstart[st];
+            const float t1 = sub == 0 ? (float)pr.relax_temperature : (float)pr.tstop[st];
+            const float xmax = sub == 0 ? (float)pr.relax_max_velocity : (float)pr.max_velocity;
+            const float vlim2 = (xmax / dt) * (xmax / dt);
+            // ---- velocity nonfixed create t0 seed+st (dist uniform, mom yes, loop all) ----
+            {
+                uint32_t seed = (uint32_t)((d->seed + st) % 2147483647ll);
+                if (seed == 0) seed = 1;
+                float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    float a = 0.f, b = 0.f, c = 0.f;
+                    if (kind[k] == IGMK_KIND_BEAD || kind[k] == IGMK_KIND_CENTROID) {
+                        uint32_t r = ranpark_jump(seed, 3u * (uint32_t)perm[k * MD2_T + tid] + 1u);
+                        const double AM = 1.0 / 2147483647.0;
+                        a = (float)(AM * r - 0.5);
+                        r = (uint32_t)(((uint64_t)r * 16807ull) % 2147483647ull); b = (float)(AM * r - 0.5);
+                        r = (uint32_t)(((uint64_t)r * 16807ull) % 2147483647ull); c = (float)(AM * r - 0.5);
+                    }
+                    vx[k] = a; vy[k] = b; vz[k] = c;
+                    s0 += a; s1 += b; s2 += c;
+                }
+                s0 = block_sum1(s0); s1 = block_sum1(s1); s2 = block_sum1(s2);
+                const float inv = d->n_nonfixed > 0 ? 1.f / (float)d->n_nonfixed : 0.f;
+                float ke = 0.f;
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    if (kind[k] == IGMK_KIND_BEAD || kind[k] == IGMK_KIND_CENTROID) {
+                        vx[k] -= s0 * inv; vy[k] -= s1 * inv; vz[k] -= s2 * inv;
+                        ke += vx[k] * vx[k] + vy[k] * vy[k] + vz[k] * vz[k];
+                    }
+                }
+                ke = block_sum1(ke);
+                const float tcur = dof > 0.f ? ke / dof : 0.f;
+                const float fac = tcur > 0.f ? sqrtf(t0 / tcur) : 0.f;
+#pragma unroll
+                for (int k = 0; k < K; k++) { vx[k] *= fac; vy[k] *= fac; vz[k] *= fac; }
+            }
+            // ---- run nsteps: velocity Verlet with the nve/limit speed cap + temp/rescale ----
+            forces();                                   // run setup
+            float scale = 1.f;
+            for (int step = 0; step <= nsteps; step++) {
+                if (step > 0) {
+                    forces();
+                    float ke = 0.f;
+#pragma unroll
+                    for (int k = 0; k < K; k++) {       // second half kick (frozen/empty: f = v = 0)
+                        float a = vx[k] + dtf * fx[k], b = vy[k] + dtf * fy[k], c = vz[k] + dtf * fz[k];
+                        const float vsq = a * a + b * b + c * c;
+                        if (vsq > vlim2) { const float sc = sqrtf(vlim2 / vsq); a *= sc; b *= sc; c *= sc; }
+                        vx[k] = a; vy[k] = b; vz[k] = c;
+                        ke += a * a + b * b + c * c;
+                    }
+                    ke = block_sum1(ke);                // its barrier also ends every read of x for this step
+                    const float tcur = dof > 0.f ? ke / dof : 0.f;
+                    const float ttar = t0 + ((float)step / (float)nsteps) * (t1 - t0);
+                    scale = 1.f;
+                    if (tcur > 0.f && fabsf(tcur - ttar) > 0.1f) scale = sqrtf(ttar / tcur);
+                    last_temp = tcur * scale * scale;
+                } else {
+                    __syncthreads();
+                }
+                if (step == nsteps) {
+#pragma unroll
+                    for (int k = 0; k < K; k++) { vx[k] *= scale; vy[k] *= scale; vz[k] *= scale; }
+                    break;
+                }
+                int need = 0;
+#pragma unroll
+                for (int k = 0; k < K; k++) {           // rescale + first half kick + drift
+                    if (kind[k] == IGMK_KIND_BEAD || kind[k] == IGMK_KIND_CENTROID) {
+                        const int p = k * MD2_T + tid;
+                        float a = vx[k] * scale + dtf * fx[k], b = vy[k] * scale + dtf * fy[k], c = vz[k] * scale + dtf * fz[k];
+                        const float vsq = a * a + b * b + c * c;
+                        if (vsq > vlim2) { const float sc = sqrtf(vlim2 / vsq); a *= sc; b *= sc; c *= sc; }
+                        vx[k] = a; vy[k] = b; vz[k] = c;
+                        float4 q = x[p];
+                        q.x += dt * a; q.y += dt * b; q.z += dt * c;
+                        x[p] = q;
+                        const float ddx = q.x - xbx[p], ddy = q.y - xby[p], ddz = q.z - xbz[p];
+                        need |= (ddx * ddx + ddy * ddy + ddz * ddz > lim);
+                    }
+                }
+                if (__syncthreads_or(need)) rebuild();
+            }
+        }
+    }
+    // results: coordinates back in the original atom order (float32 like Particle.pos)
+    int bad = 0;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const uint16_t a = perm[k * MD2_T + tid];
+        if (a != MD2_NONE) {
+            const float4 q = x[k * MD2_T + tid];
+            xg[a] = q;
+            bad |= !(isfinite(q.x) && isfinite(q.y) && isfinite(q.z));
+        }
+    }
+    bad = __syncthreads_or(bad);
+    if (tid == 0) {
+        igmk_result_t* r = B.res + blockIdx.x;
+        const double dof_all = 3.0 * n - 3.0;     // thermo `temp` is over group all
+        r->temperature = dof_all > 0 ? (double)last_temp * (double)dof / dof_all : 0.0;
+        r->n_rebuilds = n_rebuild;
+        B.flags[blockIdx.x] = (overflow ? 1 : 0) | (bad ? 2 : 0);
+    }
+}
+
+}  // namespace igmk

@@ -580,149 +580,9 @@ k_single_point(Batch B, double ev_scale, double env_scale, double bond_pref)
 // `velocity create` + nve/limit + temp/rescale.  float32 arithmetic, everything in shared memory.
 struct MdParams {
     igmk_protocol_t prot;
+    float skin_factor;       // neighbour skin = skin_factor * largest bead radius.  The LAMMPS script uses 1
+                             // (`neighbor maxrad bin`, lammps.py:216); results do not depend on it, only the cost
 };
-
-__global__ void __launch_bounds__(MD_THREADS, 1)
-k_md(Batch B, MdParams P)
-{
-    typedef float T;
-    extern __shared__ __align__(16) unsigned char smem[];
-    const StructDesc* d = B.desc + blockIdx.x;
-    Ctx<T> c;
-    T* vel = ctx_carve<T>(c, smem, d->n_atoms, true, nullptr);
-    ctx_bind(c, B, d);
-    const int n = c.n, tid = threadIdx.x, nt = blockDim.x;
-    const size_t np = (size_t)((n + 31) / 32 * 32);
-    T *vx = vel, *vy = vel + np, *vz = vel + 2 * np;
-    const igmk_protocol_t& pr = P.prot;
-    c.bond_pref = T(pr.bond_prefactor);
-    float4* xg = B.xyzr + d->atom_off;
-    for (int i = tid; i < n; i += nt) { c.x[i] = xg[i]; vx[i] = 0.f; vy[i] = 0.f; vz[i] = 0.f; }
-    __syncthreads();
-    c.rebuild();
-
-    const T dt = T(pr.timestep), dtf = T(0.5) * dt;
-    const T dof = T(3.0 * c.n_nonfixed - 3.0);
-    const int team = tid / TEAM, tl = tid % TEAM, nteam = nt / TEAM;
-    const unsigned tmask = ((1u << TEAM) - 1u) << ((tid & 31) / TEAM * TEAM);
-    T last_temp = 0;
-
-    for (int st = 0; st < pr.n_stage; st++) {
-        c.set_stage(pr.evfactor[st], pr.envfactor[st]);
-        for (int sub = (pr.relax_mdsteps > 0 ? 0 : 1); sub < 2; sub++) {
-            const int nsteps = sub == 0 ? pr.relax_mdsteps : pr.mdsteps[st];
-            const T t0 = sub == 0 ? T(pr.relax_temperature) : T(pr.tstart[st]);
-            const T t1 = sub == 0 ? T(pr.relax_temperature) : T(pr.tstop[st]);
-            const T xmax = sub == 0 ? T(pr.relax_max_velocity) : T(pr.max_velocity);
-            const T vlim2 = (xmax / dt) * (xmax / dt);
-            // ---- velocity nonfixed create t0 seed+st (uniform, mom yes, loop all) ----
-            {
-                uint32_t seed = (uint32_t)((d->seed + st) % 2147483647ll);
-                if (seed == 0) seed = 1;
-                T s[3] = {0, 0, 0};
-                for (int i = tid; i < n; i += nt) {
-                    T a = 0, b = 0, cc = 0;
-                    if (c.kind[i] != IGMK_KIND_STATIC) {
-                        uint32_t r = ranpark_jump(seed, 3u * (uint32_t)i + 1u);
-                        const double AM = 1.0 / 2147483647.0;
-                        a = T(AM * r - 0.5);
-                        r = (uint32_t)(((uint64_t)r * 16807ull) % 2147483647ull); b = T(AM * r - 0.5);
-                        r = (uint32_t)(((uint64_t)r * 16807ull) % 2147483647ull); cc = T(AM * r - 0.5);
-                    }
-                    vx[i] = a; vy[i] = b; vz[i] = cc;
-                    s[0] += a; s[1] += b; s[2] += cc;
-                }
-                block_sum<T, 3>(s, c.red());
-                const T inv = c.n_nonfixed > 0 ? T(1) / T(c.n_nonfixed) : T(0);
-                T ke[1] = {0};
-                for (int i = tid; i < n; i += nt) {
-                    if (c.kind[i] != IGMK_KIND_STATIC) {
-                        T a = vx[i] - s[0] * inv, b = vy[i] - s[1] * inv, cc = vz[i] - s[2] * inv;
-                        vx[i] = a; vy[i] = b; vz[i] = cc;
-                        ke[0] += a * a + b * b + cc * cc;
-                    }
-                }
-                __syncthreads();
-                block_sum<T, 1>(ke, c.red());
-                const T tcur = dof > 0 ? ke[0] / dof : T(0);
-                const T fac = tcur > 0 ? sqrtf(t0 / tcur) : T(0);
-                for (int i = tid; i < n; i += nt) { vx[i] *= fac; vy[i] *= fac; vz[i] *= fac; }
-                __syncthreads();
-            }
-            // ---- run nsteps ----
-            // setup: forces at the current coordinates, then the first half kick + drift
-            c.template forces<false>(nullptr);
-            T scale = T(1);
-            for (int step = 0; step <= nsteps; step++) {
-                if (step > 0) {
-                    // forces at x(step) + second half kick of this step (team lane 0) + kinetic energy
-                    T ke[1] = {0};
-                    for (int base = 0; base < n; base += nteam) {
-                        const int i = base + team;
-                        if (i < n) {
-                            T ax, ay, az, dum0, dum1;
-                            c.template atom_force<false>(i, tl, tmask, ax, ay, az, dum0, dum1, nullptr);
-                            if (tl == 0) {
-                                c.fx[i] = ax; c.fy[i] = ay; c.fz[i] = az;
-                                if (c.kind[i] != IGMK_KIND_STATIC) {
-                                    T a = vx[i] + dtf * ax, b = vy[i] + dtf * ay, cc = vz[i] + dtf * az;
-                                    const T vsq = a * a + b * b + cc * cc;
-                                    if (vsq > vlim2) { const T sc = sqrtf(vlim2 / vsq); a *= sc; b *= sc; cc *= sc; }
-                                    vx[i] = a; vy[i] = b; vz[i] = cc;
-                                    ke[0] += a * a + b * b + cc * cc;
-                                }
-                            }
-                        }
-                    }
-                    block_sum<T, 1>(ke, c.red());          // contains the barrier that publishes f and v
-                    // fix temp/rescale 1 t0 t1 0.1 1.0
-                    const T tcur = dof > 0 ? ke[0] / dof : T(0);
-                    const T ttar = t0 + (T(step) / T(nsteps)) * (t1 - t0);
-                    scale = T(1);
-                    if (tcur > T(0) && fabsf(tcur - ttar) > T(0.1)) scale = sqrtf(ttar / tcur);
-                    last_temp = tcur * scale * scale;
-                }
-                if (step == nsteps) {
-                    for (int i = tid; i < n; i += nt) { vx[i] *= scale; vy[i] *= scale; vz[i] *= scale; }
-                    __syncthreads();
-                    break;
-                }
-                // first half kick of the next step + drift (thread per atom)
-                const T lim = T(0.25) * c.skin * c.skin;
-                int need = 0;
-                for (int i = tid; i < n; i += nt) {
-                    if (c.kind[i] == IGMK_KIND_STATIC) continue;
-                    T a = vx[i] * scale + dtf * c.fx[i], b = vy[i] * scale + dtf * c.fy[i], cc = vz[i] * scale + dtf * c.fz[i];
-                    const T vsq = a * a + b * b + cc * cc;
-                    if (vsq > vlim2) { const T sc = sqrtf(vlim2 / vsq); a *= sc; b *= sc; cc *= sc; }
-                    vx[i] = a; vy[i] = b; vz[i] = cc;
-                    float4 p = c.x[i];
-                    p.x += dt * a; p.y += dt * b; p.z += dt * cc;
-                    c.x[i] = p;
-                    const T ddx = p.x - c.bx[i], ddy = p.y - c.by[i], ddz = p.z - c.bz[i];
-                    need |= (ddx * ddx + ddy * ddy + ddz * ddz > lim);
-                }
-                if (__syncthreads_or(need)) c.rebuild();
-            }
-        }
-    }
-    // results: coordinates back to global (float32 like Particle.pos), thermo temperature over ALL atoms
-    int bad = 0;
-    for (int i = tid; i < n; i += nt) {
-        float4 p = c.x[i];
-        xg[i] = p;
-        bad |= !(isfinite(p.x) && isfinite(p.y) && isfinite(p.z));
-    }
-    bad = __syncthreads_or(bad);
-    if (tid == 0) {
-        igmk_result_t* r = B.res + blockIdx.x;
-        // thermo `temp` uses group all: dof = 3*N_all - 3 (velocities of frozen atoms are zero)
-        const double dof_all = 3.0 * n - 3.0;
-        r->temperature = dof_all > 0 ? (double)last_temp * (double)dof / dof_all : 0.0;
-        r->n_rebuilds = c.n_rebuild;
-        B.flags[blockIdx.x] = (c.overflow ? 1 : 0) | (bad ? 2 : 0);
-    }
-}
 
 // ---------------------------------------------------------------------------------------
 // min_style cg / minimize etol ftol maxiter maxeval (lammps.py:354-355): Polak-Ribiere with the

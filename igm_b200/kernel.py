@@ -102,6 +102,12 @@ class MStepBatch(object):
         _abi.check(self._lib.igmk_fetch(self._h, slot, xyz.ctypes.data_as(_abi.c_f32p), C.byref(res)), "igmk_fetch")
         return xyz, res
 
+    def last_timings(self):
+        """-> (md_ms, cg_ms, h2d_bytes) of the last run() / upload()"""
+        a, b, c = C.c_double(0), C.c_double(0), C.c_int64(0)
+        _abi.check(self._lib.igmk_last_timings(self._h, C.byref(a), C.byref(b), C.byref(c)), "igmk_last_timings")
+        return a.value, b.value, c.value
+
     def fetch_forces(self, slot):
         n = self._packed[slot].n_atoms
         f = np.empty((n, 3), dtype=np.float64)

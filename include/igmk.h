@@ -143,6 +143,9 @@ int igmk_single_point_f32(igmk_handle_t* h, double ev_scale, double env_scale,
 int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out /* [n_atoms][3] */,
                igmk_result_t* res);
 int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out /* [n_atoms][3] */);
+/* device time (ms) of the MD and CG launches of the last igmk_run and the bytes the last
+ * upload moved host -> device (any pointer may be NULL) */
+int igmk_last_timings(igmk_handle_t* h, double* md_ms, double* cg_ms, int64_t* h2d_bytes);
 
 /* ---- A-step: device-resident population ------------------------------------------ */
 /*
@@ -192,6 +195,15 @@ int igmk_pop_set_pairs(igmk_pop_t* p, int64_t n_pairs,
 int igmk_pop_actdist_launch(igmk_pop_t* p, double contact_range);
 int igmk_pop_actdist_collect(igmk_pop_t* p, int64_t max_rows, int32_t* row, int32_t* col,
                              float* dist, float* prob, int64_t* n_rows_out);
+
+/*
+ * Contact frequency of haploid pairs in the resident population: the `pnow` of get_actdist
+ * (ActivationDistanceStep.py:373,:419-422), count(d_sq <= (contact_range*(ri+rj))^2) over all copy
+ * pairs and structures divided by their number, as float32.  freq: host, [n_pairs].
+ */
+int igmk_pop_contact_freq(igmk_pop_t* p, int64_t n_pairs,
+                          const int32_t* pair_i, const int32_t* pair_j,
+                          double contact_range, float* freq);
 
 /*
  * Contact assignment: for every actdist row r and every structure s decide
