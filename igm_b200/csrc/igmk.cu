@@ -119,7 +119,7 @@ extern "C" int igmk_create(int device, igmk_handle_t** out)
     h->smem_optin = (int)prop.sharedMemPerBlockOptin;
     if (const char* e = getenv("IGMK_NL_WIDTH")) {          // initial neighbour-table width (tuning / profiling aid)
         const int w = atoi(e);
-        if (w >= 8 && w <= 65536) { h->md2_nlw = w; h->nl_width = w; }
+        if (w >= 8 && w <= 65536) { h->md2_nlw = (w + 7) / 8 * 8; h->nl_width = h->md2_nlw; }
     }
     if (const char* e = getenv("IGMK_SKIN")) {              // neighbour skin in units of the bead radius (results do not depend on it)
         const float f = (float)atof(e);
@@ -317,9 +317,12 @@ static void md2_build(igmk_handle* h)
                 const int a = perm[k * MD2_T + w * 32 + l];
                 if (a != MD2_NONE) cols = std::max(cols, bp[a + 1] - bp[a]);
             }
+            cols = (cols + 3) / 4 * 4;                 // the kernel reads 4 columns at a time, unguarded
             eoff[gi] = (int32_t)(h->md2_ell_items.size() - base);
-            h->md2_ell_items.resize(h->md2_ell_items.size() + (size_t)cols * 32, MD2_PAD);
+            h->md2_ell_items.resize(h->md2_ell_items.size() + (size_t)cols * 32, 0u);
             uint32_t* blk = h->md2_ell_items.data() + base + eoff[gi];
+            for (int l = 0; l < 32; l++)               // padding = bond of type 0 to oneself: r = 0, no force
+                for (int c = 0; c < cols; c++) blk[c * 32 + l] = (uint32_t)(k * MD2_T + w * 32 + l);
             for (int l = 0; l < 32; l++) {
                 const int a = perm[k * MD2_T + w * 32 + l];
                 if (a == MD2_NONE) continue;

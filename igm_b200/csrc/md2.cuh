@@ -37,6 +37,19 @@ struct Md2Desc {               // per structure
     int32_t pad;
 };
 
+// single-instruction approximations (MUFU) without the denormal fix-up code of the CUDA intrinsics;
+// their ~1e-6 relative error is below the float32 round-off the MD trajectory carries anyway
+__device__ __forceinline__ float fast_rsqrt(float v) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ float fast_rcp(float v) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ float fast_sin(float v) { float r; asm("sin.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+// shared-memory load through an explicit 32-bit shared address (keeps the address arithmetic to one shift-add)
+__device__ __forceinline__ float4 lds_f4(uint32_t addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
 __host__ __device__ inline size_t md2_smem_bytes(int K)
 {
     const size_t np = (size_t)K * MD2_T;
@@ -259,6 +272,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                     }
                 }
                 if (cnt > nlw) { ovf = 1; cnt = nlw; }
+                for (int c = cnt; c & 3; c++) row[(size_t)c * np] = (uint16_t)p;     // self padding (nlw % 4 == 0)
             }
             ncnt[k] = cnt;
         }
@@ -267,6 +281,10 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     };
 
     // ---- forces on my atoms (gather) -------------------------------------------------------
+    // Rows of the neighbour table are padded with the atom's own index to a multiple of 4 and the bond
+    // blocks with self-bonds of type 0: a self pair has r2 = 0 and contributes nothing, so the inner
+    // loops need no bounds or validity tests and run branch-free.
+    const uint32_t xs = (uint32_t)__cvta_generic_to_shared(x);
     auto forces = [&]() {
 #pragma unroll
         for (int k = 0; k < K; k++) {
@@ -278,24 +296,20 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 const uint16_t* col = nl + p;
                 const int cnt = ncnt[k];
                 for (int q = 0; q < cnt; q += 4) {
-                    int j[4];
+                    uint32_t j[4];
 #pragma unroll
-                    for (int u = 0; u < 4; u++) j[u] = (q + u < cnt) ? (int)col[(size_t)(q + u) * np] : -1;
+                    for (int u = 0; u < 4; u++) j[u] = col[(size_t)(q + u) * np];
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
-                        if (j[u] >= 0) {
-                            const float4 pj = x[j[u]];
-                            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                            const float rc = pi.w + pj.w;
-                            const float r2 = dx * dx + dy * dy + dz * dz;
-                            if (r2 < rc * rc && r2 > 0.f) {
-                                const float rinv = rsqrtf(r2);
-                                const float r = r2 * rinv;
-                                const float s = __sinf(3.14159265358979323846f * __fdividef(r, rc));
-                                const float fp = ev_c * rc * s * rinv;
-                                ax += dx * fp; ay += dy * fp; az += dz * fp;
-                            }
-                        }
+                        const float4 pj = lds_f4(xs + (j[u] << 4));
+                        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                        const float rc = pi.w + pj.w;
+                        const float r2 = dx * dx + dy * dy + dz * dz;
+                        const float rinv = fast_rsqrt(r2);
+                        const float s = fast_sin(3.14159265358979323846f * (r2 * rinv) * fast_rcp(rc));
+                        float fp = ev_c * rc * s * rinv;
+                        fp = (r2 < rc * rc && r2 > 0.f) ? fp : 0.f;
+                        ax += dx * fp; ay += dy * fp; az += dz * fp;
                     }
                 }
             }
@@ -306,23 +320,20 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 for (int c = 0; c < nc; c += 4) {
                     uint32_t v[4];
 #pragma unroll
-                    for (int u = 0; u < 4; u++) v[u] = (c + u < nc) ? it[(c + u) * 32] : MD2_PAD;
+                    for (int u = 0; u < 4; u++) v[u] = it[(c + u) * 32];
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
-                        if (v[u] != MD2_PAD) {
-                            const uint32_t ti = v[u] >> 16;
-                            const float2 t = ti == 0 ? bt0 : (ti == 1 ? bt1 : btype[ti]);   // (r0, k); k < 0: lower bound
-                            const float4 pj = x[v[u] & 0xffffu];
-                            const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                            const float r2 = dx * dx + dy * dy + dz * dz;
-                            const float r02 = t.x * t.x;
-                            const bool act = t.y > 0.f ? (r2 > r02) : (r2 < r02);
-                            if (act && r2 > 0.f) {
-                                const float rinv = rsqrtf(r2);
-                                const float fb = -bond_pref2 * fabsf(t.y) * (1.f - t.x * rinv);
-                                ax += dx * fb; ay += dy * fb; az += dz * fb;
-                            }
-                        }
+                        const uint32_t ti = v[u] >> 16;
+                        float2 t = ti == 0 ? bt0 : bt1;                    // (r0, k); k < 0: lower bound
+                        if (ti > 1) t = btype[ti];
+                        const float4 pj = lds_f4(xs + ((v[u] & 0xffffu) << 4));
+                        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                        const float r2 = dx * dx + dy * dy + dz * dz;
+                        const float r02 = t.x * t.x;
+                        const bool act = (t.y > 0.f ? (r2 > r02) : (r2 < r02)) && r2 > 0.f;
+                        float fb = -bond_pref2 * fabsf(t.y) * (1.f - t.x * fast_rsqrt(r2));
+                        fb = act ? fb : 0.f;
+                        ax += dx * fb; ay += dy * fb; az += dz * fb;
                     }
                 }
             }
@@ -330,13 +341,13 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             uint32_t m = emask[k];
             while (m) {
                 const int e = __ffs(m) - 1; m &= m - 1;
-                const float a = envp[4 * e] - pi.w, b = envp[4 * e + 1] - pi.w, c = envp[4 * e + 2] - pi.w, kk = envp[4 * e + 3];
-                const float k2 = pi.x * pi.x / (a * a) + pi.y * pi.y / (b * b) + pi.z * pi.z / (c * c);
-                const bool act = kk > 0.f ? (k2 > 1.f) : (kk < 0.f && k2 < 1.f);
-                if (act && k2 > 0.f) {
-                    const float g = fabsf(kk) * (1.f - rsqrtf(k2));
-                    ax -= g * pi.x; ay -= g * pi.y; az -= g * pi.z;
-                }
+                const float ia = fast_rcp(envp[4 * e] - pi.w), ib = fast_rcp(envp[4 * e + 1] - pi.w),
+                            ic = fast_rcp(envp[4 * e + 2] - pi.w), kk = envp[4 * e + 3];
+                const float ux = pi.x * ia, uy = pi.y * ib, uz = pi.z * ic;
+                const float k2 = ux * ux + uy * uy + uz * uz;
+                const bool act = (kk > 0.f ? (k2 > 1.f) : (kk < 0.f && k2 < 1.f)) && k2 > 0.f;
+                const float g = act ? fabsf(kk) * (1.f - fast_rsqrt(k2)) : 0.f;
+                ax -= g * pi.x; ay -= g * pi.y; az -= g * pi.z;
             }
             if (kind[k] != IGMK_KIND_BEAD && kind[k] != IGMK_KIND_CENTROID) { ax = 0.f; ay = 0.f; az = 0.f; }   // frozen / empty
             fx[k] = ax; fy[k] = ay; fz[k] = az;
