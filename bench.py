@@ -24,7 +24,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from igm_b200 import _abi, synth          # noqa: E402
+from igm_b200 import _abi, synth, parallel          # noqa: E402
 
 NUCLEUS_R = 5500.0
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # non-tensor FP32 FMA peak at max clock (derived)
@@ -146,14 +146,8 @@ def build_workload(args, rank, world, device, log):
 
     # ---- A-step: all-gather the slab on the struct axis, shard the pairs ----
     local = torch.from_numpy(crd).to("cuda:%d" % device)
-    if world > 1:
-        parts = [torch.empty_like(local) for _ in range(world)]
-        dist.all_gather(parts, local)
-        slab = torch.cat(parts, dim=1).contiguous()
-    else:
-        slab = local
+    slab = parallel.all_gather_slab(local)            # NCCL all-gather on the structure axis
     S_tot = S * world
-    sl = slice(rank, None, world)                   # interleaved pair shard: equal intra/inter mix per rank
     astep = {}
     with Population(S_tot, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop:
         pop.attach(slab)
@@ -171,12 +165,14 @@ def build_workload(args, rank, world, device, log):
         pi, pj = iu[keep].astype(np.int32), ju[keep].astype(np.int32)
         pw = pw_all[keep].astype(np.float64)
         pl = np.round(freq[keep].astype(np.float64), 4).astype(np.float32).astype(np.float64)
+        lo_p, hi_p = parallel.pair_shards(parallel.pair_cost(pi, pj, g.chrom, g.copy_off), world)[rank]
+        sl = slice(lo_p, hi_p)
         kt, et = [], []
         rows = None
         for rep in range(3):
             torch.cuda.synchronize(device)
             t1 = time.perf_counter()
-            rows = pop.actdist(pi[sl], pj[sl], pw[sl], pl[sl], 2.0)
+            rows = pop.actdist(pi[sl], pj[sl], pw[sl], pl[sl], 2.0)     # this rank's contiguous chunk of the pair list
             et.append(time.perf_counter() - t1)
             kt.append(pop.last_kernel_ms())
         astep["actdist_kernel_ms"] = min(kt)
@@ -184,11 +180,7 @@ def build_workload(args, rank, world, device, log):
         astep["pairs_local"] = int(pi[sl].size)
         n_copies = np.diff(g.copy_off)
         astep["actdist_bytes"] = float(12.0 * S_tot * (n_copies[pi[sl]] + n_copies[pj[sl]]).sum() + 32.0 * pi[sl].size)
-    if world > 1:
-        gathered = [None] * world
-        dist.all_gather_object(gathered, rows)
-        # restore the global pair order: rank r holds pairs r, r+world, ... -> merge by pair ordinal
-        rows = tuple(np.concatenate([gg[k] for gg in gathered]) for k in range(4))
+    rows = parallel.all_gather_rows(rows, device="cuda:%d" % device)      # rank order == global pair order
     row, col, dst, prb = rows
     with Population(S, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop:
         pop.attach(local)

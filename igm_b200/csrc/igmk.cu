@@ -766,21 +766,35 @@ extern "C" int igmk_pop_actdist_launch(igmk_pop_t* p, double contact_range)
     p->last_ms = 0.f;
     if (p->n_pairs == 0) { p->actdist_done = true; return 0; }
     CU(cudaSetDevice(p->device));
-    const size_t smem = (size_t)p->max_copies * p->max_copies * p->n_struct * sizeof(float);
-    if ((long long)smem + 1024 > (long long)p->smem_optin) {
-        char msg[256];
-        snprintf(msg, sizeof msg, "igmk_pop_actdist: %d copy pairs x %d structures need %zu B of shared memory per CTA (limit %d)",
-                 p->max_copies * p->max_copies, p->n_struct, smem, p->smem_optin);
-        return fail(msg);
+    const int spt = (p->n_struct + AD_THREADS - 1) / AD_THREADS;       // structures per thread
+    if (spt <= 8 && !getenv("IGMK_ACTDIST_SMEM")) {
+        // register-resident selection (up to 2048 structures)
+        void (*kern)(PopView, int64_t, const int32_t*, const int32_t*, const double*, const double*, float, float*, float*, uint8_t*) =
+            spt <= 1 ? k_actdist_reg<1> : spt <= 2 ? k_actdist_reg<2> : spt <= 4 ? k_actdist_reg<4> : k_actdist_reg<8>;
+        int per_sm = 1;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, AD_THREADS, 0));
+        if (per_sm < 1) per_sm = 1;
+        const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * per_sm);
+        CU(cudaEventRecord(p->ev0, p->stream));
+        kern<<<(int)grid, AD_THREADS, 0, p->stream>>>(p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, p->d_pw.p, p->d_pl.p,
+                                                      (float)contact_range, p->d_dist.p, p->d_prob.p, p->d_valid.p);
+    } else {
+        const size_t smem = (size_t)p->max_copies * p->max_copies * p->n_struct * sizeof(float);
+        if ((long long)smem + 1024 > (long long)p->smem_optin) {
+            char msg[256];
+            snprintf(msg, sizeof msg, "igmk_pop_actdist: %d copy pairs x %d structures need %zu B of shared memory per CTA (limit %d)",
+                     p->max_copies * p->max_copies, p->n_struct, smem, p->smem_optin);
+            return fail(msg);
+        }
+        CU(cudaFuncSetAttribute(k_actdist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 1;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_actdist, AD_THREADS, smem));
+        if (per_sm < 1) per_sm = 1;
+        const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * per_sm);
+        CU(cudaEventRecord(p->ev0, p->stream));
+        k_actdist<<<(int)grid, AD_THREADS, smem, p->stream>>>(p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, p->d_pw.p, p->d_pl.p,
+                                                              (float)contact_range, p->d_dist.p, p->d_prob.p, p->d_valid.p);
     }
-    CU(cudaFuncSetAttribute(k_actdist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 1;
-    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_actdist, AD_THREADS, smem));
-    if (per_sm < 1) per_sm = 1;
-    const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * per_sm);
-    CU(cudaEventRecord(p->ev0, p->stream));
-    k_actdist<<<(int)grid, AD_THREADS, smem, p->stream>>>(p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, p->d_pw.p, p->d_pl.p,
-                                                          (float)contact_range, p->d_dist.p, p->d_prob.p, p->d_valid.p);
     CU(cudaGetLastError());
     CU(cudaEventRecord(p->ev1, p->stream));
     CU(cudaEventSynchronize(p->ev1));
