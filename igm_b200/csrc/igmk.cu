@@ -932,3 +932,118 @@ extern "C" int igmk_pop_assign(igmk_pop_t* p, int64_t n_rows, const int32_t* row
     if (int rc = igmk_pop_assign_launch(p)) return rc;
     return igmk_pop_assign_collect(p, bits);
 }
+
+// =========================================================================================
+// Single point for callers that must not allocate (see include/igmk.h).
+//
+// The regular igmk_single_point keeps its neighbour table, neighbour counts and the coordinates of
+// the last neighbour build in cudaMalloc'ed buffers that grow with the batch.  This variant runs the
+// same device code for ONE structure with that scratch in a fixed array that is part of the loaded
+// module, so nothing is allocated, freed or resized at call time.
+namespace {
+
+constexpr int NOALLOC_NL_WIDTH = 96;
+constexpr size_t NOALLOC_NL_BYTES = (size_t)IGMK_NOALLOC_MAX_ATOMS * NOALLOC_NL_WIDTH * sizeof(uint16_t);
+constexpr size_t NOALLOC_CNT_BYTES = ((size_t)IGMK_NOALLOC_MAX_ATOMS * sizeof(uint16_t) + 255) / 256 * 256;
+constexpr size_t NOALLOC_BUILD_BYTES = (size_t)IGMK_NOALLOC_MAX_ATOMS * 3 * sizeof(double);
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_NL_BYTES + NOALLOC_CNT_BYTES + NOALLOC_BUILD_BYTES;
+
+// ~0.72 MB held by every GPU that loads the library, until the process exits.  In host code this
+// name is only a handle for cudaGetSymbolAddress -- it is NOT a device address.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};   // per device: device address of the array above
+
+struct NoallocArgs {
+    StructDesc desc;
+    const float4* xyzr; const uint8_t* kind; const uint32_t* envmask;
+    const int32_t* bond_ptr; const uint32_t* bond_items; const double2* btype;
+    unsigned char* scratch;
+    double* forces; double* energies; int32_t* status;
+    double ev_scale, env_scale, bond_pref;
+};
+
+__global__ void __launch_bounds__(MD_THREADS, 1)
+k_single_point_noalloc(const __grid_constant__ NoallocArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    typedef double T;
+    const StructDesc* d = &a.desc;
+    Batch B;
+    B.n_struct = 1; B.max_atoms = d->n_atoms; B.desc = d;
+    B.xyzr = nullptr; B.kind = a.kind; B.envmask = a.envmask;
+    B.bond_ptr = a.bond_ptr; B.bond_items = a.bond_items; B.btype_f = nullptr; B.btype_d = a.btype;
+    B.nl = (uint16_t*)a.scratch; B.nl_width = NOALLOC_NL_WIDTH;
+    B.nl_cnt = (uint16_t*)(a.scratch + NOALLOC_NL_BYTES);
+    B.xd = nullptr; B.fd = nullptr; B.work = nullptr; B.res = nullptr; B.flags = nullptr;
+    Ctx<T> c;
+    ctx_carve<T>(c, smem, d->n_atoms, false, (T*)(a.scratch + NOALLOC_NL_BYTES + NOALLOC_CNT_BYTES));
+    ctx_bind(c, B, d);
+    c.set_stage(a.ev_scale, a.env_scale);
+    c.bond_pref = a.bond_pref;
+    for (int i = threadIdx.x; i < c.n; i += blockDim.x) {
+        const float4 p = a.xyzr[i];
+        double4 q; q.x = p.x; q.y = p.y; q.z = p.z; q.w = p.w;
+        c.x[i] = q;
+    }
+    __syncthreads();
+    c.rebuild();               // rewrites every neighbour row / count / build coordinate it later reads
+    T e[10];
+    c.template forces<true>(e);
+    for (int i = threadIdx.x; i < c.n; i += blockDim.x) {
+        a.forces[3 * i] = c.fx[i]; a.forces[3 * i + 1] = c.fy[i]; a.forces[3 * i + 2] = c.fz[i];
+    }
+    if (threadIdx.x == 0) {
+        double tot = e[0] + e[1];
+        for (int k = 0; k < IGMK_MAX_ENVELOPES; k++) {
+            a.energies[3 + k] = k < d->n_env ? e[2 + k] : 0.0;
+            if (k < d->n_env) tot += e[2 + k];
+        }
+        a.energies[0] = tot; a.energies[1] = e[0]; a.energies[2] = e[1];
+        *a.status = c.overflow ? 1 : (isfinite(tot) ? 0 : 2);
+    }
+}
+
+}  // namespace
+
+extern "C" int igmk_single_point_noalloc(int device, void* stream, int32_t n_atoms,
+                                         const float* d_xyzr, const uint8_t* d_kind, const uint32_t* d_envmask,
+                                         const int32_t* d_bond_ptr, const uint32_t* d_bond_items, const double* d_btype,
+                                         int32_t n_env, const double* env_abck, double evfactor, float max_radius,
+                                         double ev_scale, double env_scale, double bond_prefactor,
+                                         double* d_forces, double* d_energies, int32_t* d_status)
+{
+    if (!d_xyzr || !d_kind || !d_envmask || !d_bond_ptr || !d_bond_items || !d_btype || !d_forces || !d_energies || !d_status)
+        return fail("igmk_single_point_noalloc: NULL argument");
+    if (n_atoms < 1 || n_atoms > IGMK_NOALLOC_MAX_ATOMS) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "igmk_single_point_noalloc: %d atoms; the built-in scratch array holds at most %d "
+                 "(use igmk_single_point, which allocates what it needs)", n_atoms, IGMK_NOALLOC_MAX_ATOMS);
+        return fail(msg);
+    }
+    if (n_env < 0 || n_env > IGMK_MAX_ENVELOPES || (n_env > 0 && !env_abck)) return fail("igmk_single_point_noalloc: bad envelope arguments");
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail("igmk_single_point_noalloc: bad device ordinal");
+    CU(cudaSetDevice(device));
+    const size_t sm = ctx_smem_bytes<double>(n_atoms, false);
+    if (!g_noalloc_ptr[device]) {
+        // one-time set-up on this device (with it current): resolve the array's device address
+        void* p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        CU(cudaFuncSetAttribute(k_single_point_noalloc, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)ctx_smem_bytes<double>(IGMK_NOALLOC_MAX_ATOMS, false)));
+        g_noalloc_ptr[device] = (unsigned char*)p;
+    }
+    NoallocArgs a;
+    memset(&a, 0, sizeof a);
+    a.desc.n_atoms = n_atoms; a.desc.n_env = n_env; a.desc.evfactor = evfactor; a.desc.maxrad = max_radius;
+    for (int e = 0; e < n_env; e++) for (int k = 0; k < 4; k++) a.desc.env[e][k] = env_abck[4 * e + k];
+    a.xyzr = (const float4*)d_xyzr; a.kind = d_kind; a.envmask = d_envmask;
+    a.bond_ptr = d_bond_ptr; a.bond_items = d_bond_items; a.btype = (const double2*)d_btype;
+    a.scratch = g_noalloc_ptr[device];
+    a.forces = d_forces; a.energies = d_energies; a.status = d_status;
+    a.ev_scale = ev_scale; a.env_scale = env_scale; a.bond_pref = bond_prefactor;
+    k_single_point_noalloc<<<1, MD_THREADS, sm, (cudaStream_t)stream>>>(a);
+    CU(cudaGetLastError());
+    return 0;
+}

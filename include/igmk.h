@@ -147,6 +147,41 @@ int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out /* [n_atoms]
  * upload moved host -> device (any pointer may be NULL) */
 int igmk_last_timings(igmk_handle_t* h, double* md_ms, double* cg_ms, int64_t* h2d_bytes);
 
+/*
+ * igmk_single_point_noalloc -- no counterpart in the reference; added for hosts that are not
+ * allowed to touch the CUDA allocator: a service that grabbed one arena at start-up and runs with
+ * allocation disabled afterwards, a caller inside a latency-critical loop where an implicit
+ * device synchronisation from cudaMalloc/cudaFree is unacceptable, or code running where the
+ * allocator may fail because another tenant filled the card.  It evaluates energies and forces of
+ * ONE structure (the `run 0` of igmk_single_point, double precision) and calls no cudaMalloc,
+ * cudaFree or other allocating routine: the neighbour table the kernel needs as scratch lives in a
+ * fixed ~0.72 MB array inside the library image, which every GPU that loads the library keeps until
+ * the process exits.  Hence the size limit: n_atoms <= IGMK_NOALLOC_MAX_ATOMS, at most 96
+ * neighbours within the list cutoff per bead (status 1 otherwise); larger problems are refused with
+ * an error -- use igmk_single_point for those.
+ *
+ * All d_* pointers are DEVICE pointers owned by the caller, in the layouts igmk_submit builds:
+ *   d_xyzr [n][4] x,y,z,radius float32; d_kind [n] IGMK_KIND_*; d_envmask [n] bit e = member of
+ *   envelope e; d_bond_ptr [n+1] + d_bond_items: every bond listed under both of its atoms as
+ *   partner | type << 16; d_btype [n_types][2] = (r0, k) with k < 0 for a lower bound.
+ *   env_abck is a HOST array [n_env][4]; max_radius = largest bead radius.
+ * Outputs (device): d_forces [n][3], d_energies [3 + IGMK_MAX_ENVELOPES] = total, pair, bond,
+ * envelope 0.., d_status: 0 ok, 1 neighbour table full, 2 non-finite energy.
+ * The launch is asynchronous on `stream` (a cudaStream_t, NULL = default stream); read the outputs
+ * after synchronising it.  The first call on each device also looks up the scratch array's address
+ * and raises the kernel's shared-memory limit -- make that first call before starting any stream
+ * capture.  All calls on a device share the one scratch array: nothing in it has to start at zero
+ * (each call rewrites every entry it reads), but two calls running on the GPU at the same time
+ * would overwrite each other's neighbour table -- keep them on one stream or order them yourself.
+ */
+#define IGMK_NOALLOC_MAX_ATOMS 3328
+int igmk_single_point_noalloc(int device, void* stream, int32_t n_atoms,
+                              const float* d_xyzr, const uint8_t* d_kind, const uint32_t* d_envmask,
+                              const int32_t* d_bond_ptr, const uint32_t* d_bond_items, const double* d_btype,
+                              int32_t n_env, const double* env_abck, double evfactor, float max_radius,
+                              double ev_scale, double env_scale, double bond_prefactor,
+                              double* d_forces, double* d_energies, int32_t* d_status);
+
 /* ---- A-step: device-resident population ------------------------------------------ */
 /*
  * Population geometry.  `crd` uses the .hss layout coordinates[bead][struct][3]
