@@ -321,14 +321,16 @@ static void md2_build(igmk_handle* h)
             eoff[gi] = (int32_t)(h->md2_ell_items.size() - base);
             h->md2_ell_items.resize(h->md2_ell_items.size() + (size_t)cols * 32, 0u);
             uint32_t* blk = h->md2_ell_items.data() + base + eoff[gi];
+            // layout [batch of 4 columns][lane][4]: one 16-byte load per lane and batch
+            auto at = [&](int c, int l) -> uint32_t& { return blk[((c >> 2) * 32 + l) * 4 + (c & 3)]; };
             for (int l = 0; l < 32; l++)               // padding = bond of type 0 to oneself: r = 0, no force
-                for (int c = 0; c < cols; c++) blk[c * 32 + l] = (uint32_t)(k * MD2_T + w * 32 + l);
+                for (int c = 0; c < cols; c++) at(c, l) = (uint32_t)(k * MD2_T + w * 32 + l);
             for (int l = 0; l < 32; l++) {
                 const int a = perm[k * MD2_T + w * 32 + l];
                 if (a == MD2_NONE) continue;
                 for (int c = 0; c < bp[a + 1] - bp[a]; c++) {
                     const uint32_t it = bi[bp[a] + c];
-                    blk[c * 32 + l] = (uint32_t)pos[it & 0xffffu] | (it & 0xffff0000u);
+                    at(c, l) = (uint32_t)pos[it & 0xffffu] | (it & 0xffff0000u);
                 }
             }
         }
@@ -453,8 +455,20 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
     Md2View V;
     V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
     V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw;
+    V.prof = nullptr;
+    const bool prof = getenv("IGMK_PROF") != nullptr;
+    if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 4 * sizeof(long long))); CU(cudaMemset(V.prof, 0, (size_t)ns * 4 * sizeof(long long))); }
     k_md2<K><<<ns, MD2_T, sm>>>(B, V, h->d_md2_desc, P);
     CU(cudaGetLastError());
+    if (prof) {                  // diagnostics only: per-phase SM cycles of thread 0, averaged over the structures
+        std::vector<long long> t((size_t)ns * 4);
+        CU(cudaMemcpy(t.data(), V.prof, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+        cudaFree(V.prof);
+        double a[4] = {0, 0, 0, 0};
+        for (int s = 0; s < ns; s++) for (int k = 0; k < 4; k++) a[k] += (double)t[4 * (size_t)s + k] / ns;
+        fprintf(stderr, "[igmk prof] k_md2 mean cycles per structure: forces %.3g, rebuild-search %.3g, rebuilds %.3g, n_rebuilds %.1f\n",
+                a[0], a[1], a[2], a[3]);
+    }
     return 0;
 }
 

@@ -27,6 +27,7 @@ struct Md2View {
     const uint32_t* ell_items; // sliced-ELL bond items
     uint16_t*       nl;        // [sum np * nl_width] column-major per structure
     int32_t         nl_width;
+    long long*      prof;      // optional [n_struct][4] SM cycles: force loops, integration, rebuilds, total (IGMK_PROF=1)
 };
 
 struct Md2Desc {               // per structure
@@ -54,6 +55,7 @@ __host__ __device__ inline size_t md2_smem_bytes(int K)
 {
     const size_t np = (size_t)K * MD2_T;
     size_t b = np * 16;                       // x
+    b += np * 16;                             // positions in cell order (neighbour search)
     b += np * 12;                             // build coordinates
     b += ((size_t)MAX_CELLS + 1) * 4;         // cell_start
     b += np * 2 * 2;                          // cell_atoms, cell_of
@@ -74,7 +76,8 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     const int n = d->n_atoms;
 
     float4* x = (float4*)smem;
-    float* xbx = (float*)(x + np); float* xby = xbx + np; float* xbz = xby + np;
+    float4* xsort = x + np;
+    float* xbx = (float*)(xsort + np); float* xby = xbx + np; float* xbz = xby + np;
     uint32_t* cell_start = (uint32_t*)(xbz + np);
     uint16_t* cell_atoms = (uint16_t*)(cell_start + MAX_CELLS + 1);
     uint16_t* cell_of = cell_atoms + np;
@@ -121,6 +124,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     const float bond_pref2 = 2.f * (float)pr.bond_prefactor;
     float ev_c = -1.f;                 // evfactor * stage scale / pi  (force prefactor / rc), < 0: no sterics
     int n_rebuild = 0, overflow = 0;
+    long long t_search = 0;
     __syncthreads();
 
     // ------------------------------------------------------------------------------------
@@ -239,44 +243,64 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < K; k++) xbx[k * MD2_T + tid] = x[k * MD2_T + tid].x;
-        // neighbour search: my rows
+        // positions in cell order: the search below walks them contiguously
+        const long long ts0 = clock64();
+        const int nbead = cell_start[ncell];
+        for (int s0 = tid; s0 < nbead; s0 += MD2_T) xsort[s0] = x[cell_atoms[s0]];
+        __syncthreads();
+        // neighbour search.  Thread t takes the t-th bead IN CELL ORDER (not one of its own atoms), so the
+        // lanes of a warp sit in the same or adjacent cells, scan nearly the same ranges (little divergence,
+        // broadcast shared-memory reads) and need no index indirection until a candidate is accepted.
+        // Row layout: nl[batch][position][4] -- the force loop fetches 4 neighbours with one 8-byte load.
         int ovf = 0;
-#pragma unroll
-        for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
-            int cnt = 0;
+        for (int s0 = tid; s0 < nbead; s0 += MD2_T) {
+            const int p = cell_atoms[s0];
+            const float4 q = xsort[s0];
             const int c = cell_of[p];
-            if (c != MD2_NONE) {
-                const float4 q = x[p];
-                const int cx = c % dim[0], cy = (c / dim[0]) % dim[1], cz = c / (dim[0] * dim[1]);
-                const int ax0 = max(cx - 1, 0), ax1 = min(cx + 1, dim[0] - 1);
-                uint16_t* row = nl + p;
-                for (int dz = -1; dz <= 1; dz++) {
-                    const int az = cz + dz;
-                    if (az < 0 || az >= dim[2]) continue;
-                    for (int dy = -1; dy <= 1; dy++) {
-                        const int ay = cy + dy;
-                        if (ay < 0 || ay >= dim[1]) continue;
-                        const int cb = (az * dim[1] + ay) * dim[0];
-                        const int b = cell_start[cb + ax0], e = cell_start[cb + ax1 + 1];   // 3 cells, contiguous
-                        for (int s = b; s < e; s++) {
-                            const int j = cell_atoms[s];
-                            const float4 pj = x[j];
+            const int cx = c % dim[0], cy = (c / dim[0]) % dim[1], cz = c / (dim[0] * dim[1]);
+            const int ax0 = max(cx - 1, 0), ax1 = min(cx + 1, dim[0] - 1);
+            uint16_t* row = nl + ((size_t)p << 2);
+            int cnt = 0;
+            for (int dz = -1; dz <= 1; dz++) {
+                const int az = cz + dz;
+                if (az < 0 || az >= dim[2]) continue;
+                for (int dy = -1; dy <= 1; dy++) {
+                    const int ay = cy + dy;
+                    if (ay < 0 || ay >= dim[1]) continue;
+                    const int cb = (az * dim[1] + ay) * dim[0];
+                    const int b = cell_start[cb + ax0], e = cell_start[cb + ax1 + 1];   // 3 cells, contiguous
+                    for (int s1 = b; s1 < e; s1 += 4) {
+                        bool hit[4];
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            const int s2 = min(s1 + u, e - 1);
+                            const float4 pj = xsort[s2];
                             const float ddx = q.x - pj.x, ddy = q.y - pj.y, ddz = q.z - pj.z;
                             const float rl = q.w + pj.w + skin;
-                            if (j != p && ddx * ddx + ddy * ddy + ddz * ddz < rl * rl) {
-                                if (cnt < nlw) row[(size_t)cnt * np] = (uint16_t)j;
+                            hit[u] = (s1 + u < e) && (s2 != s0) && (ddx * ddx + ddy * ddy + ddz * ddz < rl * rl);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            if (hit[u]) {
+                                if (cnt < nlw) row[(((size_t)(cnt >> 2) * np) << 2) + (cnt & 3)] = cell_atoms[s1 + u];
                                 cnt++;
                             }
                         }
                     }
                 }
-                if (cnt > nlw) { ovf = 1; cnt = nlw; }
-                for (int c = cnt; c & 3; c++) row[(size_t)c * np] = (uint16_t)p;     // self padding (nlw % 4 == 0)
             }
-            ncnt[k] = cnt;
+            if (cnt > nlw) { ovf = 1; cnt = nlw; }
+            for (int cc = cnt; cc & 3; cc++) row[(((size_t)(cc >> 2) * np) << 2) + (cc & 3)] = (uint16_t)p;   // self padding
+            cell_of[p] = (uint16_t)cnt;            // hand the row length to the atom's owner
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const uint16_t c = cell_of[k * MD2_T + tid];
+            ncnt[k] = c == MD2_NONE ? 0 : (int)c;
         }
         overflow |= __syncthreads_or(ovf);
+        t_search += clock64() - ts0;
         n_rebuild++;
     };
 
@@ -293,12 +317,11 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             float ax = 0.f, ay = 0.f, az = 0.f;
             // pair_style soft: F = A pi/rc sin(pi r/rc) r_hat, A = rc^2 ev/pi^2  =>  F/r = ev_c rc sin(pi r/rc) / r
             if (ev_c >= 0.f) {
-                const uint16_t* col = nl + p;
-                const int cnt = ncnt[k];
-                for (int q = 0; q < cnt; q += 4) {
-                    uint32_t j[4];
-#pragma unroll
-                    for (int u = 0; u < 4; u++) j[u] = col[(size_t)(q + u) * np];
+                const uint2* col = (const uint2*)nl + p;
+                const int nb4 = (ncnt[k] + 3) >> 2;
+                for (int q = 0; q < nb4; q++) {
+                    const uint2 w = col[(size_t)q * np];
+                    const uint32_t j[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
                         const float4 pj = lds_f4(xs + (j[u] << 4));
@@ -315,12 +338,13 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             }
             // harmonic upper / lower bounds: F = -2 pref k (r - r0) r_hat when violated
             {
-                const uint32_t* it = eitems + boff[k] + lane;
-                const int nc = bcols[k];
-                for (int c = 0; c < nc; c += 4) {
-                    uint32_t v[4];
-#pragma unroll
-                    for (int u = 0; u < 4; u++) v[u] = it[(c + u) * 32];
+                const uint4* it = (const uint4*)(eitems + boff[k]) + lane;     // [batch][lane][4 items]
+                const int nb4 = bcols[k] >> 2;
+                uint4 nxt = nb4 > 0 ? it[0] : make_uint4(0, 0, 0, 0);
+                for (int c = 0; c < nb4; c++) {
+                    const uint4 cur = nxt;
+                    if (c + 1 < nb4) nxt = it[(c + 1) * 32];                  // next batch in flight while this one is used
+                    const uint32_t v[4] = {cur.x, cur.y, cur.z, cur.w};
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
                         const uint32_t ti = v[u] >> 16;
@@ -355,7 +379,10 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     };
 
     // ------------------------------------------------------------------------------------
+    long long t_force = 0, t_integ = 0, t_build = 0;
+    const long long t_begin = clock64();
     rebuild();
+    t_build += clock64() - t_begin;
     const float dt = (float)pr.timestep, dtf = 0.5f * dt;
     const float dof = 3.f * (float)d->n_nonfixed - 3.f;
     float last_temp = 0.f;
@@ -406,8 +433,10 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             forces();                                   // run setup
             float scale = 1.f;
             for (int step = 0; step <= nsteps; step++) {
+                const long long tc0 = clock64();
                 if (step > 0) {
                     forces();
+                    t_force += clock64() - tc0;
                     float ke = 0.f;
 #pragma unroll
                     for (int k = 0; k < K; k++) {       // second half kick (frozen/empty: f = v = 0)
@@ -447,7 +476,10 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                         need |= (ddx * ddx + ddy * ddy + ddz * ddz > lim);
                     }
                 }
-                if (__syncthreads_or(need)) rebuild();
+                const bool stale = __syncthreads_or(need);
+                const long long tc1 = clock64();
+                if (stale) { rebuild(); t_build += clock64() - tc1; }
+                t_integ += tc1 - tc0;
             }
         }
     }
@@ -469,6 +501,10 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         r->temperature = dof_all > 0 ? (double)last_temp * (double)dof / dof_all : 0.0;
         r->n_rebuilds = n_rebuild;
         B.flags[blockIdx.x] = (overflow ? 1 : 0) | (bad ? 2 : 0);
+        if (V.prof) {
+            long long* o = V.prof + 4 * (size_t)blockIdx.x;
+            o[0] = t_force; o[1] = t_search; o[2] = t_build; o[3] = n_rebuild;
+        }
     }
 }
 
