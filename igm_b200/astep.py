@@ -165,6 +165,51 @@ class Population(object):
         return self.assign_collect()
 
 
+def _damid_actdist(self, loc, pwish, plast, contact_range=0.05, shape="sphere", nucleus_param=5000.0):
+    """get_damid_actdist (igm/steps/DamidActivationDistanceStep.py:285-356) for a batch of loci
+    -> (bead i4, dist f4, prob f4) exactly as the rows land in damid_actdist.hdf5."""
+    lc = np.ascontiguousarray(loc, dtype=np.int32)
+    pw = np.ascontiguousarray(pwish, dtype=np.float64)
+    pl = np.ascontiguousarray(plast, dtype=np.float64)
+    if not (lc.size == pw.size == pl.size):
+        raise ValueError("locus arrays differ in length")
+    if shape not in ("sphere", "ellipsoid"):
+        raise NotImplementedError("shape %s has not been implemented yet." % shape)      # DamidActivationDistanceStep.py:183
+    param = np.ascontiguousarray(np.atleast_1d(nucleus_param), dtype=np.float64)
+    if param.size != (1 if shape == "sphere" else 3):
+        raise ValueError("nucleus_param does not match the shape")
+    cap = max(1, lc.size * self.max_copies)
+    bead = np.empty(cap, dtype=np.int32)
+    dist = np.empty(cap, dtype=np.float32)
+    prob = np.empty(cap, dtype=np.float32)
+    n = C.c_int64(0)
+    _abi.check(self._lib.igmk_pop_damid_actdist(
+        self._p, lc.size, lc.ctypes.data_as(_abi.c_i32p), pw.ctypes.data_as(_abi.c_f64p), pl.ctypes.data_as(_abi.c_f64p),
+        float(contact_range), 0 if shape == "sphere" else 1, param.ctypes.data_as(_abi.c_f64p), cap,
+        bead.ctypes.data_as(_abi.c_i32p), dist.ctypes.data_as(_abi.c_f32p), prob.ctypes.data_as(_abi.c_f32p), C.byref(n)),
+        "igmk_pop_damid_actdist")
+    return bead[:n.value], dist[:n.value], prob[:n.value]
+
+
+def _damid_assign(self, bead, dist, contact_range=0.05, semiaxes=(5000.0, 5000.0, 5000.0)):
+    """Damid._apply_envelope's predicate (igm/restraints/damid.py:116-130) for all structures:
+    bit s of row r set <=> bead[r] of structure s joins the lamina envelope."""
+    b = np.ascontiguousarray(bead, dtype=np.int32)
+    d = np.ascontiguousarray(dist, dtype=np.float32)
+    if b.size != d.size:
+        raise ValueError("row arrays differ in length")
+    abc = np.ascontiguousarray(semiaxes, dtype=np.float64)
+    bits = np.zeros((b.size, (self.n_struct + 31) // 32), dtype=np.uint32)
+    _abi.check(self._lib.igmk_pop_damid_assign(self._p, b.size, b.ctypes.data_as(_abi.c_i32p), d.ctypes.data_as(_abi.c_f32p),
+                                               float(contact_range), abc.ctypes.data_as(_abi.c_f64p),
+                                               bits.ctypes.data_as(_abi.c_u32p)), "igmk_pop_damid_assign")
+    return bits
+
+
+Population.damid_actdist = _damid_actdist
+Population.damid_assign = _damid_assign
+
+
 def unpack_bits(bits, n_struct):
     """uint32 [n_rows][nw] -> bool [n_rows][n_struct]"""
     b = (bits[:, :, None] >> np.arange(32, dtype=np.uint32)) & np.uint32(1)

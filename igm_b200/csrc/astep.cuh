@@ -29,18 +29,19 @@ struct PopView {
 // half-to-even to 4 decimals (glibc printf is exact), and parsing it gives the double nearest to
 // r / 10^4 -- which is what IEEE division of the two exactly representable numbers returns.
 // Then np.genfromtxt casts that double to float32.
-__device__ __forceinline__ float text_roundtrip4(double x)
+__device__ __forceinline__ float text_roundtrip(double x, double scale /* 10^ndec, exact */)
 {
-    const double p = x * 1.0e4;                       // rounded product
-    const double err = fma(x, 1.0e4, -p);             // exact residual: x*1e4 = p + err
+    const double p = x * scale;                       // rounded product
+    const double err = fma(x, scale, -p);             // exact residual: x*scale = p + err
     double r = rint(p);                               // half-to-even on p
     const double fl = floor(p);
     if (p - fl == 0.5) {                              // p is an exact tie: the residual decides
         if (err > 0.0) r = fl + 1.0;
         else if (err < 0.0) r = fl;
     }
-    return (float)(r / 1.0e4);
+    return (float)(r / scale);
 }
+__device__ __forceinline__ float text_roundtrip4(double x) { return text_roundtrip(x, 1.0e4); }
 
 // order-preserving key for non-negative floats is the bit pattern itself
 __device__ __forceinline__ uint32_t fkey(float v) { return __float_as_uint(v); }
@@ -348,6 +349,120 @@ k_assign(PopView P, int64_t n_rows, const int32_t* __restrict__ row, const int32
                 const double acc = __dadd_rn(__dadd_rn((double)__fmul_rn(dx, dx), (double)__fmul_rn(dy, dy)),
                                              (double)__fmul_rn(dz, dz));
                 hit = __fsqrt_rn(__double2float_rn(acc)) <= d;
+            }
+            const uint32_t b = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) bits[r * nw + w] = b;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// DamID (lamina) A-step.  k_damid_actdist restates get_damid_actdist
+// (igm/steps/DamidActivationDistanceStep.py:285-356): per locus the normalised squared distance to
+// the shrunken envelope of every copy in every structure -- float32 squares, then float64
+// arithmetic exactly as numpy promotes it (snormsq_sphere :35-54: float32 sum (x2+y2)+z2 divided by
+// the float64 (R-r)^2; snormsq_ellipse :58-76: each float32 square divided by a float64 (axis-r)^2,
+// summed left to right) -- the count of values >= 1, the two cleanProbability corrections, the
+// o-th LARGEST value (descending sort, :335) and the "%10.2f" / "%.5f" text round trip (:31).
+// One CTA per locus; the values live in shared memory as float64.
+// The denominators (axis*(1-contact_range) - r)**2 come from the host, which evaluates them with
+// libm pow(x, 2.0) like numpy's scalar `**` does (it differs from x*x in ~0.1 % of the cases).
+
+__global__ void __launch_bounds__(AD_THREADS)
+k_damid_actdist(PopView P, int64_t n_loci, const int32_t* __restrict__ loc, const double* __restrict__ pwish,
+                const double* __restrict__ plast, const double* __restrict__ den /* [n_loci][3] */, int ellipsoid,
+                float* __restrict__ out_dist, float* __restrict__ out_prob)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    unsigned long long* key = (unsigned long long*)smem_raw;      // non-negative doubles order like their bit patterns
+    __shared__ int s_red[2][AD_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int S = P.n_struct;
+    for (int64_t q = blockIdx.x; q < n_loci; q += gridDim.x) {
+        const int h = loc[q];
+        const int o0 = P.copy_off[h], nc = P.copy_off[h + 1] - o0;
+        const int total = nc * S;
+        const double a2 = den[3 * q], b2 = den[3 * q + 1], c2 = den[3 * q + 2];
+        int cnt = 0;
+        for (int c = 0; c < nc; c++) {
+            const float* x = P.crd + (size_t)P.copy_beads[o0 + c] * S * 3;
+            for (int s = tid; s < S; s += AD_THREADS) {
+                const float xx = __fmul_rn(x[3 * s], x[3 * s]), yy = __fmul_rn(x[3 * s + 1], x[3 * s + 1]),
+                            zz = __fmul_rn(x[3 * s + 2], x[3 * s + 2]);
+                double v;
+                if (ellipsoid) v = __dadd_rn(__dadd_rn(__ddiv_rn((double)xx, a2), __ddiv_rn((double)yy, b2)), __ddiv_rn((double)zz, c2));
+                else v = __ddiv_rn((double)__fadd_rn(__fadd_rn(xx, yy), zz), a2);
+                key[c * S + s] = (unsigned long long)__double_as_longlong(v);
+                cnt += (v >= 1.0);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0) s_red[0][warp] = cnt;
+        __syncthreads();
+        cnt = 0;
+#pragma unroll
+        for (int w = 0; w < AD_THREADS / 32; w++) cnt += s_red[0][w];
+        const double pnow = (double)cnt / (double)S / (double)nc;                     // :339
+        const double pl = plast[q], pw = pwish[q];
+        double t = pl < 1.0 ? (pnow - pl) / (1.0 - pl) : pnow; t = t > 0.0 ? t : 0.0;
+        double p = t < 1.0 ? (pw - t) / (1.0 - t) : pw; p = p > 0.0 ? p : 0.0;
+        double ad = 2.0;                                                              // :347
+        if (p > 0.0) {
+            long long o = (long long)rint((double)total * p);                         // :350-351
+            if (o > (long long)total - 1) o = total - 1;
+            // o-th largest == (total-1-o)-th smallest; bitwise descent over the 64-bit keys
+            unsigned long long prefix = 0ull;
+            unsigned int k = (unsigned int)(total - 1 - o);
+            int par = 1;
+            for (int bit = 62; bit >= 0; bit--) {                 // bit 63 (sign) is clear in every key
+                const unsigned long long hmask = ~0ull << (bit + 1);
+                int c0 = 0;
+                for (int i = tid; i < total; i += AD_THREADS) {
+                    const unsigned long long kk = key[i];
+                    c0 += ((kk & hmask) == prefix) && !((kk >> bit) & 1ull);
+                }
+#pragma unroll
+                for (int o2 = 16; o2 > 0; o2 >>= 1) c0 += __shfl_xor_sync(0xffffffffu, c0, o2);
+                if (lane == 0) s_red[par][warp] = c0;
+                __syncthreads();
+                c0 = 0;
+#pragma unroll
+                for (int w = 0; w < AD_THREADS / 32; w++) c0 += s_red[par][w];
+                par ^= 1;
+                if (k >= (unsigned int)c0) { k -= (unsigned int)c0; prefix |= (1ull << bit); }
+            }
+            ad = sqrt(__longlong_as_double((long long)prefix));                       // :354
+        }
+        if (tid == 0) {
+            out_dist[q] = text_roundtrip(ad, 1.0e2);
+            out_prob[q] = text_roundtrip(p, 1.0e5);
+        }
+        __syncthreads();
+    }
+}
+
+// Damid._apply_envelope (igm/restraints/damid.py:116-130): bead `loc[r]` of structure s joins the
+// lamina envelope iff snormsq_ellipsoid(pos, abc*cutoff, r) >= d^2, with d^2 squared in float32 and
+// widened, the left side in float64 from float32 squares.  One warp per row; bit matrix like k_assign.
+__global__ void __launch_bounds__(1024)
+k_damid_assign(PopView P, int64_t n_rows, const int32_t* __restrict__ bead, const float* __restrict__ dist,
+               const double* __restrict__ den /* [n_rows][3] */, uint32_t* __restrict__ bits)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int S = P.n_struct, nw = (S + 31) >> 5;
+    for (int64_t r = (int64_t)blockIdx.x * 32 + warp; r < n_rows; r += (int64_t)gridDim.x * 32) {
+        const float* x = P.crd + (size_t)bead[r] * S * 3;
+        const double a2 = den[3 * r], b2 = den[3 * r + 1], c2 = den[3 * r + 2];
+        const double d2 = (double)__fmul_rn(dist[r], dist[r]);
+        for (int w = 0; w < nw; w++) {
+            const int s = w * 32 + lane;
+            bool hit = false;
+            if (s < S) {
+                const float xx = __fmul_rn(x[3 * s], x[3 * s]), yy = __fmul_rn(x[3 * s + 1], x[3 * s + 1]),
+                            zz = __fmul_rn(x[3 * s + 2], x[3 * s + 2]);
+                const double v = __dadd_rn(__dadd_rn(__ddiv_rn((double)xx, a2), __ddiv_rn((double)yy, b2)), __ddiv_rn((double)zz, c2));
+                hit = v >= d2;
             }
             const uint32_t b = __ballot_sync(0xffffffffu, hit);
             if (lane == 0) bits[r * nw + w] = b;

@@ -631,7 +631,8 @@ struct igmk_pop {
     int64_t n_pairs = 0;
     std::vector<int32_t> h_pi, h_pj;
     DevBuf<int32_t> d_pi, d_pj; DevBuf<double> d_pw, d_pl;
-    DevBuf<float> d_dist, d_prob; DevBuf<uint8_t> d_valid;
+    DevBuf<float> d_dist, d_prob; DevBuf<uint8_t> d_valid; DevBuf<double> d_den;
+    std::vector<float> radii;
     bool actdist_done = false;
     // staged actdist rows (assignment)
     int64_t n_rows = 0;
@@ -650,7 +651,7 @@ struct igmk_pop {
         if (own_crd) cudaFree(d_crd);
         cudaFree(d_radii); cudaFree(d_chrom); cudaFree(d_copy_off); cudaFree(d_copy_beads);
         d_pi.release(); d_pj.release(); d_pw.release(); d_pl.release(); d_dist.release(); d_prob.release();
-        d_valid.release(); d_row.release(); d_col.release(); d_rdist.release(); d_bits.release();
+        d_valid.release(); d_den.release(); d_row.release(); d_col.release(); d_rdist.release(); d_bits.release();
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -685,6 +686,7 @@ extern "C" int igmk_pop_create(int device, int32_t n_bead, int32_t n_struct, int
     p->copy_off.assign(copy_off, copy_off + n_hap + 1);
     p->copy_beads.assign(copy_beads, copy_beads + copy_off[n_hap]);
     p->chrom.assign(chrom_bead, chrom_bead + n_bead);
+    p->radii.assign(radii, radii + n_bead);
     CU(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&p->ev0)); CU(cudaEventCreate(&p->ev1));
     CU(cudaMalloc((void**)&p->d_crd, (size_t)n_bead * n_struct * 3 * sizeof(float)));
@@ -884,6 +886,97 @@ extern "C" int igmk_pop_contact_freq(igmk_pop_t* p, int64_t n_pairs, const int32
     CU(cudaStreamSynchronize(p->stream));
     CU(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
     p->n_pairs = 0; p->actdist_done = false;
+    return 0;
+}
+
+// ---- DamID (lamina) A-step -----------------------------------------------------------------
+static void damid_denominators(const igmk_pop* p, int64_t n, const int32_t* bead_of, double contact_range, int ellipsoid,
+                               const double* nucleus_param, const std::vector<float>& radii, std::vector<double>& den)
+{
+    den.resize((size_t)n * 3);
+    for (int64_t q = 0; q < n; q++) {
+        const double r = (double)radii[bead_of[q]];
+        for (int k = 0; k < 3; k++) {
+            const double axis = nucleus_param[ellipsoid ? k : 0] * (1 - contact_range);
+            den[3 * q + k] = pow(axis - r, 2.0);          // numpy scalar `**2` == libm pow
+        }
+    }
+    (void)p;
+}
+
+extern "C" int igmk_pop_damid_actdist(igmk_pop_t* p, int64_t n_loci, const int32_t* loc, const double* pwish, const double* plast,
+                                      double contact_range, int32_t ellipsoid, const double* nucleus_param,
+                                      int64_t max_rows, int32_t* row_bead, float* dist, float* prob, int64_t* n_rows_out)
+{
+    if (!p || !n_rows_out) return fail("igmk_pop_damid_actdist: NULL argument");
+    *n_rows_out = 0;
+    if (n_loci == 0) return 0;
+    if (!loc || !pwish || !plast || !nucleus_param || !row_bead || !dist || !prob) return fail("igmk_pop_damid_actdist: NULL argument");
+    for (int64_t q = 0; q < n_loci; q++)
+        if (loc[q] < 0 || loc[q] >= p->n_hap) return fail("igmk_pop_damid_actdist: locus index out of range");
+    CU(cudaSetDevice(p->device));
+    const size_t smem = (size_t)p->max_copies * p->n_struct * sizeof(double);
+    if ((long long)smem + 1024 > (long long)p->smem_optin) return fail("igmk_pop_damid_actdist: population too large for one CTA's shared memory");
+    std::vector<int32_t> bead0((size_t)n_loci);
+    for (int64_t q = 0; q < n_loci; q++) bead0[q] = p->copy_beads[p->copy_off[loc[q]]];
+    std::vector<double> den;
+    damid_denominators(p, n_loci, bead0.data(), contact_range, ellipsoid, nucleus_param, p->radii, den);
+    CU(p->d_pi.reserve(n_loci)); CU(p->d_pw.reserve(n_loci)); CU(p->d_pl.reserve(n_loci));
+    CU(p->d_dist.reserve(n_loci)); CU(p->d_prob.reserve(n_loci)); CU(p->d_den.reserve((size_t)n_loci * 3));
+    CU(cudaMemcpyAsync(p->d_pi.p, loc, n_loci * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_pw.p, pwish, n_loci * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_pl.p, plast, n_loci * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_den.p, den.data(), den.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaFuncSetAttribute(k_damid_actdist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t grid = std::min<int64_t>(n_loci, (int64_t)p->sm_count * 8);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_damid_actdist<<<(int)grid, AD_THREADS, smem, p->stream>>>(p->view(), n_loci, p->d_pi.p, p->d_pw.p, p->d_pl.p, p->d_den.p,
+                                                                 ellipsoid ? 1 : 0, p->d_dist.p, p->d_prob.p);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(p->ev1, p->stream));
+    std::vector<float> hd((size_t)n_loci), hp((size_t)n_loci);
+    CU(cudaMemcpyAsync(hd.data(), p->d_dist.p, n_loci * sizeof(float), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaMemcpyAsync(hp.data(), p->d_prob.p, n_loci * sizeof(float), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    CU(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+    p->n_pairs = 0; p->actdist_done = false;
+    // one row per copy of the locus, always (DamidActivationDistanceStep.py:356)
+    int64_t nr = 0;
+    for (int64_t q = 0; q < n_loci; q++) {
+        const int o0 = p->copy_off[loc[q]], nc = p->copy_off[loc[q] + 1] - o0;
+        if (nr + nc > max_rows) return fail("igmk_pop_damid_actdist: output buffers too small");
+        for (int c = 0; c < nc; c++) { row_bead[nr] = p->copy_beads[o0 + c]; dist[nr] = hd[q]; prob[nr] = hp[q]; nr++; }
+    }
+    *n_rows_out = nr;
+    return 0;
+}
+
+extern "C" int igmk_pop_damid_assign(igmk_pop_t* p, int64_t n_rows, const int32_t* bead, const float* dist,
+                                     double contact_range, const double* semiaxes, uint32_t* bits)
+{
+    if (!p) return fail("igmk_pop_damid_assign: NULL handle");
+    if (n_rows == 0) return 0;
+    if (!bead || !dist || !semiaxes || !bits) return fail("igmk_pop_damid_assign: NULL argument");
+    for (int64_t r = 0; r < n_rows; r++)
+        if (bead[r] < 0 || bead[r] >= p->n_bead) return fail("igmk_pop_damid_assign: bead index out of range");
+    CU(cudaSetDevice(p->device));
+    std::vector<double> den;
+    damid_denominators(p, n_rows, bead, contact_range, 1, semiaxes, p->radii, den);
+    const int nw = (p->n_struct + 31) / 32;
+    CU(p->d_row.reserve(n_rows)); CU(p->d_rdist.reserve(n_rows)); CU(p->d_den.reserve((size_t)n_rows * 3));
+    CU(p->d_bits.reserve((size_t)n_rows * nw));
+    CU(cudaMemcpyAsync(p->d_row.p, bead, n_rows * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_rdist.p, dist, n_rows * sizeof(float), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_den.p, den.data(), den.size() * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+    const int64_t grid = std::min<int64_t>((n_rows + 31) / 32, (int64_t)p->sm_count * 2);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_damid_assign<<<(int)grid, 1024, 0, p->stream>>>(p->view(), n_rows, p->d_row.p, p->d_rdist.p, p->d_den.p, p->d_bits.p);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(p->ev1, p->stream));
+    CU(cudaMemcpyAsync(bits, p->d_bits.p, (size_t)n_rows * nw * sizeof(uint32_t), cudaMemcpyDeviceToHost, p->stream));
+    CU(cudaStreamSynchronize(p->stream));
+    CU(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+    p->n_rows = 0; p->assign_done = false;
     return 0;
 }
 

@@ -254,6 +254,23 @@ int igmk_pop_set_rows(igmk_pop_t* p, int64_t n_rows,
 int igmk_pop_assign_launch(igmk_pop_t* p);
 int igmk_pop_assign_collect(igmk_pop_t* p, uint32_t* bits);
 
+/*
+ * DamID (lamina) A-step.  igmk_pop_damid_actdist = get_damid_actdist
+ * (igm/steps/DamidActivationDistanceStep.py:285-356) for a batch of loci (haploid indices), with
+ * the "%6d %10.2f %.5f" text round trip (:31, :229).  ellipsoid = 0: nucleus_param[0] is the
+ * radius (`sphere`); 1: nucleus_param[0..2] are the semi-axes.  One output row per copy of each
+ * locus, always (p = 0 gives dist 2.0, :347).  igmk_pop_damid_assign = the predicate of
+ * Damid._apply_envelope (igm/restraints/damid.py:116-130) for every (row, structure):
+ * snormsq_ellipsoid(pos, semiaxes*(1-contact_range), r) >= dist^2; bits as in igmk_pop_assign.
+ */
+int igmk_pop_damid_actdist(igmk_pop_t* p, int64_t n_loci, const int32_t* loc,
+                           const double* pwish, const double* plast, double contact_range,
+                           int32_t ellipsoid, const double* nucleus_param,
+                           int64_t max_rows, int32_t* row_bead, float* dist, float* prob,
+                           int64_t* n_rows_out);
+int igmk_pop_damid_assign(igmk_pop_t* p, int64_t n_rows, const int32_t* bead, const float* dist,
+                          double contact_range, const double* semiaxes, uint32_t* bits);
+
 #ifdef __cplusplus
 }
 #endif

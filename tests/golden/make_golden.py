@@ -149,6 +149,45 @@ def main():
     )
     print("astep golden: %d pairs -> %d rows; bonds/struct %s" % (len(pi), len(row), [len(b) for b in bonds]))
 
+    # ---------------- DamID (lamina) A-step through the reference's own functions ------------
+    dads = sys.modules["igm.steps.DamidActivationDistanceStep"]
+    from igm.restraints import Damid
+    from oracle import damid_oracle
+    d_loc = np.sort(rng.choice(nhap, 150, replace=False)).astype(np.int32)
+    d_pw = np.round(np.clip(rng.normal(0.3, 0.25, d_loc.size), 0, 1), 3)
+    d_pl = np.where(rng.random(d_loc.size) < 0.5, 0.0, np.round(rng.random(d_loc.size) * d_pw, 5))
+    d_pl[::41] = 1.0
+    damid = {}
+    for shape, param, cr in (("sphere", 5500.0, 0.05), ("ellipsoid", [5600.0, 5400.0, 5100.0], 0.08)):
+        lines = []
+        for i, pw, pl in zip(d_loc, d_pw, d_pl):
+            for r in dads.get_damid_actdist(int(i), pw, pl, fake, contact_range=cr, shape=shape, nucleus_param=param):
+                lines.append(dads.damid_actdist_fmt_str % r)
+        parsed = np.genfromtxt(io.StringIO("\n".join(lines)), dtype=dads.damid_actdist_shape)
+        o_b, o_d, o_p = damid_oracle.damid_rows(d_loc, d_pw, d_pl, m_crd, m_rad, m_copy_index, cr, shape, param)
+        assert np.array_equal(o_b, parsed["loc"])
+        assert np.array_equal(o_d.view(np.uint32), parsed["dist"].view(np.uint32))
+        assert np.array_equal(o_p.view(np.uint32), parsed["prob"].view(np.uint32))
+        damid[shape + "_bead"], damid[shape + "_dist"], damid[shape + "_prob"] = parsed["loc"], parsed["dist"], parsed["prob"]
+        # the restraint's predicate on a few structures (Damid._apply_envelope)
+        refstub.FAKE_FILES["golden_damid_" + shape] = {"loc": parsed["loc"], "dist": parsed["dist"], "prob": parsed["prob"]}
+        semi = (param,) * 3 if shape == "sphere" else tuple(param)
+        mask = damid_oracle.damid_assign(m_crd, m_rad, parsed["loc"], parsed["dist"], cr, semi)
+        for s in assign_structs:
+            model = Model(uid=s)
+            for b in range(len(m_rad)):
+                model.addParticle(m_crd[b, s], m_rad[b], Particle.NORMAL)
+            model.addRestraint(Damid("golden_damid_" + shape, contact_range=cr, nuclear_radius=param if shape == "sphere" else 0.0,
+                                     shape=shape, semiaxes=semi, k=0.3))
+            got = sorted(int(v) for v in model.forces[-1].particle_ids)
+            assert got == sorted(int(v) for v in parsed["loc"][mask[:, s]]), "DamID predicate differs (struct %d)" % s
+            damid["%s_members_%d" % (shape, s)] = np.array(got, dtype=np.int32)
+    np.savez_compressed(os.path.join(HERE, "damid_golden.npz"), loc=d_loc, pwish=d_pw, plast=d_pl,
+                        sphere_param=np.float64(5500.0), sphere_cr=np.float64(0.05),
+                        ellipsoid_param=np.array([5600.0, 5400.0, 5100.0]), ellipsoid_cr=np.float64(0.08), **damid)
+    print("damid golden: %d loci -> %d rows per shape; members/struct %s" %
+          (d_loc.size, damid["sphere_bead"].size, [damid["sphere_members_%d" % s].size for s in assign_structs]))
+
     # ---------------- reference LAMMPS front end on a small model ----------------------
     from igm.model.kernel import lammps as reflammps
     from igm.model.kernel.lammps_model import LammpsModel
