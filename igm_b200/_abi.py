@@ -206,6 +206,8 @@ _SIGNATURES = {
     "igmk_pop_damid_actdist": (C.c_int, [_vp, C.c_int64, c_i32p, c_f64p, c_f64p, C.c_double, C.c_int32, c_f64p,
                                          C.c_int64, c_i32p, c_f32p, c_f32p, c_i64p]),
     "igmk_pop_damid_assign": (C.c_int, [_vp, C.c_int64, c_i32p, c_f32p, C.c_double, c_f64p, c_u32p]),
+    "igmk_pop_fish_ranks": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p, c_f32p, c_i32p, c_i32p]),
+    "igmk_pop_sprite_rg2": (C.c_int, [_vp, C.c_int32, c_i32p, c_i32p, c_i32p, c_f32p, C.POINTER(C.c_int8), c_i32p]),
     "igmk_pop_set_rows": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p]),
     "igmk_pop_assign_launch": (C.c_int, [_vp]),
     "igmk_pop_assign_collect": (C.c_int, [_vp, c_u32p]),

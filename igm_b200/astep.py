@@ -206,6 +206,49 @@ def _damid_assign(self, bead, dist, contact_range=0.05, semiaxes=(5000.0, 5000.0
     return bits
 
 
+def _fish_ranks(self, hap_i, hap_j=None):
+    """get_pair_dists / get_rad_dists + get_min_max_and_idx (igm/steps/FishAssignmentStep.py:31-88)
+    for a batch: pairs (hap_i, hap_j) or, with hap_j None / negative entries, radial probes.
+    -> (mindists f4 [n][S], maxdists f4 [n][S], idxmin i4 [n][S], idxmax i4 [n][S])"""
+    hi = np.ascontiguousarray(hap_i, dtype=np.int32)
+    hj = np.full(hi.size, -1, dtype=np.int32) if hap_j is None else np.ascontiguousarray(hap_j, dtype=np.int32)
+    if hi.size != hj.size:
+        raise ValueError("locus arrays differ in length")
+    shape = (hi.size, self.n_struct)
+    lo, hi2 = np.empty(shape, dtype=np.float32), np.empty(shape, dtype=np.float32)
+    ra, rb = np.empty(shape, dtype=np.int32), np.empty(shape, dtype=np.int32)
+    _abi.check(self._lib.igmk_pop_fish_ranks(self._p, hi.size, hi.ctypes.data_as(_abi.c_i32p), hj.ctypes.data_as(_abi.c_i32p),
+                                             lo.ctypes.data_as(_abi.c_f32p), hi2.ctypes.data_as(_abi.c_f32p),
+                                             ra.ctypes.data_as(_abi.c_i32p), rb.ctypes.data_as(_abi.c_i32p)), "igmk_pop_fish_ranks")
+    return lo, hi2, ra, rb
+
+
+def _sprite_rg2(self, clusters):
+    """get_rgs2 (igm/cython_compiled/sprite.pyx:36-101) for many clusters at once.
+    clusters: list of clusters, each a list of regions, each a list of alternative bead ids.
+    -> list of (rg2s f4 [S], best_structure int, copy_idxs i4 [S][n_regions]) like the reference returns."""
+    cl_off, rg_off, beads = [0], [0], []
+    for cl in clusters:
+        for region in cl:
+            beads.extend(int(b) for b in region)
+            rg_off.append(len(beads))
+        cl_off.append(len(rg_off) - 1)
+    cl = np.array(cl_off, dtype=np.int32)
+    rg = np.array(rg_off, dtype=np.int32)
+    bd = np.array(beads if beads else [0], dtype=np.int32)
+    S = self.n_struct
+    rg2 = np.empty((len(clusters), S), dtype=np.float32)
+    ci = np.empty((max(len(rg_off) - 1, 1), S), dtype=np.int8)
+    ms = np.empty(max(len(clusters), 1), dtype=np.int32)
+    _abi.check(self._lib.igmk_pop_sprite_rg2(self._p, len(clusters), cl.ctypes.data_as(_abi.c_i32p), rg.ctypes.data_as(_abi.c_i32p),
+                                             bd.ctypes.data_as(_abi.c_i32p), rg2.ctypes.data_as(_abi.c_f32p),
+                                             ci.ctypes.data_as(C.POINTER(C.c_int8)), ms.ctypes.data_as(_abi.c_i32p)),
+               "igmk_pop_sprite_rg2")
+    return [(rg2[c], int(ms[c]), np.ascontiguousarray(ci[cl_off[c]:cl_off[c + 1]].T.astype(np.int32))) for c in range(len(clusters))]
+
+
+Population.sprite_rg2 = _sprite_rg2
+Population.fish_ranks = _fish_ranks
 Population.damid_actdist = _damid_actdist
 Population.damid_assign = _damid_assign
 

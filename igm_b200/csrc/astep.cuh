@@ -470,4 +470,155 @@ k_damid_assign(PopView P, int64_t n_rows, const int32_t* __restrict__ bead, cons
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// FISH A-step (igm/steps/FishAssignmentStep.py): per probe pair the four diploid distances
+// (get_pair_dists :31-51) or per probe the two radial distances (get_rad_dists :55-72) in every
+// structure -- np.linalg.norm(axis=1) on float32 = sqrtf((x2+y2)+z2) -- their minimum and maximum
+// over the copies, and the rank of every structure in the population for both
+// (get_min_max_and_idx :74-88, argsort(argsort(.))).  Ties (practically absent for float32
+// distances) are ranked by structure index, numpy's quicksort leaves their order unspecified.
+// One CTA per item; hap_j < 0 marks a radial probe.
+__global__ void __launch_bounds__(AD_THREADS)
+k_fish_ranks(PopView P, int64_t n_items, const int32_t* __restrict__ hap_i, const int32_t* __restrict__ hap_j,
+             float* __restrict__ out_min, float* __restrict__ out_max, int32_t* __restrict__ rank_min, int32_t* __restrict__ rank_max)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int S = P.n_struct;
+    float* vmin = (float*)smem_raw;
+    float* vmax = vmin + S;
+    for (int64_t q = blockIdx.x; q < n_items; q += gridDim.x) {
+        const int hi = hap_i[q], hj = hap_j[q];
+        const float* x1 = P.crd + (size_t)P.copy_beads[P.copy_off[hi]] * S * 3;
+        const float* x2 = P.crd + (size_t)P.copy_beads[P.copy_off[hi] + 1] * S * 3;
+        const float *y1 = nullptr, *y2 = nullptr;
+        if (hj >= 0) {
+            y1 = P.crd + (size_t)P.copy_beads[P.copy_off[hj]] * S * 3;
+            y2 = P.crd + (size_t)P.copy_beads[P.copy_off[hj] + 1] * S * 3;
+        }
+        auto norm3 = [](float a, float b, float c) {
+            return __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), __fmul_rn(c, c)));
+        };
+        for (int s = threadIdx.x; s < S; s += AD_THREADS) {
+            const float ax = x1[3 * s], ay = x1[3 * s + 1], az = x1[3 * s + 2];
+            const float bx = x2[3 * s], by = x2[3 * s + 1], bz = x2[3 * s + 2];
+            float lo, hi2;
+            if (hj >= 0) {
+                const float cx = y1[3 * s], cy = y1[3 * s + 1], cz = y1[3 * s + 2];
+                const float dx = y2[3 * s], dy = y2[3 * s + 1], dz = y2[3 * s + 2];
+                const float d0 = norm3(__fsub_rn(ax, cx), __fsub_rn(ay, cy), __fsub_rn(az, cz));
+                const float d1 = norm3(__fsub_rn(ax, dx), __fsub_rn(ay, dy), __fsub_rn(az, dz));
+                const float d2 = norm3(__fsub_rn(bx, cx), __fsub_rn(by, cy), __fsub_rn(bz, cz));
+                const float d3 = norm3(__fsub_rn(bx, dx), __fsub_rn(by, dy), __fsub_rn(bz, dz));
+                lo = fminf(fminf(d0, d1), fminf(d2, d3)); hi2 = fmaxf(fmaxf(d0, d1), fmaxf(d2, d3));
+            } else {
+                const float d0 = norm3(ax, ay, az), d1 = norm3(bx, by, bz);
+                lo = fminf(d0, d1); hi2 = fmaxf(d0, d1);
+            }
+            vmin[s] = lo; vmax[s] = hi2;
+            out_min[q * S + s] = lo; out_max[q * S + s] = hi2;
+        }
+        __syncthreads();
+        for (int s = threadIdx.x; s < S; s += AD_THREADS) {
+            const float a = vmin[s], b = vmax[s];
+            int ra = 0, rb = 0;
+            for (int t = 0; t < S; t++) {
+                const float u = vmin[t], w = vmax[t];
+                ra += (u < a) || (u == a && t < s);
+                rb += (w < b) || (w == b && t < s);
+            }
+            rank_min[q * S + s] = ra; rank_max[q * S + s] = rb;
+        }
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// SPRITE A-step numerics: get_rg2s_cpp (igm/cython_compiled/cpp_sprite_assignment.cpp:79-143).
+// A cluster is a list of regions, each with K(i) alternative beads (chromosome copies); for every
+// structure the combination of alternatives with the smallest squared radius of gyration is found
+// by enumeration in the reference's order (get_combination :63-77: region 0 is the fastest digit)
+// with its float32 arithmetic (gyration_radius_sq :49-61: sequential mean, divide by float(n),
+// sum of ((dx*dx + dy*dy) + dz*dz), divide by float(n); strict `<` keeps the first minimum).
+// One thread per (cluster, structure); a warp-aligned group of structures per cluster.
+constexpr int SPRITE_MAX_REGIONS = 8;
+
+__global__ void __launch_bounds__(256)
+k_sprite_rg2(PopView P, int32_t n_clusters, const int32_t* __restrict__ cl_off /* [n_clusters+1] regions */,
+             const int32_t* __restrict__ rg_off /* [n_regions+1] beads */, const int32_t* __restrict__ beads,
+             float* __restrict__ rg2 /* [n_clusters][S] */, int8_t* __restrict__ copy_idx /* [n_regions][S] */,
+             int32_t* __restrict__ min_struct /* [n_clusters] */)
+{
+    __shared__ float s_val[8];
+    __shared__ int s_idx[8];
+    const int S = P.n_struct;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int c = blockIdx.x; c < n_clusters; c += gridDim.x) {
+        const int r0 = cl_off[c], nr = cl_off[c + 1] - r0;
+        int ncopy[SPRITE_MAX_REGIONS], boff[SPRITE_MAX_REGIONS];
+        int ncomb = 1;
+#pragma unroll
+        for (int i = 0; i < SPRITE_MAX_REGIONS; i++) {
+            ncopy[i] = 1; boff[i] = 0;
+            if (i < nr) { boff[i] = rg_off[r0 + i]; ncopy[i] = rg_off[r0 + i + 1] - boff[i]; ncomb *= ncopy[i]; }
+        }
+        const float fn = (float)nr;
+        float best_v = 3.0e38f; int best_s = 0x7fffffff;
+        for (int s = threadIdx.x; s < S; s += blockDim.x) {
+            float min_rg2 = 100000000.0f;             // INF of the reference (:4)
+            int min_k = -1;
+            for (int k = 0; k < ncomb; k++) {
+                float px[SPRITE_MAX_REGIONS], py[SPRITE_MAX_REGIONS], pz[SPRITE_MAX_REGIONS];
+                float mx = 0.f, my = 0.f, mz = 0.f;
+                int kk = k;
+#pragma unroll
+                for (int i = 0; i < SPRITE_MAX_REGIONS; i++) {
+                    if (i < nr) {
+                        const int si = kk % ncopy[i]; kk /= ncopy[i];
+                        const float* x = P.crd + ((size_t)beads[boff[i] + si] * S + s) * 3;
+                        px[i] = x[0]; py[i] = x[1]; pz[i] = x[2];
+                        mx = __fadd_rn(mx, px[i]); my = __fadd_rn(my, py[i]); mz = __fadd_rn(mz, pz[i]);
+                    }
+                }
+                mx = __fdiv_rn(mx, fn); my = __fdiv_rn(my, fn); mz = __fdiv_rn(mz, fn);
+                float rg = 0.f;
+#pragma unroll
+                for (int i = 0; i < SPRITE_MAX_REGIONS; i++) {
+                    if (i < nr) {
+                        const float dx = __fsub_rn(px[i], mx), dy = __fsub_rn(py[i], my), dz = __fsub_rn(pz[i], mz);
+                        rg = __fadd_rn(rg, __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+                    }
+                }
+                rg = __fdiv_rn(rg, fn);
+                if (rg < min_rg2) { min_rg2 = rg; min_k = k; }
+            }
+            rg2[(size_t)c * S + s] = min_rg2;
+            int kk = min_k;
+#pragma unroll
+            for (int i = 0; i < SPRITE_MAX_REGIONS; i++) {
+                if (i < nr) {
+                    int si = -1;                       // min_copy_idx starts at -1 (:118) and stays there if no rg2 < INF
+                    if (min_k >= 0) { si = kk % ncopy[i]; kk /= ncopy[i]; }
+                    copy_idx[(size_t)(r0 + i) * S + s] = (int8_t)si;
+                }
+            }
+            if (min_rg2 < best_v || (min_rg2 == best_v && s < best_s)) { best_v = min_rg2; best_s = s; }
+        }
+        // first structure with the smallest rg2 (:136-140, strict `<`, initial minimum INF)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best_v, o);
+            const int os = __shfl_xor_sync(0xffffffffu, best_s, o);
+            if (ov < best_v || (ov == best_v && os < best_s)) { best_v = ov; best_s = os; }
+        }
+        if (lane == 0) { s_val[warp] = best_v; s_idx[warp] = best_s; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < (int)(blockDim.x >> 5); w++)
+                if (s_val[w] < best_v || (s_val[w] == best_v && s_idx[w] < best_s)) { best_v = s_val[w]; best_s = s_idx[w]; }
+            min_struct[c] = best_v < 100000000.0f ? best_s : -1;      // the reference leaves it unset in that case
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace igmk

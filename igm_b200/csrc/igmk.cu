@@ -980,6 +980,99 @@ extern "C" int igmk_pop_damid_assign(igmk_pop_t* p, int64_t n_rows, const int32_
     return 0;
 }
 
+// ---- FISH A-step ---------------------------------------------------------------------------
+extern "C" int igmk_pop_fish_ranks(igmk_pop_t* p, int64_t n_items, const int32_t* hap_i, const int32_t* hap_j,
+                                   float* min_dist, float* max_dist, int32_t* rank_min, int32_t* rank_max)
+{
+    if (!p) return fail("igmk_pop_fish_ranks: NULL handle");
+    if (n_items == 0) return 0;
+    if (!hap_i || !hap_j || !min_dist || !max_dist || !rank_min || !rank_max) return fail("igmk_pop_fish_ranks: NULL argument");
+    for (int64_t q = 0; q < n_items; q++) {
+        if (hap_i[q] < 0 || hap_i[q] >= p->n_hap || hap_j[q] >= p->n_hap) return fail("igmk_pop_fish_ranks: locus index out of range");
+        // the reference indexes copies [0] and [1] (FishAssignmentStep.py:41-44, :63-64): diploid loci only
+        if (p->copy_off[hap_i[q] + 1] - p->copy_off[hap_i[q]] < 2 ||
+            (hap_j[q] >= 0 && p->copy_off[hap_j[q] + 1] - p->copy_off[hap_j[q]] < 2))
+            return fail("igmk_pop_fish_ranks: locus has fewer than two copies (IndexError in the reference)");
+    }
+    CU(cudaSetDevice(p->device));
+    const size_t S = (size_t)p->n_struct;
+    const size_t smem = 2 * S * sizeof(float);
+    if ((long long)smem + 1024 > (long long)p->smem_optin) return fail("igmk_pop_fish_ranks: population too large for one CTA's shared memory");
+    CU(p->d_pi.reserve(n_items)); CU(p->d_pj.reserve(n_items));
+    DevBuf<float> d_lo, d_hi; DevBuf<int32_t> d_ra, d_rb;
+    CU(d_lo.reserve(n_items * S)); CU(d_hi.reserve(n_items * S)); CU(d_ra.reserve(n_items * S)); CU(d_rb.reserve(n_items * S));
+    CU(cudaMemcpyAsync(p->d_pi.p, hap_i, n_items * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaMemcpyAsync(p->d_pj.p, hap_j, n_items * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream));
+    CU(cudaFuncSetAttribute(k_fish_ranks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t grid = std::min<int64_t>(n_items, (int64_t)p->sm_count * 8);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_fish_ranks<<<(int)grid, AD_THREADS, smem, p->stream>>>(p->view(), n_items, p->d_pi.p, p->d_pj.p, d_lo.p, d_hi.p, d_ra.p, d_rb.p);
+    cudaError_t le = cudaGetLastError();
+    if (le == cudaSuccess) le = cudaEventRecord(p->ev1, p->stream);
+    if (le == cudaSuccess) le = cudaMemcpyAsync(min_dist, d_lo.p, n_items * S * sizeof(float), cudaMemcpyDeviceToHost, p->stream);
+    if (le == cudaSuccess) le = cudaMemcpyAsync(max_dist, d_hi.p, n_items * S * sizeof(float), cudaMemcpyDeviceToHost, p->stream);
+    if (le == cudaSuccess) le = cudaMemcpyAsync(rank_min, d_ra.p, n_items * S * sizeof(int32_t), cudaMemcpyDeviceToHost, p->stream);
+    if (le == cudaSuccess) le = cudaMemcpyAsync(rank_max, d_rb.p, n_items * S * sizeof(int32_t), cudaMemcpyDeviceToHost, p->stream);
+    if (le == cudaSuccess) le = cudaStreamSynchronize(p->stream);
+    if (le == cudaSuccess) le = cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1);
+    d_lo.release(); d_hi.release(); d_ra.release(); d_rb.release();
+    CU(le);
+    p->n_pairs = 0; p->actdist_done = false;
+    return 0;
+}
+
+// ---- SPRITE A-step ---------------------------------------------------------------------------
+extern "C" int igmk_pop_sprite_rg2(igmk_pop_t* p, int32_t n_clusters, const int32_t* cl_off, const int32_t* rg_off,
+                                   const int32_t* beads, float* rg2, int8_t* copy_idx, int32_t* min_struct)
+{
+    if (!p) return fail("igmk_pop_sprite_rg2: NULL handle");
+    if (n_clusters == 0) return 0;
+    if (!cl_off || !rg_off || !beads || !rg2 || !copy_idx || !min_struct) return fail("igmk_pop_sprite_rg2: NULL argument");
+    if (cl_off[0] != 0 || rg_off[0] != 0) return fail("igmk_pop_sprite_rg2: offsets must start at 0");
+    const int32_t n_regions = cl_off[n_clusters];
+    for (int c = 0; c < n_clusters; c++) {
+        const int nr = cl_off[c + 1] - cl_off[c];
+        if (nr < 1 || nr > SPRITE_MAX_REGIONS) return fail("igmk_pop_sprite_rg2: a cluster needs 1..8 regions");
+        long long comb = 1;
+        for (int i = cl_off[c]; i < cl_off[c + 1]; i++) {
+            const int k = rg_off[i + 1] - rg_off[i];
+            if (k < 1 || k > 127) return fail("igmk_pop_sprite_rg2: a region needs 1..127 alternative beads");
+            comb *= k;
+        }
+        if (comb > 65536) return fail("igmk_pop_sprite_rg2: more than 65536 copy combinations in one cluster");
+    }
+    const int32_t n_beads = rg_off[n_regions];
+    for (int i = 0; i < n_beads; i++)
+        if (beads[i] < 0 || beads[i] >= p->n_bead) return fail("igmk_pop_sprite_rg2: bead index out of range");
+    CU(cudaSetDevice(p->device));
+    const size_t S = (size_t)p->n_struct;
+    DevBuf<int32_t> d_cl, d_rg, d_b, d_ms; DevBuf<float> d_v; DevBuf<int8_t> d_ci;
+    cudaError_t e = d_cl.reserve(n_clusters + 1);
+    if (e == cudaSuccess) e = d_rg.reserve(n_regions + 1);
+    if (e == cudaSuccess) e = d_b.reserve(std::max(n_beads, 1));
+    if (e == cudaSuccess) e = d_ms.reserve(n_clusters);
+    if (e == cudaSuccess) e = d_v.reserve((size_t)n_clusters * S);
+    if (e == cudaSuccess) e = d_ci.reserve((size_t)n_regions * S);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_cl.p, cl_off, (n_clusters + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_rg.p, rg_off, (n_regions + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_b.p, beads, n_beads * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(p->ev0, p->stream);
+    if (e == cudaSuccess) {
+        const int grid = std::min<int>(n_clusters, p->sm_count * 8);
+        k_sprite_rg2<<<grid, 256, 0, p->stream>>>(p->view(), n_clusters, d_cl.p, d_rg.p, d_b.p, d_v.p, d_ci.p, d_ms.p);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaEventRecord(p->ev1, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rg2, d_v.p, (size_t)n_clusters * S * sizeof(float), cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(copy_idx, d_ci.p, (size_t)n_regions * S, cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(min_struct, d_ms.p, n_clusters * sizeof(int32_t), cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1);
+    d_cl.release(); d_rg.release(); d_b.release(); d_ms.release(); d_v.release(); d_ci.release();
+    CU(e);
+    return 0;
+}
+
 extern "C" int igmk_pop_set_rows(igmk_pop_t* p, int64_t n_rows, const int32_t* row, const int32_t* col, const float* dist)
 {
     if (!p) return fail("igmk_pop_set_rows: NULL handle");

@@ -271,6 +271,28 @@ int igmk_pop_damid_actdist(igmk_pop_t* p, int64_t n_loci, const int32_t* loc,
 int igmk_pop_damid_assign(igmk_pop_t* p, int64_t n_rows, const int32_t* bead, const float* dist,
                           double contact_range, const double* semiaxes, uint32_t* bits);
 
+/*
+ * FISH A-step (igm/steps/FishAssignmentStep.py:31-88): for item q = pair (hap_i, hap_j) or radial
+ * probe (hap_j < 0) the minimum and maximum over the diploid copies of the pair / radial distance
+ * in every structure (min_dist, max_dist: [n_items][n_struct] float32 = the values numpy holds) and
+ * the rank of each structure in the population (argsort(argsort(.)), rank_*: [n_items][n_struct]);
+ * the caller then gathers target[rank] like FishAssignmentStep.task (:220-225, :247-252).
+ */
+int igmk_pop_fish_ranks(igmk_pop_t* p, int64_t n_items, const int32_t* hap_i, const int32_t* hap_j,
+                        float* min_dist, float* max_dist, int32_t* rank_min, int32_t* rank_max);
+
+/*
+ * SPRITE A-step numerics = get_rgs2 / get_rg2s_cpp (igm/cython_compiled/sprite.pyx:36-101,
+ * cpp_sprite_assignment.cpp:79-143) for a batch of clusters taken straight from the resident
+ * population: cluster c has regions cl_off[c]..cl_off[c+1]; region i has the alternative beads
+ * beads[rg_off[i]..rg_off[i+1]] (its chromosome copies).  Outputs: rg2 [n_clusters][n_struct] the
+ * smallest squared radius of gyration over all copy combinations, copy_idx [n_regions][n_struct]
+ * the chosen alternative per region (int8), min_struct [n_clusters] the first structure with the
+ * smallest rg2.  float32 arithmetic in the reference's order: results are bit-identical.
+ */
+int igmk_pop_sprite_rg2(igmk_pop_t* p, int32_t n_clusters, const int32_t* cl_off, const int32_t* rg_off,
+                        const int32_t* beads, float* rg2, int8_t* copy_idx, int32_t* min_struct);
+
 #ifdef __cplusplus
 }
 #endif

@@ -188,6 +188,29 @@ def main():
     print("damid golden: %d loci -> %d rows per shape; members/struct %s" %
           (d_loc.size, damid["sphere_bead"].size, [damid["sphere_members_%d" % s].size for s in assign_structs]))
 
+    # ---------------- FISH A-step through the reference's own helpers ----------------------------
+    fas = sys.modules["igm.steps.FishAssignmentStep"]
+    dip = np.array([h for h in range(nhap) if len(m_copy_index[h]) == 2])
+    f_i = rng.choice(dip, 40, replace=False).astype(np.int32)
+    f_j = rng.choice(dip, 40, replace=False).astype(np.int32)
+    f_j[f_j == f_i] = dip[0]
+    f_probe = rng.choice(dip, 25, replace=False).astype(np.int32)
+    fish = {k: [] for k in ("pmin", "pmax", "pimin", "pimax", "rmin", "rmax", "rimin", "rimax")}
+    n_conf = m_crd.shape[1]
+    for a_, b_ in zip(f_i, f_j):
+        d = fas.get_pair_dists(m_copy_index[int(a_)], m_copy_index[int(b_)], len(m_rad), n_conf, m_crd)
+        mn, mx, imn, imx = fas.get_min_max_and_idx(d)
+        assert len(np.unique(mn)) == n_conf and len(np.unique(mx)) == n_conf      # no ties in the fixture
+        fish["pmin"].append(mn); fish["pmax"].append(mx); fish["pimin"].append(imn); fish["pimax"].append(imx)
+    for a_ in f_probe:
+        d = fas.get_rad_dists(m_copy_index[int(a_)], len(m_rad), n_conf, m_crd)
+        mn, mx, imn, imx = fas.get_min_max_and_idx(d)
+        assert len(np.unique(mn)) == n_conf and len(np.unique(mx)) == n_conf
+        fish["rmin"].append(mn); fish["rmax"].append(mx); fish["rimin"].append(imn); fish["rimax"].append(imx)
+    np.savez_compressed(os.path.join(HERE, "fish_golden.npz"), pair_i=f_i, pair_j=f_j, probes=f_probe,
+                        **{k: np.array(v) for k, v in fish.items()})
+    print("fish golden: %d pairs, %d probes" % (len(f_i), len(f_probe)))
+
     # ---------------- reference LAMMPS front end on a small model ----------------------
     from igm.model.kernel import lammps as reflammps
     from igm.model.kernel.lammps_model import LammpsModel
@@ -275,6 +298,28 @@ def main():
     assert np.allclose(r1[0], [1.0]) and r1[1] == 0
     assert np.allclose(r3[0], [0.125, 0.01]) and r3[1] == 1 and np.array_equal(r3[2], [[1, 0], [0, 1]])
     print("sprite known answers reproduce")
+    # random clusters on the mini genome through the reference's native code
+    rng2 = np.random.default_rng(13)
+    chroms_dip = [c for c in keep_chrom if c < 22]
+    sp = {}
+    n_cl = 30
+    cl_regions = []
+    for c in range(n_cl):
+        nreg = int(rng2.integers(1, 5))
+        regs = []
+        for _ in range(nreg):
+            h = int(rng2.choice(dip if rng2.random() < 0.8 else np.arange(nhap)))
+            regs.append(m_copy_index[h])
+        cl_regions.append(regs)
+        flat = [b for r in regs for b in r]
+        crds = np.ascontiguousarray(m_crd[flat])
+        rg2s, best, idx = get_rgs2(crds, np.array([len(r) for r in regs], dtype=np.int32))
+        sp["rg2_%d" % c], sp["best_%d" % c], sp["idx_%d" % c] = rg2s, np.int32(best), idx
+    sp["cl_off"] = np.cumsum([0] + [len(r) for r in cl_regions]).astype(np.int32)
+    sp["rg_off"] = np.cumsum([0] + [len(r) for regs in cl_regions for r in regs]).astype(np.int32)
+    sp["beads"] = np.array([b for regs in cl_regions for r in regs for b in r], dtype=np.int32)
+    np.savez_compressed(os.path.join(HERE, "sprite_golden.npz"), **sp)
+    print("sprite golden: %d clusters" % n_cl)
 
 
 if __name__ == "__main__":
