@@ -58,6 +58,10 @@ struct igmk_handle {
     std::vector<float2>   btype_f;
     std::vector<double2>  btype_d;
     std::vector<int64_t>  struct_id;
+    // bonds / envelope members in submit order, for the violation statistics (M10)
+    std::vector<SubBond> sub_bonds; std::vector<int32_t> sub_bond_atom_off; std::vector<int64_t> sub_bond_start;
+    std::vector<EnvMember> sub_env; std::vector<int64_t> sub_env_start;
+    std::vector<double> viol_bond, viol_env; bool viol_valid = false;
     int max_atoms = 0;
     int nl_width = NL_WIDTH0;
     // thread-per-atom MD layout (md2.cuh), built at upload time
@@ -146,6 +150,8 @@ extern "C" int igmk_clear(igmk_handle_t* h)
     h->free_device();
     h->desc.clear(); h->xyzr.clear(); h->xyzr0.clear(); h->kind.clear(); h->envmask.clear(); h->bond_ptr.clear();
     h->bond_items.clear(); h->btype_f.clear(); h->btype_d.clear(); h->struct_id.clear();
+    h->sub_bonds.clear(); h->sub_bond_atom_off.clear(); h->sub_bond_start.clear(); h->sub_env.clear(); h->sub_env_start.clear();
+    h->viol_valid = false;
     h->res.clear(); h->flags.clear(); h->forces.clear();
     h->max_atoms = 0; h->dirty = true; h->have_forces = false;
     return 0;
@@ -257,6 +263,23 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
     h->bond_items.insert(h->bond_items.end(), items.begin(), items.end());
     h->desc.push_back(d);
     h->struct_id.push_back(s->struct_id);
+    h->sub_bond_start.push_back((int64_t)h->sub_bonds.size());
+    for (int b = 0; b < s->n_bonds; b++) {
+        SubBond q;
+        q.i = s->bond_i[b]; q.j = s->bond_j[b]; q.r0 = s->bond_r0[b]; q.k = s->bond_k[b]; q.style = s->bond_style[b];
+        q.f32 = ((double)(float)q.r0 == q.r0) ? 1 : 0;
+        h->sub_bonds.push_back(q);
+        h->sub_bond_atom_off.push_back(d.atom_off);
+    }
+    h->sub_env_start.push_back((int64_t)h->sub_env.size());
+    for (int e = 0; e < s->n_env; e++)
+        for (int q = s->env_off[e]; q < s->env_off[e + 1]; q++) {
+            EnvMember m;
+            m.atom = d.atom_off + s->env_members[q]; m.pad = 0;
+            m.a = s->env_abck[4 * e]; m.b = s->env_abck[4 * e + 1]; m.c = s->env_abck[4 * e + 2]; m.k = s->env_abck[4 * e + 3];
+            h->sub_env.push_back(m);
+        }
+    h->viol_valid = false;
     h->max_atoms = std::max(h->max_atoms, n);
     h->dirty = true;
     if (slot_out) *slot_out = (int32_t)h->desc.size() - 1;
@@ -387,6 +410,42 @@ extern "C" int igmk_upload(igmk_handle_t* h)
     return upload(h);
 }
 
+// M10: violation ratios of every submitted restraint at the batch's current coordinates
+extern "C" int igmk_violation_ratios(igmk_handle_t* h, int32_t slot, double* bond_ratio, double* env_u)
+{
+    if (!h) return fail("igmk_violation_ratios: NULL handle");
+    if (slot < 0 || slot >= (int)h->desc.size()) return fail("igmk_violation_ratios: bad slot");
+    CU(cudaSetDevice(h->device));
+    if (!h->viol_valid) {
+        if (int rc = upload(h)) return rc;
+        const int64_t nb = (int64_t)h->sub_bonds.size(), ne = (int64_t)h->sub_env.size();
+        h->viol_bond.assign((size_t)nb, 0.0); h->viol_env.assign((size_t)ne, 0.0);
+        SubBond* d_b = nullptr; int32_t* d_o = nullptr; EnvMember* d_e = nullptr; double* d_r = nullptr;
+        cudaError_t e = dev_alloc_copy(&d_b, h->sub_bonds);
+        if (e == cudaSuccess) e = dev_alloc_copy(&d_o, h->sub_bond_atom_off);
+        if (e == cudaSuccess) e = dev_alloc_copy(&d_e, h->sub_env);
+        if (e == cudaSuccess) e = cudaMalloc((void**)&d_r, (size_t)std::max<int64_t>(std::max(nb, ne), 1) * sizeof(double));
+        if (e == cudaSuccess && nb > 0) {
+            k_bond_violations<<<(int)std::min<int64_t>((nb + 255) / 256, 148 * 16), 256>>>(h->d_xyzr, d_b, d_o, nb, d_r);
+            e = cudaGetLastError();
+            if (e == cudaSuccess) e = cudaMemcpy(h->viol_bond.data(), d_r, (size_t)nb * sizeof(double), cudaMemcpyDeviceToHost);
+        }
+        if (e == cudaSuccess && ne > 0) {
+            k_env_violations<<<(int)std::min<int64_t>((ne + 255) / 256, 148 * 16), 256>>>(h->d_xyzr, d_e, ne, d_r);
+            e = cudaGetLastError();
+            if (e == cudaSuccess) e = cudaMemcpy(h->viol_env.data(), d_r, (size_t)ne * sizeof(double), cudaMemcpyDeviceToHost);
+        }
+        cudaFree(d_b); cudaFree(d_o); cudaFree(d_e); cudaFree(d_r);
+        CU(e);
+        h->viol_valid = true;
+    }
+    const int64_t b0 = h->sub_bond_start[slot], b1 = slot + 1 < (int)h->desc.size() ? h->sub_bond_start[slot + 1] : (int64_t)h->sub_bonds.size();
+    const int64_t e0 = h->sub_env_start[slot], e1 = slot + 1 < (int)h->desc.size() ? h->sub_env_start[slot + 1] : (int64_t)h->sub_env.size();
+    if (bond_ratio && b1 > b0) memcpy(bond_ratio, h->viol_bond.data() + b0, (size_t)(b1 - b0) * sizeof(double));
+    if (env_u && e1 > e0) memcpy(env_u, h->viol_env.data() + e0, (size_t)(e1 - e0) * sizeof(double));
+    return 0;
+}
+
 extern "C" int igmk_last_timings(igmk_handle_t* h, double* md_ms, double* cg_ms, int64_t* h2d_bytes)
 {
     if (!h) return fail("igmk_last_timings: NULL handle");
@@ -399,6 +458,7 @@ extern "C" int igmk_last_timings(igmk_handle_t* h, double* md_ms, double* cg_ms,
 extern "C" int igmk_reset_coordinates(igmk_handle_t* h)
 {
     if (!h) return fail("igmk_reset_coordinates: NULL handle");
+    h->viol_valid = false;
     h->xyzr = h->xyzr0;
     if (!h->dirty && h->d_xyzr) {
         CU(cudaSetDevice(h->device));
@@ -526,6 +586,7 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
         if (rc) return 1;
         break;
     }
+    h->viol_valid = false;
     for (auto& r : h->res) r.md_seconds = ms * 1e-3;
     h->forces.clear();                 // copied on demand by igmk_fetch_forces
     h->have_forces = true;

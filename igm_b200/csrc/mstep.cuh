@@ -757,4 +757,70 @@ k_cg(Batch B, igmk_protocol_t pr)
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// M10: per-restraint violation ratios at the current coordinates, what ModelingStep.task gathers
+// force by force (igm/steps/ModelingStep.py:345-372) through HarmonicUpperBound/LowerBound
+// .getViolationRatio (igm/model/forces.py:128-136, :176-184) and EllipticEnvelope.getScores
+// (:220-250).  Arithmetic as numpy does it on float32 positions: dist = np.linalg.norm of a float32
+// 3-vector (float32 products, double accumulation, one rounding, float32 sqrt); then the float32
+// chain score = k*(dist-d), ratio = score/(k*d) when d is a float32 value (Polymer, Hi-C, SPRITE:
+// contactRange*(ri+rj) on float32 radii) or the same in float64 when it is not (FISH targets).
+struct SubBond { int32_t i, j; double r0, k; int32_t style, f32; };
+
+__device__ __forceinline__ float norm_f32_sdot(float dx, float dy, float dz)
+{
+    const double acc = __dadd_rn(__dadd_rn((double)__fmul_rn(dx, dx), (double)__fmul_rn(dy, dy)), (double)__fmul_rn(dz, dz));
+    return __fsqrt_rn(__double2float_rn(acc));
+}
+
+__global__ void __launch_bounds__(256)
+k_bond_violations(const float4* __restrict__ xyzr, const SubBond* __restrict__ bonds, const int32_t* __restrict__ atom_off_of_bond,
+                  int64_t n_bonds, double* __restrict__ ratio)
+{
+    for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_bonds; b += (int64_t)gridDim.x * blockDim.x) {
+        const SubBond q = bonds[b];
+        const float4 pi = xyzr[atom_off_of_bond[b] + q.i], pj = xyzr[atom_off_of_bond[b] + q.j];
+        const float dist = norm_f32_sdot(__fsub_rn(pi.x, pj.x), __fsub_rn(pi.y, pj.y), __fsub_rn(pi.z, pj.z));
+        double r = 0.0;
+        if (q.r0 != 0.0) {                                                   // forces.py:136, :184
+            if (q.f32) {
+                const float d = (float)q.r0, k = (float)q.k;
+                const bool viol = q.style == IGMK_BOND_UPPER ? !(dist <= d) : !(dist >= d);
+                if (viol) {
+                    const float diff = q.style == IGMK_BOND_UPPER ? __fsub_rn(dist, d) : __fsub_rn(d, dist);
+                    r = (double)__fdiv_rn(__fmul_rn(k, diff), __fmul_rn(k, d));
+                }
+            } else {
+                const double dd = (double)dist;
+                const bool viol = q.style == IGMK_BOND_UPPER ? !(dd <= q.r0) : !(dd >= q.r0);
+                if (viol) r = (q.k * (q.style == IGMK_BOND_UPPER ? dd - q.r0 : q.r0 - dd)) / (q.k * q.r0);
+            }
+        }
+        ratio[b] = r;
+    }
+}
+
+// Envelope members: u = (1 - 1/sqrt(q)) * |x| for k > 0 and q > 1, u = 1 - sqrt(q) for k < 0 and q < 1,
+// else 0, with q = sqrt(sum x^2/(axis - r)^2) (forces.py:224-244; the reference takes the square root
+// twice); the host finishes with the force's `scale`: ratio = max(0, t*k)/(k*scale), t = u/scale (k > 0).
+struct EnvMember { int32_t atom; int32_t pad; double a, b, c, k; };
+
+__global__ void __launch_bounds__(256)
+k_env_violations(const float4* __restrict__ xyzr, const EnvMember* __restrict__ mem, int64_t n_mem, double* __restrict__ u_out)
+{
+    for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < n_mem; m += (int64_t)gridDim.x * blockDim.x) {
+        const EnvMember e = mem[m];
+        const float4 p = xyzr[e.atom];
+        const double r = (double)p.w;
+        const double sa = e.a - r, sb = e.b - r, sc = e.c - r;
+        const double s = __dadd_rn(__dadd_rn(__ddiv_rn((double)__fmul_rn(p.x, p.x), sa * sa), __ddiv_rn((double)__fmul_rn(p.y, p.y), sb * sb)),
+                                   __ddiv_rn((double)__fmul_rn(p.z, p.z), sc * sc));
+        const double q = sqrt(s);
+        double u = 0.0;
+        if (q > 1.0 && e.k > 0.0) u = (1.0 - 1.0 / sqrt(q)) * (double)norm_f32_sdot(p.x, p.y, p.z);
+        else if (q < 1.0 && e.k < 0.0) u = 1.0 - sqrt(q);
+        u_out[m] = u;
+    }
+}
+
 }  // namespace igmk

@@ -102,6 +102,16 @@ class MStepBatch(object):
         _abi.check(self._lib.igmk_fetch(self._h, slot, xyz.ctypes.data_as(_abi.c_f32p), C.byref(res)), "igmk_fetch")
         return xyz, res
 
+    def violation_ratios(self, slot):
+        """-> (bond_ratio f8 [n_bonds] in submit order, env_u f8 [sum of envelope members]) at the
+        current coordinates; see igmk_violation_ratios in include/igmk.h."""
+        ps = self._packed[slot]
+        br = np.zeros(ps.bond_i.size, dtype=np.float64)
+        eu = np.zeros(ps.env_members.size, dtype=np.float64)
+        _abi.check(self._lib.igmk_violation_ratios(self._h, slot, br.ctypes.data_as(_abi.c_f64p), eu.ctypes.data_as(_abi.c_f64p)),
+                   "igmk_violation_ratios")
+        return br, eu
+
     def last_timings(self):
         """-> (md_ms, cg_ms, h2d_bytes) of the last run() / upload()"""
         a, b, c = C.c_double(0), C.c_double(0), C.c_int64(0)
@@ -127,6 +137,23 @@ def info_from_result(res):
         "thermo": thermo,
         "md-time": res.md_seconds,
     }
+
+
+def envelope_ratios(env_u, k, scale):
+    """Finish EllipticEnvelope.getViolationRatios (igm/model/forces.py:236-250) from the kernel's
+    scale-free part: t = u/scale for k > 0 (k2 > 1), t = u for k < 0 (k2 < 1); score = max(0, t*k);
+    ratio = score / (k*scale)."""
+    t = env_u / scale if k > 0 else env_u
+    return np.maximum(0, t * k) / (k * scale)
+
+
+def violation_histogram(v, nbins=100, vmax=1):
+    """get_violation_histogram (igm/steps/ModelingStep.py:649-659), verbatim semantics"""
+    v = np.array(v)
+    over = np.count_nonzero(v > vmax)
+    inner = v[v <= vmax]
+    H, edges = np.histogram(inner, bins=nbins, range=(0, vmax))
+    return np.concatenate([H, [over]]), np.concatenate([edges, [np.inf]])
 
 
 def optimize_population(models, cfg, device=None):

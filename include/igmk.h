@@ -143,6 +143,16 @@ int igmk_single_point_f32(igmk_handle_t* h, double ev_scale, double env_scale,
 int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out /* [n_atoms][3] */,
                igmk_result_t* res);
 int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out /* [n_atoms][3] */);
+/*
+ * Violation ratios of the structure's restraints at the batch's CURRENT coordinates (after igmk_run:
+ * the optimised ones) -- what ModelingStep.task collects force by force
+ * (igm/steps/ModelingStep.py:345-372).  bond_ratio [n_bonds], submit order: HarmonicUpperBound /
+ * LowerBound.getViolationRatio (igm/model/forces.py:128-136, :176-184).  env_u [sum of envelope
+ * members], envelope by envelope in member order: the scale-free part of EllipticEnvelope.getScores
+ * (:220-250): for k > 0, ratio = max(0, (u/scale)*k) / (k*scale); for k < 0, ratio = max(0, u*k)/(k*scale).
+ * All structures are evaluated in one pass on the first call after the coordinates changed.
+ */
+int igmk_violation_ratios(igmk_handle_t* h, int32_t slot, double* bond_ratio, double* env_u);
 /* device time (ms) of the MD and CG launches of the last igmk_run and the bytes the last
  * upload moved host -> device (any pointer may be NULL) */
 int igmk_last_timings(igmk_handle_t* h, double* md_ms, double* cg_ms, int64_t* h2d_bytes);

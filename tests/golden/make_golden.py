@@ -211,6 +211,45 @@ def main():
                         **{k: np.array(v) for k, v in fish.items()})
     print("fish golden: %d pairs, %d probes" % (len(f_i), len(f_probe)))
 
+    # ---------------- violation ratios through the reference's Force classes (M10) ---------------
+    from oracle import viol_oracle
+    from igm_b200.kernel import envelope_ratios
+    sv = 17
+    vmodel = Model(uid=sv)
+    nbv = 200
+    for b in range(nbv):
+        vmodel.addParticle(m_crd[b, sv], m_rad[b], Particle.NORMAL)
+    vb_i = rng.integers(0, nbv, 300); vb_j = (vb_i + rng.integers(1, nbv - 1, 300)) % nbv
+    vb_style = rng.integers(0, 2, 300)
+    vb_k = rng.choice([1.0, 0.5, 2.5], 300)
+    vb_r0 = np.where(rng.random(300) < 0.6,
+                     (rng.choice([2.0, 4.0, 8.0], 300) * (m_rad[vb_i] + m_rad[vb_j])).astype(np.float32).astype(np.float64),
+                     rng.uniform(200.0, 6000.0, 300))          # float32-valued (restraints) and float64-valued (FISH targets)
+    vb_r0[::37] = 0.0
+    v_ratio = []
+    for a_, b_, st, kk, d in zip(vb_i, vb_j, vb_style, vb_k, vb_r0):
+        dd = np.float32(d) if float(np.float32(d)) == d else np.float64(d)
+        f = (HarmonicUpperBound if st == 0 else HarmonicLowerBound)((int(a_), int(b_)), dd, float(kk))
+        v_ratio.append(float(f.getViolationRatio(vmodel.particles)))
+    env_specs = [((5100.0, 5100.0, 5100.0), 1.0, 510.0, list(range(nbv))),
+                 ((5225.0, 4750.0, 4275.0), -0.3, 4750.0, [int(v) for v in rng.choice(nbv, 60, replace=False)])]
+    v_env = []
+    for semi, kk, scale, members in env_specs:
+        f = EllipticEnvelope(members, 0, semi, kk, scale=scale)
+        v_env.append(f.getViolationRatios(vmodel.particles))
+        u = viol_oracle.envelope_u(m_crd[:nbv, sv], m_rad, members, semi, kk)
+        assert np.array_equal(envelope_ratios(u, kk, scale), v_env[-1])
+    o_ratio = viol_oracle.bond_ratios(m_crd[:nbv, sv], vb_i, vb_j, vb_r0, vb_k, vb_style)
+    assert np.array_equal(o_ratio, np.array(v_ratio)), np.abs(o_ratio - np.array(v_ratio)).max()
+    np.savez_compressed(os.path.join(HERE, "viol_golden.npz"), struct=np.int32(sv), n_bead=np.int32(nbv), bond_i=vb_i, bond_j=vb_j,
+                        bond_style=vb_style, bond_k=vb_k, bond_r0=vb_r0, bond_ratio=np.array(v_ratio),
+                        env0_semi=np.array(env_specs[0][0]), env0_k=np.float64(1.0), env0_scale=np.float64(510.0),
+                        env0_members=np.array(env_specs[0][3]), env0_ratio=v_env[0],
+                        env1_semi=np.array(env_specs[1][0]), env1_k=np.float64(-0.3), env1_scale=np.float64(4750.0),
+                        env1_members=np.array(env_specs[1][3]), env1_ratio=v_env[1])
+    print("violation golden: %d bonds (%d violated), envelope members violated %d / %d" %
+          (len(v_ratio), np.count_nonzero(v_ratio), np.count_nonzero(v_env[0]), np.count_nonzero(v_env[1])))
+
     # ---------------- reference LAMMPS front end on a small model ----------------------
     from igm.model.kernel import lammps as reflammps
     from igm.model.kernel.lammps_model import LammpsModel
