@@ -15,6 +15,7 @@
 #include "../../include/igmk.h"
 #include "mstep.cuh"
 #include "md2.cuh"
+#include "md_big.cuh"
 #include "astep.cuh"
 
 using namespace igmk;
@@ -73,6 +74,7 @@ struct igmk_handle {
     std::vector<uint32_t> md2_ell_items;
     Md2Desc* d_md2_desc = nullptr; uint16_t* d_md2_perm = nullptr; int32_t* d_md2_ell_off = nullptr;
     uint32_t* d_md2_ell_items = nullptr; uint16_t* d_md2_nl = nullptr;
+    bool md_big = false; float* d_big_state = nullptr; double* d_big = nullptr;
     bool dirty = true;
     // device
     StructDesc* d_desc = nullptr; float4* d_xyzr = nullptr; float4* d_xyzr0 = nullptr; uint8_t* d_kind = nullptr; uint32_t* d_envmask = nullptr;
@@ -92,6 +94,7 @@ struct igmk_handle {
         cudaFree(d_desc); cudaFree(d_xyzr); cudaFree(d_xyzr0); cudaFree(d_kind); cudaFree(d_envmask); cudaFree(d_bond_ptr);
         cudaFree(d_bond_items); cudaFree(d_btype_f); cudaFree(d_btype_d); cudaFree(d_nl); cudaFree(d_nl_cnt);
         cudaFree(d_xd); cudaFree(d_fd); cudaFree(d_work); cudaFree(d_res); cudaFree(d_flags);
+        cudaFree(d_big_state); cudaFree(d_big); d_big_state = nullptr; d_big = nullptr;
         cudaFree(d_md2_desc); cudaFree(d_md2_perm); cudaFree(d_md2_ell_off); cudaFree(d_md2_ell_items); cudaFree(d_md2_nl);
         d_md2_desc = nullptr; d_md2_perm = nullptr; d_md2_ell_off = nullptr; d_md2_ell_items = nullptr; d_md2_nl = nullptr;
         d_desc = nullptr; d_xyzr = nullptr; d_xyzr0 = nullptr; d_kind = nullptr; d_envmask = nullptr; d_bond_ptr = nullptr;
@@ -162,8 +165,8 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
     if (!h || !s) return fail("igmk_submit: NULL argument");
     char msg[256];
     const int n = s->n_atoms;
-    if (n <= 0 || n > 65535) {
-        snprintf(msg, sizeof msg, "igmk_submit: structure %lld has %d atoms (supported: 1..65535)", (long long)s->struct_id, n);
+    if (n <= 0 || n > 65534) {
+        snprintf(msg, sizeof msg, "igmk_submit: structure %lld has %d atoms (supported: 1..65534)", (long long)s->struct_id, n);
         return fail(msg);
     }
     if (s->n_env < 0 || s->n_env > IGMK_MAX_ENVELOPES) return fail("igmk_submit: too many envelopes");
@@ -385,6 +388,15 @@ static int upload(igmk_handle* h)
     CU(cudaMemset(h->d_res, 0, std::max<size_t>(ns, 1) * sizeof(igmk_result_t)));
     CU(cudaMemset(h->d_flags, 0, std::max<size_t>(ns, 1) * sizeof(int32_t)));
     h->md2_K = md2_pick_K(h->max_atoms);
+    h->md_big = h->md2_K == 0 || getenv("IGMK_FORCE_BIG") != nullptr;   // the variable routes small batches through md_big.cuh (tests)
+    if (h->md_big) {                                   // > 8192 atoms: state in global memory (md_big.cuh)
+        h->md2_K = (h->max_atoms + MD2_T - 1) / MD2_T;
+        if ((long long)md_big_smem_bytes(h->md2_K) > (long long)h->smem_optin)
+            return fail("igmk: structure too large even for the global-memory MD path (cell grid exceeds shared memory)");
+        CU(cudaMalloc((void**)&h->d_big_state, ns * (size_t)h->md2_K * MD2_T * BIG_FLOATS_PER_POS * sizeof(float)));
+    }
+    if (ctx_is_big<double>(h->max_atoms, false) || ctx_is_big<float>(h->max_atoms, false))
+        CU(cudaMalloc((void**)&h->d_big, (na + 32 * ns) * 10 * sizeof(double)));
     if (h->md2_K > 0) {
         md2_build(h);
         CU(dev_alloc_copy(&h->d_md2_desc, h->md2_desc));
@@ -473,7 +485,7 @@ static Batch make_batch(igmk_handle* h)
     B.n_struct = (int32_t)h->desc.size(); B.max_atoms = h->max_atoms;
     B.desc = h->d_desc; B.xyzr = h->d_xyzr; B.kind = h->d_kind; B.envmask = h->d_envmask;
     B.bond_ptr = h->d_bond_ptr; B.bond_items = h->d_bond_items; B.btype_f = h->d_btype_f; B.btype_d = h->d_btype_d;
-    B.nl = h->d_nl; B.nl_width = h->nl_width; B.nl_cnt = h->d_nl_cnt; B.xd = h->d_xd; B.fd = h->d_fd; B.work = h->d_work;
+    B.nl = h->d_nl; B.nl_width = h->nl_width; B.nl_cnt = h->d_nl_cnt; B.xd = h->d_xd; B.fd = h->d_fd; B.work = h->d_work; B.big = h->d_big;
     B.res = h->d_res; B.flags = h->d_flags;
     return B;
 }
@@ -534,6 +546,16 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
 
 static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
 {
+    if (h->md_big) {
+        const size_t sm = md_big_smem_bytes(h->md2_K);
+        CU(cudaFuncSetAttribute(k_md_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        Md2View V;
+        V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
+        V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.prof = nullptr;
+        k_md_big<<<ns, MD2_T, sm>>>(B, V, h->d_md2_desc, P, h->d_big_state);
+        CU(cudaGetLastError());
+        return 0;
+    }
     switch (h->md2_K) {
         case 1: return launch_md2_k<1>(h, B, P, ns);
         case 2: return launch_md2_k<2>(h, B, P, ns);
@@ -542,7 +564,7 @@ static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
         case 6: return launch_md2_k<6>(h, B, P, ns);
         case 8: return launch_md2_k<8>(h, B, P, ns);
     }
-    return fail("igmk_run: structures with more than 8192 atoms need the cluster path (not built yet)");
+    return fail("igmk_run: no MD kernel for this structure size");
 }
 
 extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
@@ -1237,7 +1259,7 @@ k_single_point_noalloc(const __grid_constant__ NoallocArgs a)
     B.bond_ptr = a.bond_ptr; B.bond_items = a.bond_items; B.btype_f = nullptr; B.btype_d = a.btype;
     B.nl = (uint16_t*)a.scratch; B.nl_width = NOALLOC_NL_WIDTH;
     B.nl_cnt = (uint16_t*)(a.scratch + NOALLOC_NL_BYTES);
-    B.xd = nullptr; B.fd = nullptr; B.work = nullptr; B.res = nullptr; B.flags = nullptr;
+    B.xd = nullptr; B.fd = nullptr; B.work = nullptr; B.big = nullptr; B.res = nullptr; B.flags = nullptr;
     Ctx<T> c;
     ctx_carve<T>(c, smem, d->n_atoms, false, (T*)(a.scratch + NOALLOC_NL_BYTES + NOALLOC_CNT_BYTES));
     ctx_bind(c, B, d);

@@ -55,6 +55,7 @@ struct Batch {
     double*   xd;            // [atoms*3] double coordinates (CG)
     double*   fd;            // [atoms*3] double forces (single point / CG output)
     double*   work;          // [atoms*12] CG vectors h, g, x0 + neighbour-build coordinates
+    double*   big;           // [(atoms + 32*n_struct)*10] state of structures too large for shared memory (or NULL)
     igmk_result_t* res;      // [n_struct]
     int32_t*  flags;         // [n_struct] bit0: neighbour overflow, bit1: non-finite
 };
@@ -480,35 +481,68 @@ struct Ctx {
 // shared-memory carve-up -----------------------------------------------------------------
 // float: everything in shared memory.  double (single point / CG): the coordinates of the last
 // neighbour build go to global memory so that 2 Mb diploid structures still fit one CTA.
+// Structures too large for that (ctx_is_big: > ~3500 atoms in double, e.g. the 30 k beads of a 200 kb
+// genome) keep positions, forces and build coordinates in a global scratch area of 10 values per
+// atom instead; only the cell grid and the reduction scratch stay in shared memory.
+constexpr size_t CTX_SMEM_LIMIT = 227 * 1024;
+
 template <typename T>
-__host__ __device__ inline size_t ctx_smem_bytes(int n_atoms, bool with_velocity)
+__host__ __device__ inline size_t ctx_smem_fixed(int n_atoms)
 {
     const size_t np = (size_t)((n_atoms + 31) / 32 * 32);
     size_t b = 0;
-    b += np * 4 * sizeof(T);                 // x
-    b += np * 3 * sizeof(T);                 // f
-    if (sizeof(T) == 4) b += np * 3 * sizeof(T);   // build coordinates
-    if (with_velocity) b += np * 3 * sizeof(T);
     b += 2 * 256 * sizeof(T);                // reduction scratch
     b += IGMK_MAX_ENVELOPES * 4 * sizeof(T); // envelope parameters
     b += 64 * sizeof(int);                   // int scratch
     b += ((size_t)MAX_CELLS + 2) * 2;        // cell_start
     b += (np + MAX_CELLS + 2) * 2;           // cell_atoms + cursors
     b += np * 2;                             // cell_of
-    return (b + 255) / 256 * 256;
+    return b;
 }
 
 template <typename T>
-__device__ inline T* ctx_carve(Ctx<T>& c, unsigned char* smem, int n_atoms, bool with_velocity, T* gbuild)
+__host__ __device__ inline size_t ctx_smem_state(int n_atoms, bool with_velocity)
+{
+    const size_t np = (size_t)((n_atoms + 31) / 32 * 32);
+    size_t b = np * 4 * sizeof(T) + np * 3 * sizeof(T);      // x, f
+    if (sizeof(T) == 4) b += np * 3 * sizeof(T);             // build coordinates
+    if (with_velocity) b += np * 3 * sizeof(T);
+    return b;
+}
+
+template <typename T>
+__host__ __device__ inline bool ctx_is_big(int n_atoms, bool with_velocity)
+{
+    return (ctx_smem_fixed<T>(n_atoms) + ctx_smem_state<T>(n_atoms, with_velocity) + 255) / 256 * 256 > CTX_SMEM_LIMIT;
+}
+
+template <typename T>
+__host__ __device__ inline size_t ctx_smem_bytes(int n_atoms, bool with_velocity)
+{
+    size_t b = ctx_smem_fixed<T>(n_atoms);
+    if (!ctx_is_big<T>(n_atoms, with_velocity)) b += ctx_smem_state<T>(n_atoms, with_velocity);
+    return (b + 255) / 256 * 256;
+}
+
+// gbig: this structure's global scratch (10 doubles per atom, Batch::big), used in big mode only
+template <typename T>
+__device__ inline T* ctx_carve(Ctx<T>& c, unsigned char* smem, int n_atoms, bool with_velocity, T* gbuild, double* gbig = nullptr)
 {
     const size_t np = (size_t)((n_atoms + 31) / 32 * 32);
     unsigned char* p = smem;
-    c.x = (typename Ctx<T>::V4*)p; p += np * 4 * sizeof(T);
-    c.fx = (T*)p; c.fy = c.fx + np; c.fz = c.fy + np; p += np * 3 * sizeof(T);
-    if (sizeof(T) == 4) { c.bx = (T*)p; c.by = c.bx + np; c.bz = c.by + np; p += np * 3 * sizeof(T); }
-    else { c.bx = gbuild; c.by = gbuild + n_atoms; c.bz = gbuild + 2 * (size_t)n_atoms; }
     T* vel = nullptr;
-    if (with_velocity) { vel = (T*)p; p += np * 3 * sizeof(T); }
+    if (ctx_is_big<T>(n_atoms, with_velocity)) {
+        T* g = (T*)gbig;
+        c.x = (typename Ctx<T>::V4*)g; g += np * 4;
+        c.fx = g; c.fy = c.fx + np; c.fz = c.fy + np; g += np * 3;
+        c.bx = g; c.by = c.bx + np; c.bz = c.by + np;
+    } else {
+        c.x = (typename Ctx<T>::V4*)p; p += np * 4 * sizeof(T);
+        c.fx = (T*)p; c.fy = c.fx + np; c.fz = c.fy + np; p += np * 3 * sizeof(T);
+        if (sizeof(T) == 4) { c.bx = (T*)p; c.by = c.bx + np; c.bz = c.by + np; p += np * 3 * sizeof(T); }
+        else { c.bx = gbuild; c.by = gbuild + n_atoms; c.bz = gbuild + 2 * (size_t)n_atoms; }
+        if (with_velocity) { vel = (T*)p; p += np * 3 * sizeof(T); }
+    }
     c.rbuf = (T*)p; p += 2 * 256 * sizeof(T);
     c.envp = (T*)p; p += IGMK_MAX_ENVELOPES * 4 * sizeof(T);
     c.ibuf = (int*)p; p += 64 * sizeof(int);
@@ -544,7 +578,8 @@ k_single_point(Batch B, double ev_scale, double env_scale, double bond_pref)
     extern __shared__ __align__(16) unsigned char smem[];
     const StructDesc* d = B.desc + blockIdx.x;
     Ctx<T> c;
-    ctx_carve<T>(c, smem, d->n_atoms, false, (T*)(B.work + (size_t)d->atom_off * 12 + (size_t)d->n_atoms * 9));
+    ctx_carve<T>(c, smem, d->n_atoms, false, (T*)(B.work + (size_t)d->atom_off * 12 + (size_t)d->n_atoms * 9),
+                 B.big ? B.big + ((size_t)d->atom_off + 32 * (size_t)blockIdx.x) * 10 : nullptr);
     ctx_bind(c, B, d);
     c.set_stage(ev_scale, env_scale);
     c.bond_pref = T(bond_pref);
@@ -594,7 +629,8 @@ k_cg(Batch B, igmk_protocol_t pr)
     extern __shared__ __align__(16) unsigned char smem[];
     const StructDesc* d = B.desc + blockIdx.x;
     Ctx<T> c;
-    ctx_carve<T>(c, smem, d->n_atoms, false, B.work + (size_t)d->atom_off * 12 + (size_t)d->n_atoms * 9);
+    ctx_carve<T>(c, smem, d->n_atoms, false, B.work + (size_t)d->atom_off * 12 + (size_t)d->n_atoms * 9,
+                 B.big ? B.big + ((size_t)d->atom_off + 32 * (size_t)blockIdx.x) * 10 : nullptr);
     ctx_bind(c, B, d);
     const int n = c.n, tid = threadIdx.x, nt = blockDim.x;
     // unfix exVolAdapt restored A (scale 1); the last stage's envelope fix stays defined

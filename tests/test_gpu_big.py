@@ -1,0 +1,116 @@
+"""Structures beyond one SM's shared memory (BASELINE config 4 territory: 200 kb genomes): the
+global-memory MD kernel (md_big.cuh) and the global-state mode of the float64 single point / CG."""
+import numpy as np
+import pytest
+
+from igm_b200 import synth
+from igm_b200.kernel import MStepBatch
+from oracle import ff
+from helpers import small_system, short_protocol
+
+pytestmark = pytest.mark.gpu
+
+
+def _big_system(n_chain=10, chain=950, seed=3):
+    g = synth.Genome([chain] * n_chain, n_autosomes=0)          # 9500 beads: K = 10 slots, above every 1-CTA limit
+    R = 6000.0
+    rad = synth.bead_radii(len(g), R, 0.3)
+    rng = np.random.default_rng(seed)
+    xyz = synth.territories(g, R, rng)
+    hi = rng.integers(0, len(g), 3000)
+    hj = (hi + rng.integers(1, len(g) - 1, 3000)) % len(g)
+    return g, rad, synth.pack_structure(xyz, rad, g, hi, hj, np.full(3000, 4.0 * float(rad[0])), nucleus_radius=R, seed=5)
+
+
+def test_big_md_kernel_follows_the_small_one(monkeypatch):
+    """the same small structures through k_md2 and, forced, through k_md_big: the same trajectory up to
+    float32 round-off (different instruction selection: 1 ulp after 2 steps, then chaos takes over),
+    and the big kernel reproduces itself bit for bit"""
+    g, rad, systems = small_system(seed=41, n_struct=3)
+    prot = short_protocol(md=5, relax=0)
+    prot.n_stage = 1
+    prot.skip_minimize = 1
+    out = []
+    for force in (False, True, True):
+        if force:
+            monkeypatch.setenv("IGMK_FORCE_BIG", "1")
+        with MStepBatch(0) as b:
+            slots = [b.submit(ps) for ps in systems]
+            b.run(prot)
+            out.append([b.fetch(s) for s in slots])
+    for (a, ra), (c, rc), (e, _) in zip(*out):
+        assert np.abs(a - c).max() <= 1e-3 and ra.n_rebuilds == rc.n_rebuilds
+        assert np.array_equal(c.view(np.uint32), e.view(np.uint32))
+
+
+def test_single_point_and_cg_beyond_shared_memory():
+    g, rad, ps = _big_system()
+    f_ref, e_ref = ff.single_point(ps)
+    prot = short_protocol()
+    prot.n_stage = 0
+    prot.max_cg_iter = 12; prot.max_cg_eval = 40
+    with MStepBatch(0) as b:
+        slot = b.submit(ps)
+        b.single_point()
+        _, res = b.fetch(slot)
+        f = b.fetch_forces(slot)
+        assert res.final_energy == pytest.approx(e_ref["total"], rel=1e-10)
+        assert np.abs(f - f_ref).max() <= 1e-10 * np.abs(f_ref).max()
+        b.single_point(f32=True)
+        _, res32 = b.fetch(slot)
+        assert res32.final_energy == pytest.approx(e_ref["total"], rel=2e-4)
+        b.run(prot)                                   # CG only
+        xyz, res = b.fetch(slot)
+    x_ref, r_ref = ff.optimize(ps, prot)
+    assert (res.cg_iters, res.cg_evals, res.cg_stop) == (r_ref.cg_iters, r_ref.cg_evals, r_ref.cg_stop)
+    assert res.final_energy == pytest.approx(r_ref.final_energy, rel=1e-8)
+
+
+def test_big_structure_full_protocol():
+    g, rad, ps = _big_system(seed=4)
+    _, e0 = ff.single_point(ps)
+    prot = short_protocol(md=150, relax=30)
+    with MStepBatch(0) as b:
+        slot = b.submit(ps)
+        b.run(prot)
+        xyz, res = b.fetch(slot)
+        br, _ = b.violation_ratios(slot)
+    assert res.status == 0 and np.isfinite(xyz).all()
+    assert res.final_energy < 0.05 * e0["total"]
+    assert res.final_energy == pytest.approx(res.pair_energy + res.bond_energy + res.env_energy[0], rel=1e-9)
+    assert np.all(xyz[len(g)] == 0.0)
+    # the energies reported are those of the returned coordinates (checked with the oracle)
+    ps2 = synth.pack_structure(xyz[:len(g)], rad, g, ps.bond_i[ps.bond_i.size - 3000:], ps.bond_j[ps.bond_j.size - 3000:],
+                               ps.bond_r0[ps.bond_r0.size - 3000:], nucleus_radius=6000.0)
+    _, e1 = ff.single_point(ps2)
+    assert e1["total"] == pytest.approx(res.final_energy, rel=1e-3, abs=1.0)
+
+
+def test_config4_size_200kb_genome():
+    """hg38 male at 200 kb: 29 838 beads (BASELINE config 4).  Single point vs the oracle at full size
+    and a few hundred MD steps + CG through the global-memory path."""
+    g = synth.genome_200kb()
+    assert len(g) == 29838
+    R = 5500.0
+    rad = synth.bead_radii(len(g), R, 0.4)
+    rng = np.random.default_rng(2)
+    xyz = synth.territories(g, R, rng)
+    hi = rng.integers(0, len(g), 20000)
+    hj = (hi + rng.integers(1, 50, 20000)) % len(g)
+    ps = synth.pack_structure(xyz, rad, g, hi, hj, np.full(20000, 4.0 * float(rad[0])), nucleus_radius=R, seed=9)
+    f_ref, e_ref = ff.single_point(ps)
+    prot = short_protocol(md=40, relax=10)
+    prot.max_cg_iter = 5; prot.max_cg_eval = 15
+    with MStepBatch(0) as b:
+        slot = b.submit(ps)
+        b.single_point()
+        _, res = b.fetch(slot)
+        f = b.fetch_forces(slot)
+        assert res.final_energy == pytest.approx(e_ref["total"], rel=1e-10)
+        assert np.abs(f - f_ref).max() <= 1e-10 * np.abs(f_ref).max()
+        b.run(prot)
+        xyz2, res = b.fetch(slot)
+        md_ms, cg_ms, _ = b.last_timings()
+    assert res.status == 0 and np.isfinite(xyz2).all() and res.final_energy < e_ref["total"]
+    print("200 kb structure: %.1f ms for %d MD force evaluations, CG %.1f ms for %d evaluations"
+          % (md_ms, 4 * (40 + 10 + 2), cg_ms, res.cg_evals))
