@@ -194,27 +194,31 @@ def build_workload(args, rank, world, device, log):
         astep["assign_e2e_ms"] = min(et) * 1e3
         astep["rows"] = int(row.size)
         astep["assign_bytes"] = float(row.size) * (24.0 * S + 12.0 + 4.0 * ((S + 31) // 32))
-    # bits -> per-structure Hi-C bonds (HarmonicUpperBound(i, j, contact_range*(ri+rj), k), inter_hic.py:55-62)
-    t1 = time.time()
+    # bits -> per-structure Hi-C bonds (HarmonicUpperBound(i, j, contact_range*(ri+rj), k), inter_hic.py:55-62):
+    # done for the whole population by igmk_submit_population; a few structures are also packed here in
+    # Python for the CPU baseline and the flop count
     r0_all = (2.0 * (rad[row] + rad[col])).astype(np.float64)
+    n_py = min(S, max(os.cpu_count() or 1, 16))
     systems = []
-    nb = []
-    for s in range(S):
+    for s in range(n_py):
         m = ((bits[:, s >> 5] >> np.uint32(s & 31)) & np.uint32(1)).astype(bool)
         systems.append(synth.pack_structure(crd[:, s, :], rad, g, row[m], col[m], r0_all[m], nucleus_radius=NUCLEUS_R,
                                             seed=7 + rank * S + s, struct_id=rank * S + s))
-        nb.append(int(m.sum()))
-    log("A-step: %d pairs -> %d rows; actdist %.2f ms, assign %.2f ms (kernels); %.0f Hi-C bonds/structure; "
-        "host bond build %.1f s" % (pi.size, row.size, astep["actdist_kernel_ms"], astep["assign_kernel_ms"],
-                                    np.mean(nb), time.time() - t1))
+    nbonds = float(np.bitwise_count(bits).sum()) / S if hasattr(np, "bitwise_count") else float(np.unpackbits(bits.view(np.uint8)).sum()) / S
+    log("A-step: %d pairs -> %d rows; actdist %.2f ms, assign %.2f ms (kernels); %.0f Hi-C bonds/structure"
+        % (pi.size, row.size, astep["actdist_kernel_ms"], astep["assign_kernel_ms"], nbonds))
     cnts = np.sort(np.bincount(np.concatenate([systems[0].bond_i, systems[0].bond_j]), minlength=3072))[::-1]
     cnts = np.concatenate([cnts, np.zeros((-cnts.size) % 32, dtype=cnts.dtype)]).reshape(-1, 32)
     log("bond items of structure 0: %d real, %d after sliced-ELL padding, longest row %d"
         % (cnts.sum(), 32 * cnts.max(axis=1).sum(), cnts.max()))
     astep["pairs_total"] = int(pi.size)
     astep["sigma"] = sigma
-    astep["hic_bonds_per_structure"] = float(np.mean(nb))
-    return {"genome": g, "radii": rad, "systems": systems, "crd": crd, "astep": astep, "prot": prot, "opts": opts}
+    astep["hic_bonds_per_structure"] = nbonds
+    template = synth.pack_structure(np.zeros((n, 3), dtype=np.float32), rad, g, nucleus_radius=NUCLEUS_R, seed=0, struct_id=rank * S)
+    seeds = (7 + rank * S + np.arange(S)).astype(np.int64)
+    return {"genome": g, "radii": rad, "systems": systems, "crd": crd, "astep": astep, "prot": prot, "opts": opts,
+            "template": template, "seeds": seeds, "rows": (row, col, dst, r0_all), "bits": bits, "pairs": (pi, pj, pw, pl),
+            "sigma": sigma}
 
 
 def cpu_mstep_baseline(systems, prot, n_sample, threads):
@@ -286,7 +290,12 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % device))
     wl = build_workload(args, rank, world, device, log)
     systems, prot = wl["systems"], wl["prot"]
-    S = len(systems)
+    S = args.structures
+    g, rad, crd = wl["genome"], wl["radii"], wl["crd"]
+    row, col, dst, r0_all = wl["rows"]
+
+    def submit_all(b):
+        b.submit_population(wl["template"], crd, len(g), row, col, r0_all, 1.0, wl["bits"], seeds=wl["seeds"])
 
     def barrier():
         if world > 1:
@@ -295,8 +304,7 @@ def main():
 
     # ---- value: batch resident in HBM, K steps inside ONE timed region --------------------
     batch = MStepBatch(device)
-    for ps in systems:
-        batch.submit(ps)
+    submit_all(batch)
     batch.upload()
     md_ms, cg_ms = [], []
     for _ in range(args.warmup):
@@ -320,25 +328,52 @@ def main():
     cg_evals = float(np.mean([batch.fetch(k)[1].cg_evals for k in range(S)]))
     h2d = batch.last_timings()[2]
     # ---- e2e: host buffers through the C ABI every step -------------------------------------
-    d2h = sum(ps.n_atoms for ps in systems) * 16 + S * 136
+    d2h = S * (len(g) + 1) * 16 + S * 136
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         batch.clear()
-        for ps in systems:
-            batch.submit(ps)
+        submit_all(batch)
         batch.run(prot)
         out = [batch.fetch(k) for k in range(S)]
     torch.cuda.synchronize(device)
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
     del out
+    # ---- one full A/M iteration from host coordinates: upload -> all-gather -> activation distances
+    #      (this rank's pair chunk) -> gather rows -> assignment -> bond build + submit -> M-step -> fetch ----
+    from igm_b200.astep import Population
+    pi, pj, pw, pl = wl["pairs"]
+    lo_p, hi_p = parallel.pair_shards(parallel.pair_cost(pi, pj, g.chrom, g.copy_off), world)[rank]
+    barrier()
+    t0 = time.perf_counter()
+    local_t = torch.from_numpy(crd).to("cuda:%d" % device)
+    slab_t = parallel.all_gather_slab(local_t)
+    with Population(S * world, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as popg:
+        popg.attach(slab_t)
+        rows_it = popg.actdist(pi[lo_p:hi_p], pj[lo_p:hi_p], pw[lo_p:hi_p], pl[lo_p:hi_p], 2.0)
+    rows_it = parallel.all_gather_rows(rows_it, device="cuda:%d" % device)
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as popl:
+        popl.attach(local_t)
+        bits_it = popl.assign(rows_it[0], rows_it[1], rows_it[2])
+    t_astep = time.perf_counter() - t0
+    batch.clear()
+    batch.submit_population(wl["template"], crd, len(g), rows_it[0], rows_it[1],
+                            (2.0 * (rad[rows_it[0]] + rad[rows_it[1]])).astype(np.float64), 1.0, bits_it, seeds=wl["seeds"])
+    t_build = time.perf_counter() - t0 - t_astep
+    batch.run(prot)
+    new_crd = np.empty_like(crd)
+    for k in range(S):
+        new_crd[:, k, :] = batch.fetch(k)[0][:len(g)]
+    torch.cuda.synchronize(device)
+    iter_s = time.perf_counter() - t0
     batch.close()
 
     tt = torch.tensor([ms_step, e2e_ms, wl["astep"]["actdist_kernel_ms"], wl["astep"]["actdist_e2e_ms"],
-                       wl["astep"]["assign_kernel_ms"], wl["astep"]["assign_e2e_ms"]], dtype=torch.float64, device="cuda:%d" % device)
+                       wl["astep"]["assign_kernel_ms"], wl["astep"]["assign_e2e_ms"], iter_s, t_astep, t_build],
+                      dtype=torch.float64, device="cuda:%d" % device)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_step, e2e_ms, ad_k, ad_e, as_k, as_e = [float(v) for v in tt.tolist()]
+    ms_step, e2e_ms, ad_k, ad_e, as_k, as_e, iter_s, t_astep, t_build = [float(v) for v in tt.tolist()]
     if rank == 0:
         peaks = {}
         try:
@@ -369,6 +404,10 @@ def main():
             "e2e": {"value": S * world / (e2e_ms * 1e-3), "unit": "structures/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": 2 * args.steps,
+            "am_iteration": {"seconds": iter_s, "structures_per_s": S * world / iter_s, "astep_seconds": t_astep,
+                             "bond_build_and_submit_seconds": t_build,
+                             "what": "host coordinates -> upload, all-gather, activation distances, row gather, assignment, "
+                                     "bond build + submit, annealing MD + CG, coordinates back on the host"},
             "clocks": clocks,
             "roofline": {"bound": "fp32", "kernel": "k_md", "achieved": md_tflops, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
                          "frac": md_tflops / FP32_PEAK_TFLOPS, "traffic": None, "flops_per_force_eval": feval,

@@ -178,6 +178,9 @@ _SIGNATURES = {
     "igmk_destroy": (C.c_int, [_vp]),
     "igmk_clear": (C.c_int, [_vp]),
     "igmk_submit": (C.c_int, [_vp, C.POINTER(System), c_i32p]),
+    "igmk_submit_population": (C.c_int, [_vp, C.POINTER(System), C.c_int32, C.c_int32, C.c_int32, C.c_int32, c_f32p, C.c_int64,
+                                         c_i32p, c_i32p, c_f64p, C.c_double, c_u32p, C.c_int32, c_i64p, c_i32p]),
+    "igmk_slot_sizes": (C.c_int, [_vp, C.c_int32, c_i32p, c_i64p, c_i64p]),
     "igmk_upload": (C.c_int, [_vp]),
     "igmk_reset_coordinates": (C.c_int, [_vp]),
     "igmk_run": (C.c_int, [_vp, C.POINTER(Protocol)]),

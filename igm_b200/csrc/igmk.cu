@@ -10,6 +10,7 @@
 #include <map>
 #include <tuple>
 #include <algorithm>
+#include <thread>
 #include <cuda_runtime.h>
 
 #include "../../include/igmk.h"
@@ -289,6 +290,100 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
     return 0;
 }
 
+// ---- whole population from a template + the assignment bit matrix ---------------------------
+static void append_handle(igmk_handle* dst, igmk_handle* src)
+{
+    const int32_t A = (int32_t)dst->xyzr.size(), BP = (int32_t)dst->bond_ptr.size(), BT = (int32_t)dst->btype_f.size();
+    const int64_t BI = (int64_t)dst->bond_items.size(), SB = (int64_t)dst->sub_bonds.size(), SE = (int64_t)dst->sub_env.size();
+    for (auto d : src->desc) { d.atom_off += A; d.bond_ptr_off += BP; d.bond_item_off += BI; d.btype_off += BT; dst->desc.push_back(d); }
+    for (auto v : src->sub_bond_atom_off) dst->sub_bond_atom_off.push_back(v + A);
+    for (auto m : src->sub_env) { m.atom += A; dst->sub_env.push_back(m); }
+    for (auto v : src->sub_bond_start) dst->sub_bond_start.push_back(v + SB);
+    for (auto v : src->sub_env_start) dst->sub_env_start.push_back(v + SE);
+    dst->xyzr.insert(dst->xyzr.end(), src->xyzr.begin(), src->xyzr.end());
+    dst->xyzr0.insert(dst->xyzr0.end(), src->xyzr0.begin(), src->xyzr0.end());
+    dst->kind.insert(dst->kind.end(), src->kind.begin(), src->kind.end());
+    dst->envmask.insert(dst->envmask.end(), src->envmask.begin(), src->envmask.end());
+    dst->bond_ptr.insert(dst->bond_ptr.end(), src->bond_ptr.begin(), src->bond_ptr.end());
+    dst->bond_items.insert(dst->bond_items.end(), src->bond_items.begin(), src->bond_items.end());
+    dst->btype_f.insert(dst->btype_f.end(), src->btype_f.begin(), src->btype_f.end());
+    dst->btype_d.insert(dst->btype_d.end(), src->btype_d.begin(), src->btype_d.end());
+    dst->struct_id.insert(dst->struct_id.end(), src->struct_id.begin(), src->struct_id.end());
+    dst->sub_bonds.insert(dst->sub_bonds.end(), src->sub_bonds.begin(), src->sub_bonds.end());
+    dst->max_atoms = std::max(dst->max_atoms, src->max_atoms);
+    dst->dirty = true; dst->viol_valid = false;
+}
+
+extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t n_bead, int32_t n_struct_total,
+                                      int32_t s_begin, int32_t n_struct, const float* crd,
+                                      int64_t n_rows, const int32_t* row, const int32_t* col, const double* row_r0, double row_k,
+                                      const uint32_t* bits, int32_t bits_words, const int64_t* seeds, int32_t* first_slot_out)
+{
+    if (!h || !tmpl || !crd) return fail("igmk_submit_population: NULL argument");
+    if (n_bead < 1 || n_bead > tmpl->n_atoms) return fail("igmk_submit_population: n_bead must be 1..tmpl->n_atoms");
+    if (n_struct < 0 || s_begin < 0 || s_begin + n_struct > n_struct_total) return fail("igmk_submit_population: bad structure range");
+    if (n_rows > 0 && (!row || !col || !row_r0 || !bits)) return fail("igmk_submit_population: NULL row arguments");
+    if (n_rows > 0 && bits_words * 32 < n_struct) return fail("igmk_submit_population: bit matrix narrower than the structure range");
+    for (int64_t r = 0; r < n_rows; r++)
+        if (row[r] < 0 || row[r] >= n_bead || col[r] < 0 || col[r] >= n_bead) return fail("igmk_submit_population: row bead index out of range");
+    if (first_slot_out) *first_slot_out = (int32_t)h->desc.size();
+    if (n_struct == 0) return 0;
+    // rows of every structure, in row order: one pass over the set bits (bit s of word s/32 = local structure s)
+    std::vector<std::vector<int32_t>> mine((size_t)n_struct);
+    for (int64_t r = 0; r < n_rows; r++) {
+        const uint32_t* w = bits + (size_t)r * bits_words;
+        for (int k = 0; k * 32 < n_struct; k++) {
+            uint32_t m = w[k];
+            while (m) {
+                const int b = __builtin_ctz(m); m &= m - 1;
+                const int sl = k * 32 + b;
+                if (sl < n_struct) mine[sl].push_back((int32_t)r);
+            }
+        }
+    }
+    const int nthr = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), (unsigned)n_struct));
+    std::vector<igmk_handle*> part((size_t)nthr, nullptr);
+    std::vector<std::string> errs((size_t)nthr);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthr; t++) {
+        part[t] = new igmk_handle();
+        part[t]->smem_optin = h->smem_optin;
+        pool.emplace_back([&, t]() {
+            const int lo = (int)((int64_t)n_struct * t / nthr), hi = (int)((int64_t)n_struct * (t + 1) / nthr);
+            const int na = tmpl->n_atoms;
+            std::vector<float> xyz((size_t)na * 3);
+            std::vector<int32_t> bi, bj; std::vector<double> bk, br; std::vector<uint8_t> bs;
+            for (int sl = lo; sl < hi; sl++) {
+                const int sg = s_begin + sl;
+                for (int a = 0; a < n_bead; a++) {
+                    const float* src = crd + ((size_t)a * n_struct_total + sg) * 3;
+                    xyz[3 * a] = src[0]; xyz[3 * a + 1] = src[1]; xyz[3 * a + 2] = src[2];
+                }
+                for (int a = n_bead; a < na; a++) { xyz[3 * a] = tmpl->xyz[3 * a]; xyz[3 * a + 1] = tmpl->xyz[3 * a + 1]; xyz[3 * a + 2] = tmpl->xyz[3 * a + 2]; }
+                bi.assign(tmpl->bond_i, tmpl->bond_i + tmpl->n_bonds); bj.assign(tmpl->bond_j, tmpl->bond_j + tmpl->n_bonds);
+                bk.assign(tmpl->bond_k, tmpl->bond_k + tmpl->n_bonds); br.assign(tmpl->bond_r0, tmpl->bond_r0 + tmpl->n_bonds);
+                bs.assign(tmpl->bond_style, tmpl->bond_style + tmpl->n_bonds);
+                for (int32_t r : mine[sl]) {           // HarmonicUpperBound((row, col), r0, k), inter_hic.py:55-62
+                    bi.push_back(row[r]); bj.push_back(col[r]); bk.push_back(row_k); br.push_back(row_r0[r]); bs.push_back(IGMK_BOND_UPPER);
+                }
+                igmk_system_t sys = *tmpl;
+                sys.xyz = xyz.data();
+                sys.n_bonds = (int32_t)bi.size();
+                sys.bond_i = bi.data(); sys.bond_j = bj.data(); sys.bond_k = bk.data(); sys.bond_r0 = br.data(); sys.bond_style = bs.data();
+                sys.seed = seeds ? seeds[sl] : tmpl->seed;
+                sys.struct_id = tmpl->struct_id + sg;
+                if (igmk_submit(part[t], &sys, nullptr)) { errs[t] = igmk_last_error(); return; }
+            }
+        });
+    }
+    for (auto& th : pool) th.join();
+    int rc = 0;
+    for (int t = 0; t < nthr; t++) if (!errs[t].empty() && !rc) rc = fail(errs[t]);
+    if (!rc) for (int t = 0; t < nthr; t++) append_handle(h, part[t]);
+    for (int t = 0; t < nthr; t++) delete part[t];
+    return rc;
+}
+
 // slots per thread the MD kernel is instantiated for
 static int md2_pick_K(int max_atoms)
 {
@@ -420,6 +515,17 @@ extern "C" int igmk_upload(igmk_handle_t* h)
     if (h->desc.empty()) return fail("igmk_upload: nothing submitted");
     CU(cudaSetDevice(h->device));
     return upload(h);
+}
+
+extern "C" int igmk_slot_sizes(igmk_handle_t* h, int32_t slot, int32_t* n_atoms, int64_t* n_bonds, int64_t* n_env_members)
+{
+    if (!h) return fail("igmk_slot_sizes: NULL handle");
+    if (slot < 0 || slot >= (int)h->desc.size()) return fail("igmk_slot_sizes: bad slot");
+    const bool last = slot + 1 >= (int)h->desc.size();
+    if (n_atoms) *n_atoms = h->desc[slot].n_atoms;
+    if (n_bonds) *n_bonds = (last ? (int64_t)h->sub_bonds.size() : h->sub_bond_start[slot + 1]) - h->sub_bond_start[slot];
+    if (n_env_members) *n_env_members = (last ? (int64_t)h->sub_env.size() : h->sub_env_start[slot + 1]) - h->sub_env_start[slot];
+    return 0;
 }
 
 // M10: violation ratios of every submitted restraint at the batch's current coordinates

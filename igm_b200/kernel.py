@@ -82,6 +82,29 @@ class MStepBatch(object):
         self._packed.append(packed)
         return slot.value
 
+    def submit_population(self, template, crd, n_bead, row, col, row_r0, row_k, bits, s_begin=0, n_struct=None, seeds=None):
+        """Submit structures ``s_begin .. s_begin+n_struct-1`` of the .hss-layout slab ``crd``
+        ([n_bead][S][3] float32): every structure = ``template`` (a PackedSystem: shared particles and
+        restraints) with the slab's coordinates and a HarmonicUpperBound per actdist row whose bit is set
+        in ``bits`` (the matrix Population.assign returned for exactly these structures).  -> first slot."""
+        crd = np.ascontiguousarray(crd, dtype=np.float32)
+        S = crd.shape[1]
+        if n_struct is None:
+            n_struct = S - s_begin
+        r = np.ascontiguousarray(row, dtype=np.int32)
+        c = np.ascontiguousarray(col, dtype=np.int32)
+        r0 = np.ascontiguousarray(row_r0, dtype=np.float64)
+        b = np.ascontiguousarray(bits, dtype=np.uint32).reshape(r.size, -1) if r.size else np.zeros((0, 1), dtype=np.uint32)
+        sd = None if seeds is None else np.ascontiguousarray(seeds, dtype=np.int64)
+        first = C.c_int32(-1)
+        _abi.check(self._lib.igmk_submit_population(
+            self._h, C.byref(template.c), int(n_bead), int(S), int(s_begin), int(n_struct), crd.ctypes.data_as(_abi.c_f32p),
+            r.size, r.ctypes.data_as(_abi.c_i32p), c.ctypes.data_as(_abi.c_i32p), r0.ctypes.data_as(_abi.c_f64p), float(row_k),
+            b.ctypes.data_as(_abi.c_u32p), int(b.shape[1]), None if sd is None else sd.ctypes.data_as(_abi.c_i64p),
+            C.byref(first)), "igmk_submit_population")
+        self._packed.extend([template] * n_struct)        # sizes for fetch(); bond arrays differ per structure
+        return first.value
+
     def upload(self):
         _abi.check(self._lib.igmk_upload(self._h), "igmk_upload")
 
@@ -95,8 +118,14 @@ class MStepBatch(object):
         fn = self._lib.igmk_single_point_f32 if f32 else self._lib.igmk_single_point
         _abi.check(fn(self._h, float(ev_scale), float(env_scale), float(bond_prefactor)), "igmk_single_point")
 
+    def slot_sizes(self, slot):
+        """-> (n_atoms, n_bonds, n_envelope_members) of a submitted structure"""
+        a, b, e = C.c_int32(0), C.c_int64(0), C.c_int64(0)
+        _abi.check(self._lib.igmk_slot_sizes(self._h, slot, C.byref(a), C.byref(b), C.byref(e)), "igmk_slot_sizes")
+        return a.value, b.value, e.value
+
     def fetch(self, slot):
-        n = self._packed[slot].n_atoms
+        n = self.slot_sizes(slot)[0]
         xyz = np.empty((n, 3), dtype=np.float32)
         res = _abi.Result()
         _abi.check(self._lib.igmk_fetch(self._h, slot, xyz.ctypes.data_as(_abi.c_f32p), C.byref(res)), "igmk_fetch")
@@ -105,9 +134,9 @@ class MStepBatch(object):
     def violation_ratios(self, slot):
         """-> (bond_ratio f8 [n_bonds] in submit order, env_u f8 [sum of envelope members]) at the
         current coordinates; see igmk_violation_ratios in include/igmk.h."""
-        ps = self._packed[slot]
-        br = np.zeros(ps.bond_i.size, dtype=np.float64)
-        eu = np.zeros(ps.env_members.size, dtype=np.float64)
+        _, nb, ne = self.slot_sizes(slot)
+        br = np.zeros(nb, dtype=np.float64)
+        eu = np.zeros(ne, dtype=np.float64)
         _abi.check(self._lib.igmk_violation_ratios(self._h, slot, br.ctypes.data_as(_abi.c_f64p), eu.ctypes.data_as(_abi.c_f64p)),
                    "igmk_violation_ratios")
         return br, eu
@@ -119,7 +148,7 @@ class MStepBatch(object):
         return a.value, b.value, c.value
 
     def fetch_forces(self, slot):
-        n = self._packed[slot].n_atoms
+        n = self.slot_sizes(slot)[0]
         f = np.empty((n, 3), dtype=np.float64)
         _abi.check(self._lib.igmk_fetch_forces(self._h, slot, f.ctypes.data_as(_abi.c_f64p)), "igmk_fetch_forces")
         return f

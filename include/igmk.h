@@ -124,6 +124,24 @@ int igmk_destroy(igmk_handle_t* h);
 int igmk_clear(igmk_handle_t* h);
 /* copies the structure into the batch; *slot_out indexes it in fetch calls */
 int igmk_submit(igmk_handle_t* h, const igmk_system_t* sys, int32_t* slot_out);
+/*
+ * Submit structures s_begin .. s_begin+n_struct-1 of a population in one call: what n_struct
+ * ModelingStep.task calls assemble one by one (igm/steps/ModelingStep.py:184-264).  `tmpl` holds what
+ * all structures share (particles incl. dummies, Steric / Envelope / Polymer restraints); the first
+ * n_bead atoms take their coordinates from the .hss-layout slab `crd` [n_bead][n_struct_total][3]
+ * (host), the others keep tmpl->xyz.  On top, structure s gets HarmonicUpperBound((row[r], col[r]),
+ * row_r0[r], row_k) for every actdist row r whose bit (s - s_begin) is set in bits[r]
+ * (`bits_words` words per row: the matrix igmk_pop_assign returns for a population of those
+ * structures; inter_hic.py:53-62, intra_hic.py:54-63).  seeds[k] (or tmpl->seed) and
+ * tmpl->struct_id + s identify structure s.  Multi-threaded on the host.
+ */
+int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t n_bead,
+                           int32_t n_struct_total, int32_t s_begin, int32_t n_struct, const float* crd,
+                           int64_t n_rows, const int32_t* row, const int32_t* col, const double* row_r0,
+                           double row_k, const uint32_t* bits, int32_t bits_words, const int64_t* seeds,
+                           int32_t* first_slot_out);
+/* sizes of a submitted structure (any pointer may be NULL) */
+int igmk_slot_sizes(igmk_handle_t* h, int32_t slot, int32_t* n_atoms, int64_t* n_bonds, int64_t* n_env_members);
 /* host -> device copy of everything submitted (what writing + re-reading the .data
  * file is in the reference, lammps.py:430-431); igmk_run does it implicitly if needed */
 int igmk_upload(igmk_handle_t* h);

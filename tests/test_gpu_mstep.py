@@ -185,3 +185,51 @@ def test_optimize_raises_runtime_error_with_model_id():
            "runtime": {"step_no": 0}}
     with pytest.raises(RuntimeError, match="modelid: 12"):
         optimize(m, cfg)
+
+
+def test_submit_population_equals_per_structure_submits():
+    """igmk_submit_population (template + slab + assignment bits) builds the same batch as one
+    igmk_submit per structure: identical single points and bit-identical optimised coordinates"""
+    from igm_b200.astep import Population
+    from oracle import astep_oracle as ao
+    g = synth.Genome([14, 11, 8, 6], n_autosomes=3)
+    R = 1400.0
+    rad = synth.bead_radii(len(g), R, 0.3)
+    S = 37
+    crd = synth.population_territories(g, S, R=R, seed=12)
+    pi, pj, pw = synth.hic_pairs(g, 0.004, seed=3)
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads) as pop:
+        pop.upload(crd)
+        row, col, dist, _ = pop.actdist(pi, pj, pw, np.zeros(pi.size), 2.0)
+        bits = pop.assign(row, col, dist)
+    mask = ao.assign(crd, row, col, dist)
+    r0 = (2.0 * (rad[row] + rad[col])).astype(np.float64)
+    tmpl = synth.pack_structure(np.zeros((len(g), 3), dtype=np.float32), rad, g, nucleus_radius=R, seed=0, struct_id=100)
+    seeds = np.arange(S, dtype=np.int64) + 5
+    prot = short_protocol(md=150, relax=30)
+    with MStepBatch(0) as a, MStepBatch(0) as b:
+        first = a.submit_population(tmpl, crd, len(g), row, col, r0, 1.0, bits, seeds=seeds)
+        assert first == 0 and len(a) == S
+        for s in range(S):
+            m = mask[:, s]
+            b.submit(synth.pack_structure(crd[:, s, :], rad, g, row[m], col[m], r0[m], nucleus_radius=R, seed=int(seeds[s]),
+                                          struct_id=100 + s))
+        assert all(a.slot_sizes(s) == b.slot_sizes(s) for s in range(S))
+        assert mask.sum() > 50 and sum(a.slot_sizes(s)[1] for s in range(S)) == S * tmpl.bond_i.size + int(mask.sum())
+        a.single_point(); b.single_point()
+        e_sp = [b.fetch(s)[1].final_energy for s in range(S)]
+        for s in range(S):
+            assert a.fetch(s)[1].final_energy == e_sp[s]
+        a.run(prot); b.run(prot)
+        for s in range(S):
+            xa, ra = a.fetch(s); xb, rb = b.fetch(s)
+            assert np.array_equal(xa.view(np.uint32), xb.view(np.uint32)) and ra.final_energy == rb.final_energy
+        # a sub-range of the population with its own bit matrix
+        with Population(10, rad, g.chrom, g.copy_off, g.copy_beads) as pop2, MStepBatch(0) as c:
+            sub = np.ascontiguousarray(crd[:, 20:30, :])
+            pop2.upload(sub)
+            bits2 = pop2.assign(row, col, dist)
+            c.submit_population(tmpl, crd, len(g), row, col, r0, 1.0, bits2, s_begin=20, n_struct=10, seeds=seeds[20:30])
+            c.single_point()
+            for k in range(10):
+                assert c.fetch(k)[1].final_energy == e_sp[20 + k]
