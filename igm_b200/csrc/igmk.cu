@@ -74,7 +74,7 @@ struct igmk_handle {
     std::vector<int32_t>  md2_ell_off;
     std::vector<uint32_t> md2_ell_items;
     Md2Desc* d_md2_desc = nullptr; uint16_t* d_md2_perm = nullptr; int32_t* d_md2_ell_off = nullptr;
-    uint32_t* d_md2_ell_items = nullptr; uint16_t* d_md2_nl = nullptr;
+    uint32_t* d_md2_ell_items = nullptr; uint32_t* d_md2_ell_act = nullptr; uint16_t* d_md2_nl = nullptr;
     bool md_big = false; float* d_big_state = nullptr; double* d_big = nullptr;
     bool dirty = true;
     // device
@@ -96,7 +96,7 @@ struct igmk_handle {
         cudaFree(d_bond_items); cudaFree(d_btype_f); cudaFree(d_btype_d); cudaFree(d_nl); cudaFree(d_nl_cnt);
         cudaFree(d_xd); cudaFree(d_fd); cudaFree(d_work); cudaFree(d_res); cudaFree(d_flags);
         cudaFree(d_big_state); cudaFree(d_big); d_big_state = nullptr; d_big = nullptr;
-        cudaFree(d_md2_desc); cudaFree(d_md2_perm); cudaFree(d_md2_ell_off); cudaFree(d_md2_ell_items); cudaFree(d_md2_nl);
+        cudaFree(d_md2_desc); cudaFree(d_md2_perm); cudaFree(d_md2_ell_off); cudaFree(d_md2_ell_items); cudaFree(d_md2_ell_act); cudaFree(d_md2_nl); d_md2_ell_act = nullptr;
         d_md2_desc = nullptr; d_md2_perm = nullptr; d_md2_ell_off = nullptr; d_md2_ell_items = nullptr; d_md2_nl = nullptr;
         d_desc = nullptr; d_xyzr = nullptr; d_xyzr0 = nullptr; d_kind = nullptr; d_envmask = nullptr; d_bond_ptr = nullptr;
         d_bond_items = nullptr; d_btype_f = nullptr; d_btype_d = nullptr; d_nl = nullptr; d_nl_cnt = nullptr;
@@ -498,6 +498,7 @@ static int upload(igmk_handle* h)
         CU(dev_alloc_copy(&h->d_md2_perm, h->md2_perm));
         CU(dev_alloc_copy(&h->d_md2_ell_off, h->md2_ell_off));
         CU(dev_alloc_copy(&h->d_md2_ell_items, h->md2_ell_items));
+        CU(cudaMalloc((void**)&h->d_md2_ell_act, std::max<size_t>(h->md2_ell_items.size(), 1) * sizeof(uint32_t)));
         CU(cudaMalloc((void**)&h->d_md2_nl, h->md2_perm.size() * (size_t)h->md2_nlw * sizeof(uint16_t)));
     }
     h->h2d_bytes = ns * sizeof(StructDesc) + 2 * na * sizeof(float4) + na * (sizeof(uint8_t) + sizeof(uint32_t)) +
@@ -632,7 +633,7 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
     CU(cudaFuncSetAttribute(k_md2<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     Md2View V;
     V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
-    V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw;
+    V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.ell_act = h->d_md2_ell_act;
     V.prof = nullptr;
     const bool prof = getenv("IGMK_PROF") != nullptr;
     if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 4 * sizeof(long long))); CU(cudaMemset(V.prof, 0, (size_t)ns * 4 * sizeof(long long))); }
@@ -657,7 +658,7 @@ static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
         CU(cudaFuncSetAttribute(k_md_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         Md2View V;
         V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
-        V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.prof = nullptr;
+        V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.prof = nullptr; V.ell_act = h->d_md2_ell_act;
         k_md_big<<<ns, MD2_T, sm>>>(B, V, h->d_md2_desc, P, h->d_big_state);
         CU(cudaGetLastError());
         return 0;

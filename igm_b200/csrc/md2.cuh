@@ -25,6 +25,7 @@ struct Md2View {
     const uint16_t* perm;      // [sum np] position -> original atom (0xffff: empty position)
     const int32_t*  ell_off;   // per structure: 32*K+1 offsets (in items) of each warp-slot block
     const uint32_t* ell_items; // sliced-ELL bond items
+    uint32_t*       ell_act;   // same size: the items that can be active before the next rebuild (k_md2 scratch)
     uint16_t*       nl;        // [sum np * nl_width] column-major per structure
     int32_t         nl_width;
     long long*      prof;      // optional [n_struct][4] SM cycles: force loops, integration, rebuilds, total (IGMK_PROF=1)
@@ -61,6 +62,7 @@ __host__ __device__ inline size_t md2_smem_bytes(int K)
     b += np * 2 * 2;                          // cell_atoms, cell_of
     b += 2 * 32 * 8 * 4;                      // reduction scratch
     b += IGMK_MAX_ENVELOPES * 4 * 4;          // envelope parameters
+    b += (size_t)K * 32 * 4;                  // active bond batches per warp-slot
     return (b + 255) / 256 * 256;
 }
 
@@ -83,10 +85,12 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     uint16_t* cell_of = cell_atoms + np;
     float* rbuf = (float*)(cell_of + np);
     float* envp = rbuf + 2 * 256;
+    int* bact = (int*)(envp + IGMK_MAX_ENVELOPES * 4);      // [K][32] batches of candidate bond items per warp-slot
     int rb_par = 0;
 
     const igmk_protocol_t& pr = P.prot;
     const uint16_t* perm = V.perm + md.perm_off;
+    uint32_t* eact = V.ell_act + md.ell_item_off;
     const int32_t* eoff = V.ell_off + md.ell_desc_off;
     const uint32_t* eitems = V.ell_items + md.ell_item_off;
     uint16_t* nl = V.nl + (size_t)md.perm_off * V.nl_width;
@@ -124,6 +128,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     const float bond_pref2 = 2.f * (float)pr.bond_prefactor;
     float ev_c = -1.f;                 // evfactor * stage scale / pi  (force prefactor / rc), < 0: no sterics
     int n_rebuild = 0, overflow = 0;
+    bool bond_build = true;
     long long t_search = 0;
     __syncthreads();
 
@@ -145,6 +150,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         __syncthreads();
     };
 
+    const uint32_t xs = (uint32_t)__cvta_generic_to_shared(x);
     // ---- neighbour table: cell binning in shared memory, every thread fills its own rows ----
     auto rebuild = [&]() {
         float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
@@ -301,6 +307,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         }
         overflow |= __syncthreads_or(ovf);
         t_search += clock64() - ts0;
+        bond_build = true;        // the next force evaluation also refreshes the bond candidate list
         n_rebuild++;
     };
 
@@ -308,7 +315,6 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     // Rows of the neighbour table are padded with the atom's own index to a multiple of 4 and the bond
     // blocks with self-bonds of type 0: a self pair has r2 = 0 and contributes nothing, so the inner
     // loops need no bounds or validity tests and run branch-free.
-    const uint32_t xs = (uint32_t)__cvta_generic_to_shared(x);
     auto forces = [&]() {
 #pragma unroll
         for (int k = 0; k < K; k++) {
@@ -338,8 +344,16 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             }
             // harmonic upper / lower bounds: F = -2 pref k (r - r0) r_hat when violated
             {
-                const uint4* it = (const uint4*)(eitems + boff[k]) + lane;     // [batch][lane][4 items]
-                const int nb4 = bcols[k] >> 2;
+                // Bond candidates.  No atom moves more than skin/2 before the next rebuild, so no pair distance
+                // changes by more than skin: an upper bound with r < r0 - skin (a lower bound with r > r0 + skin)
+                // stays inactive until then.  The first evaluation after a rebuild walks the full list and
+                // writes the candidates (original order kept) to `eact`; the others walk only those.  In a
+                // converged population most restraints are satisfied with room to spare.
+                const bool build = bond_build;
+                const uint4* it = (const uint4*)((build ? eitems : eact) + boff[k]) + lane;   // [batch][lane][4 items]
+                const int nb4 = build ? (bcols[k] >> 2) : bact[k * 32 + warp];
+                uint32_t* out = eact + boff[k] + (lane << 2);
+                int ccnt = 0;
                 uint4 nxt = nb4 > 0 ? it[0] : make_uint4(0, 0, 0, 0);
                 for (int c = 0; c < nb4; c++) {
                     const uint4 cur = nxt;
@@ -358,7 +372,16 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                         float fb = -bond_pref2 * fabsf(t.y) * (1.f - t.x * fast_rsqrt(r2));
                         fb = act ? fb : 0.f;
                         ax += dx * fb; ay += dy * fb; az += dz * fb;
+                        if (build) {
+                            const float lo = fmaxf(t.x - skin, 0.f), hi = t.x + skin;
+                            if (t.y > 0.f ? (r2 > lo * lo) : (r2 < hi * hi)) { out[((ccnt >> 2) << 7) + (ccnt & 3)] = v[u]; ccnt++; }
+                        }
                     }
+                }
+                if (build) {
+                    const int most = warp_max((ccnt + 3) >> 2);
+                    for (int cc = ccnt; cc < (most << 2); cc++) out[((cc >> 2) << 7) + (cc & 3)] = (uint32_t)p;   // self-bond padding
+                    if (lane == 0) bact[k * 32 + warp] = most;
                 }
             }
             // fix ellipsoidalenvelope
@@ -376,6 +399,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             if (kind[k] != IGMK_KIND_BEAD && kind[k] != IGMK_KIND_CENTROID) { ax = 0.f; ay = 0.f; az = 0.f; }   // frozen / empty
             fx[k] = ax; fy[k] = ay; fz[k] = az;
         }
+        bond_build = false;
     };
 
     // ------------------------------------------------------------------------------------
