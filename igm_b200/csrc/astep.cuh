@@ -160,8 +160,11 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
 // keeps its 4 * SPT squared distances in registers, the bitwise descent stops as soon as the bucket
 // that holds the wanted order statistic has at most 32 members, and one warp ranks those directly.
 // Same arithmetic, same results as k_actdist; roughly 4x fewer instructions per pair.
+#ifndef AD_REG_MIN_BLOCKS
+#define AD_REG_MIN_BLOCKS 4
+#endif
 template <int SPT>
-__global__ void __launch_bounds__(AD_THREADS)
+__global__ void __launch_bounds__(AD_THREADS, AD_REG_MIN_BLOCKS)
 k_actdist_reg(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const int32_t* __restrict__ pair_j,
               const double* __restrict__ pwish, const double* __restrict__ plast, float contact_range_f32,
               float* __restrict__ out_dist, float* __restrict__ out_prob, uint8_t* __restrict__ out_valid)

@@ -233,3 +233,29 @@ def test_submit_population_equals_per_structure_submits():
             c.single_point()
             for k in range(10):
                 assert c.fetch(k)[1].final_energy == e_sp[20 + k]
+
+
+def test_config3_restraint_set_through_md(ff_golden):
+    """2 Mb structure with every restraint kind of BASELINE config 3 at once (Hi-C-like upper bounds, lower
+    bounds, an ellipsoidal k<0 lamina envelope, bonds to the static centre as radial FISH uses them, a
+    SPRITE centroid): the MD + CG path runs it, lowers the energy, repeats itself bit for bit, and its
+    reported energies are those of the returned coordinates."""
+    ps = demo_structure(ff_golden, 8, n_extra_bonds=3000)
+    prot = short_protocol(md=120, relax=30)
+    outs = []
+    for rep in range(2):
+        with MStepBatch(0) as b:
+            slot = b.submit(ps)
+            b.single_point()
+            e0 = b.fetch(slot)[1].final_energy
+            b.reset_coordinates()
+            b.run(prot)
+            outs.append(b.fetch(slot))
+    (xa, ra), (xb, rb) = outs
+    assert np.array_equal(xa.view(np.uint32), xb.view(np.uint32)) and ra.final_energy == rb.final_energy
+    assert ra.status == 0 and ra.n_env == 2 and ra.final_energy < e0
+    assert np.all(xa[3008] == 0.0) and not np.array_equal(xa[3009], ps.xyz[3009])      # dummy fixed, centroid moved
+    ps.xyz[:] = xa
+    _, e = ff.single_point(ps)
+    assert e["total"] == pytest.approx(ra.final_energy, rel=1e-4)
+    assert e["env"][1] == pytest.approx(ra.env_energy[1], rel=1e-3, abs=1e-3 * abs(e["total"]))
