@@ -210,5 +210,10 @@ def optimize_population(models, cfg, device=None):
 
 
 def optimize(model, cfg):
-    """Drop-in for ``igm.model.kernel.lammps.optimize`` (lammps.py:361)."""
+    """Drop-in for ``igm.model.kernel.lammps.optimize`` (lammps.py:361).  Under
+    ``igm_b200.controller.B200Controller`` concurrent calls are gathered into one launch."""
+    from .controller import current_batcher
+    batcher = current_batcher()
+    if batcher is not None:
+        return batcher.optimize(model, cfg)
     return optimize_population([model], cfg)[0]

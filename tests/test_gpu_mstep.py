@@ -259,3 +259,26 @@ def test_config3_restraint_set_through_md(ff_golden):
     _, e = ff.single_point(ps)
     assert e["total"] == pytest.approx(ra.final_energy, rel=1e-4)
     assert e["env"][1] == pytest.approx(ra.env_energy[1], rel=1e-3, abs=1e-3 * abs(e["total"]))
+
+
+def test_controller_batches_real_optimize_calls():
+    """ModelingStep-style tasks under B200Controller: one launch, same results as optimize_population"""
+    from igm_b200.controller import B200Controller
+    opts = synth.demo_protocol_options()
+    opts["custom_annealing_protocol"]["mdsteps"] = [60, 60, 60, 60]
+    opts["custom_annealing_protocol"]["relax"]["mdsteps"] = 10
+    cfg = {"optimization": {"kernel": "b200", "optimizer_options": opts, "kernel_opts": {"b200": {"seed": 77}}},
+           "runtime": {"step_no": 1}}
+
+    def task(i):
+        m, _ = _toy_model(i + 1, seed=20 + i)
+        info = optimize(m, cfg)
+        return np.array([p.pos for p in m.particles]), info["final-energy"]
+
+    ctl = B200Controller(max_threads=16)
+    out = ctl.map(task, range(6))
+    assert ctl.last_batcher.batches == [6]
+    models = [_toy_model(i + 1, seed=20 + i)[0] for i in range(6)]
+    infos = optimize_population(models, cfg)
+    for (xyz, e), m, info in zip(out, models, infos):
+        assert np.array_equal(xyz, np.array([p.pos for p in m.particles])) and e == info["final-energy"]
