@@ -230,7 +230,12 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
     std::vector<int32_t> btype_of((size_t)s->n_bonds);
     std::vector<std::tuple<double, double, int>> tkeys;
     std::vector<int64_t> tuse;
+    int last_t = -1;
     for (int b = 0; b < s->n_bonds; b++) {
+        if (last_t >= 0 && s->bond_r0[b] == s->bond_r0[b - 1] && s->bond_k[b] == s->bond_k[b - 1] && s->bond_style[b] == s->bond_style[b - 1]) {
+            tuse[last_t]++; btype_of[b] = last_t;       // runs of equal restraints (Hi-C, polymer) skip the map
+            continue;
+        }
         auto key = std::make_tuple(s->bond_r0[b], s->bond_k[b], (int)s->bond_style[b]);
         auto it = types.find(key);
         int t;
@@ -242,6 +247,7 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
         } else t = it->second;
         tuse[t]++;
         btype_of[b] = t;
+        last_t = t;
     }
     std::vector<int32_t> torder(tkeys.size()), tnew(tkeys.size());
     for (size_t t = 0; t < torder.size(); t++) torder[t] = (int32_t)t;
@@ -403,9 +409,9 @@ static void md2_build(igmk_handle* h)
     h->md2_desc.assign(ns, Md2Desc());
     h->md2_perm.assign(ns * (size_t)np, MD2_NONE);
     h->md2_ell_off.assign(ns * (size_t)(G + 1), 0);
-    h->md2_ell_items.clear();
-    std::vector<int> order, pos;
-    for (size_t s = 0; s < ns; s++) {
+    std::vector<std::vector<uint32_t>> items(ns);            // per structure, concatenated below
+    auto build_one = [&](size_t s) {
+        std::vector<int> order, pos;
         const StructDesc& d = h->desc[s];
         const int n = d.n_atoms;
         const int32_t* bp = h->bond_ptr.data() + d.bond_ptr_off;
@@ -427,10 +433,9 @@ static void md2_build(igmk_handle* h)
         Md2Desc& m = h->md2_desc[s];
         m.perm_off = (int32_t)(s * (size_t)np);
         m.ell_desc_off = (int32_t)(s * (size_t)(G + 1));
-        m.ell_item_off = (int64_t)h->md2_ell_items.size();
         m.K = K;
         int32_t* eoff = h->md2_ell_off.data() + m.ell_desc_off;
-        size_t base = h->md2_ell_items.size();
+        std::vector<uint32_t>& out = items[s];
         for (int gi = 0; gi < G; gi++) {           // blocks in (slot, warp) order = the order the kernel indexes them
             const int k = gi / 32, w = gi % 32;
             int cols = 0;
@@ -439,9 +444,9 @@ static void md2_build(igmk_handle* h)
                 if (a != MD2_NONE) cols = std::max(cols, bp[a + 1] - bp[a]);
             }
             cols = (cols + 3) / 4 * 4;                 // the kernel reads 4 columns at a time, unguarded
-            eoff[gi] = (int32_t)(h->md2_ell_items.size() - base);
-            h->md2_ell_items.resize(h->md2_ell_items.size() + (size_t)cols * 32, 0u);
-            uint32_t* blk = h->md2_ell_items.data() + base + eoff[gi];
+            eoff[gi] = (int32_t)out.size();
+            out.resize(out.size() + (size_t)cols * 32, 0u);
+            uint32_t* blk = out.data() + eoff[gi];
             // layout [batch of 4 columns][lane][4]: one 16-byte load per lane and batch
             auto at = [&](int c, int l) -> uint32_t& { return blk[((c >> 2) * 32 + l) * 4 + (c & 3)]; };
             for (int l = 0; l < 32; l++)               // padding = bond of type 0 to oneself: r = 0, no force
@@ -455,8 +460,24 @@ static void md2_build(igmk_handle* h)
                 }
             }
         }
-        eoff[G] = (int32_t)(h->md2_ell_items.size() - base);
-    }
+        eoff[G] = (int32_t)out.size();
+    };
+    const int nthr = (int)std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), ns));
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthr; t++)
+        pool.emplace_back([&, t]() { for (size_t s = (size_t)t; s < ns; s += (size_t)nthr) build_one(s); });
+    for (auto& th : pool) th.join();
+    size_t total = 0;
+    for (size_t s = 0; s < ns; s++) { h->md2_desc[s].ell_item_off = (int64_t)total; total += items[s].size(); }
+    h->md2_ell_items.resize(total);
+    pool.clear();
+    for (int t = 0; t < nthr; t++)
+        pool.emplace_back([&, t]() {
+            for (size_t s = (size_t)t; s < ns; s += (size_t)nthr)
+                if (!items[s].empty())
+                    memcpy(h->md2_ell_items.data() + h->md2_desc[s].ell_item_off, items[s].data(), items[s].size() * sizeof(uint32_t));
+        });
+    for (auto& th : pool) th.join();
 }
 
 static int upload(igmk_handle* h)
