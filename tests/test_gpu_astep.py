@@ -108,3 +108,52 @@ def test_bad_indices_are_rejected(astep_golden):
             pop.actdist([0], [10 ** 6], [0.5], [0.0])
         with pytest.raises(RuntimeError, match="out of range"):
             pop.assign([0], [10 ** 6], [1.0])
+
+
+def test_full_size_population_properties():
+    """BASELINE configs[1] size (3008 beads x 1000 structures): properties that need no CPU replay of
+    the whole batch -- the emitted distance IS the o-th order statistic of the pair's squared distances
+    (checked in numpy on a sample), launches repeat bit for bit, and splitting the pair list (what the
+    multi-GPU path does) changes nothing."""
+    g = synth.genome_2mb()
+    rad = synth.bead_radii(len(g))
+    S = 1000
+    crd = synth.population_territories(g, S, seed=77)
+    pi, pj, pw = synth.hic_pairs(g, 0.02, seed=5)
+    pl = np.zeros(pi.size)
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads) as pop:
+        pop.upload(crd)
+        a = pop.actdist(pi, pj, pw, pl, 2.0)
+        b = pop.actdist(pi, pj, pw, pl, 2.0)
+        assert _bits_equal(a, b) and a[0].size > 10000
+        cut = pi.size // 3
+        parts = [pop.actdist(pi[s], pj[s], pw[s], pl[s], 2.0) for s in (slice(0, cut), slice(cut, None))]
+        assert _bits_equal(a, tuple(np.concatenate([p[k] for p in parts]) for k in range(4)))
+        bits = pop.assign(a[0], a[1], a[2])
+        assert np.array_equal(bits, pop.assign(a[0], a[1], a[2]))
+    # order-statistic property on a sample of pairs, from first principles
+    rng = np.random.default_rng(0)
+    checked = 0
+    for q in rng.choice(pi.size, 400, replace=False):
+        i, j = int(pi[q]), int(pj[q])
+        rows = np.nonzero((a[0] == g.copy_index[i][0]) & (a[1] == g.copy_index[j][0]))[0]
+        if rows.size == 0:
+            continue                                   # corrected probability was 0: no row emitted
+        dist, prob = float(a[2][rows[0]]), float(a[3][rows[0]])
+        ii, jj = g.copy_index[i], g.copy_index[j]
+        pairs = list(zip(ii, jj)) if g.chrom[i] == g.chrom[j] else [(x, y) for x in ii for y in jj]
+        d2 = np.concatenate([((crd[x] - crd[y]) ** 2).sum(axis=1) for x, y in pairs]).astype(np.float64)
+        n = d2.size
+        # prob and dist went through a 4-decimal text round trip: bracket the rank accordingly
+        below = np.count_nonzero(np.sqrt(d2) <= dist - 1e-3)
+        upto = np.count_nonzero(np.sqrt(d2) <= dist + 1e-3)
+        o_lo, o_hi = int(np.floor(n * (prob - 6e-5))) - 1, int(np.ceil(n * (prob + 6e-5))) + 1
+        assert below <= o_hi + 1 and upto >= min(o_lo, n - 1) + 1, (i, j, below, upto, o_lo, o_hi)
+        checked += 1
+    assert checked > 40
+    # assignment bits: a structure is assigned iff its distance is within the activation distance
+    mask = unpack_bits(bits[:200], S)
+    for r in range(0, 200, 7):
+        d = np.sqrt(((crd[a[0][r]].astype(np.float64) - crd[a[1][r]]) ** 2).sum(axis=1))
+        sure_in, sure_out = d < a[2][r] - 1e-2, d > a[2][r] + 1e-2
+        assert mask[r][sure_in].all() and not mask[r][sure_out].any()
