@@ -58,6 +58,8 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
     float* dsq = (float*)smem_raw;
     __shared__ int s_red[2][AD_THREADS / 32];
     __shared__ uint32_t s_mm[2][AD_THREADS / 32];
+    __shared__ uint32_t s_fin[32];
+    __shared__ int s_nfin;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = P.n_struct;
 
@@ -124,12 +126,14 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
 
         // ---- exact o-th smallest (A3): MSB-first descent over the float bit patterns.
         //      All keys share the bits above the highest bit in which min and max differ.
+        //      The descent stops once the bucket holding the wanted rank has at most 32 members; one warp ranks those.
         uint32_t prefix, k = (uint32_t)o;
-        int bit;
+        int bit, remaining = total;
         if (kmin == kmax) { prefix = kmin; bit = -1; }
         else { bit = 31 - __clz(kmin ^ kmax); prefix = (bit == 31) ? 0u : (kmin >> (bit + 1)) << (bit + 1); }
         int par = 1;
-        for (; bit >= 0; bit--) {
+        if (tid == 0) s_nfin = 0;
+        for (; bit >= 0 && remaining > 32; bit--) {
             const uint32_t hmask = (bit == 31) ? 0u : (0xffffffffu << (bit + 1));
             int c0 = 0;                                   // keys matching the prefix with this bit clear
             for (int q = tid; q < total; q += AD_THREADS) {
@@ -144,7 +148,28 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
 #pragma unroll
             for (int w = 0; w < AD_THREADS / 32; w++) c0 += s_red[par][w];
             par ^= 1;
-            if (k >= (uint32_t)c0) { k -= (uint32_t)c0; prefix |= (1u << bit); }
+            if (k >= (uint32_t)c0) { k -= (uint32_t)c0; prefix |= (1u << bit); remaining -= c0; }
+            else remaining = c0;
+        }
+        if (bit >= 0) {
+            const uint32_t hmask = (bit == 31) ? 0u : (0xffffffffu << (bit + 1));
+            __syncthreads();                              // s_nfin = 0 is visible
+            for (int q = tid; q < total; q += AD_THREADS) {
+                const uint32_t key = fkey(dsq[q]);
+                if ((key & hmask) == prefix) s_fin[atomicAdd(&s_nfin, 1)] = key;
+            }
+            __syncthreads();
+            if (warp == 0) {
+                const uint32_t mine = lane < remaining ? s_fin[lane] : 0xffffffffu;
+                int rank = 0;
+#pragma unroll
+                for (int m = 0; m < 32; m++) {
+                    const uint32_t other = __shfl_sync(0xffffffffu, mine, m);
+                    rank += (other < mine) || (other == mine && m < lane);
+                }
+                const uint32_t hit = __ballot_sync(0xffffffffu, rank == (int)k && lane < remaining);
+                prefix = __shfl_sync(0xffffffffu, mine, __ffs(hit) - 1);
+            }
         }
         if (tid == 0) {
             const double ad = sqrt((double)__uint_as_float(prefix));            // :446
