@@ -341,32 +341,12 @@ def main():
     del out
     # ---- one full A/M iteration from host coordinates: upload -> all-gather -> activation distances
     #      (this rank's pair chunk) -> gather rows -> assignment -> bond build + submit -> M-step -> fetch ----
-    from igm_b200.astep import Population
-    pi, pj, pw, pl = wl["pairs"]
-    lo_p, hi_p = parallel.pair_shards(parallel.pair_cost(pi, pj, g.chrom, g.copy_off), world)[rank]
-    barrier()
-    t0 = time.perf_counter()
-    local_t = torch.from_numpy(crd).to("cuda:%d" % device)
-    slab_t = parallel.all_gather_slab(local_t)
-    with Population(S * world, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as popg:
-        popg.attach(slab_t)
-        rows_it = popg.actdist(pi[lo_p:hi_p], pj[lo_p:hi_p], pw[lo_p:hi_p], pl[lo_p:hi_p], 2.0)
-    rows_it = parallel.all_gather_rows(rows_it, device="cuda:%d" % device)
-    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as popl:
-        popl.attach(local_t)
-        bits_it = popl.assign(rows_it[0], rows_it[1], rows_it[2])
-    t_astep = time.perf_counter() - t0
-    batch.clear()
-    batch.submit_population(wl["template"], crd, len(g), rows_it[0], rows_it[1],
-                            (2.0 * (rad[rows_it[0]] + rad[rows_it[1]])).astype(np.float64), 1.0, bits_it, seeds=wl["seeds"])
-    t_build = time.perf_counter() - t0 - t_astep
-    batch.run(prot)
-    new_crd = np.empty_like(crd)
-    for k in range(S):
-        new_crd[:, k, :] = batch.fetch(k)[0][:len(g)]
-    torch.cuda.synchronize(device)
-    iter_s = time.perf_counter() - t0
+    from igm_b200.iteration import hic_iteration
     batch.close()
+    barrier()
+    it = hic_iteration(crd, g, rad, wl["template"], wl["pairs"], wl["opts"], device=device, seeds=wl["seeds"])
+    torch.cuda.synchronize(device)
+    iter_s, t_astep, t_build = it["timings"]["total_s"], it["timings"]["astep_s"], it["timings"]["bond_build_and_submit_s"]
 
     tt = torch.tensor([ms_step, e2e_ms, wl["astep"]["actdist_kernel_ms"], wl["astep"]["actdist_e2e_ms"],
                        wl["astep"]["assign_kernel_ms"], wl["astep"]["assign_e2e_ms"], iter_s, t_astep, t_build],

@@ -385,7 +385,18 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
     for (auto& th : pool) th.join();
     int rc = 0;
     for (int t = 0; t < nthr; t++) if (!errs[t].empty() && !rc) rc = fail(errs[t]);
-    if (!rc) for (int t = 0; t < nthr; t++) append_handle(h, part[t]);
+    if (!rc) {
+        size_t a = 0, bp = 0, bi = 0, sb = 0, se = 0;            // grow the destination once
+        for (int t = 0; t < nthr; t++) {
+            a += part[t]->xyzr.size(); bp += part[t]->bond_ptr.size(); bi += part[t]->bond_items.size();
+            sb += part[t]->sub_bonds.size(); se += part[t]->sub_env.size();
+        }
+        h->xyzr.reserve(h->xyzr.size() + a); h->xyzr0.reserve(h->xyzr0.size() + a); h->kind.reserve(h->kind.size() + a);
+        h->envmask.reserve(h->envmask.size() + a); h->bond_ptr.reserve(h->bond_ptr.size() + bp);
+        h->bond_items.reserve(h->bond_items.size() + bi); h->sub_bonds.reserve(h->sub_bonds.size() + sb);
+        h->sub_bond_atom_off.reserve(h->sub_bond_atom_off.size() + sb); h->sub_env.reserve(h->sub_env.size() + se);
+        for (int t = 0; t < nthr; t++) append_handle(h, part[t]);
+    }
     for (int t = 0; t < nthr; t++) delete part[t];
     return rc;
 }

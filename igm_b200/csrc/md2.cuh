@@ -4,12 +4,14 @@
 // (K slots per thread) of a host-chosen ordering in which the 32 atoms of a warp-slot have
 // similar bond counts.  Each thread gathers the complete force on its own atoms (no atomics, no
 // cross-lane reductions => bit-reproducible), and keeps their velocities and forces in registers.
-// Shared memory holds only what other threads read: the positions (float4 x,y,z,radius), plus the
-// coordinates of the last neighbour build and the cell grid used during a rebuild.
-// Lists are laid out so that a warp reads them with full 32-lane coalescing:
-//   * neighbour table   nl[c][p]   (uint16, column c of position p)  -- rebuilt in-kernel
-//   * bond items        ell[g][c][lane] (uint32 partner | type<<16) -- sliced ELL per warp-slot g
-// Both live in global memory and are streamed through L1/L2.
+// Shared memory holds only what other threads read: the positions (float4 x,y,z,radius), a copy of
+// them in cell order for the neighbour search, the coordinates of the last neighbour build and the
+// cell grid.  Lists are laid out so that a warp reads them with full 32-lane coalescing:
+//   * neighbour table   nl[batch][position][4]   (uint16; 4 neighbours per 8-byte load; rebuilt in-kernel)
+//   * bond items        ell[warp-slot][batch][lane][4] (uint32 partner | type<<16; 4 items per 16-byte load)
+//   * bond candidates   same layout, rewritten by the first force evaluation after every rebuild
+// They live in global memory and are streamed through L1/L2.  Rows are padded with self-references
+// (r = 0, no force) so that the inner loops carry no bounds tests.
 #pragma once
 #include "mstep.cuh"
 
@@ -19,7 +21,6 @@ constexpr int MD2_T = 1024;           // threads per CTA
 constexpr int MD2_KMAX = 8;           // slots per thread supported (n_atoms <= 8192 on the 1-CTA path)
 constexpr int MD2_NLW0 = 256;         // initial neighbour-table width (columns)
 constexpr uint16_t MD2_NONE = 0xffffu;
-constexpr uint32_t MD2_PAD = 0xffffffffu;
 
 struct Md2View {
     const uint16_t* perm;      // [sum np] position -> original atom (0xffff: empty position)

@@ -1,0 +1,74 @@
+"""One Hi-C A/M iteration on the GPU(s): what ``ActivationDistanceStep`` followed by ``ModelingStep``
+do for a population (bin/igm-run:99-131), minus the file system.
+
+    coordinates (this rank's structures, host)                      igm/steps/...
+      -> upload, all-gather of the slab on the structure axis       (workers read the .hss)
+      -> activation distances of this rank's chunk of the pairs     ActivationDistanceStep.task   :192-222
+      -> all-gather of the rows (= actdist.hdf5)                    ActivationDistanceStep.reduce :226-290
+      -> contact assignment for this rank's structures              inter/intraHiC._apply  inter_hic.py:49-64
+      -> structures = template + slab + assigned bonds              ModelingStep.task             :184-264
+      -> annealing MD + CG for all of them in one launch sequence   Model.optimize -> lammps.optimize
+      -> optimised coordinates, per-structure info, violation stats ModelingStep.task :341-382
+
+Single process: ranks = 1.  Several GPUs: one process per GPU under torch.distributed (NCCL); every
+rank passes its own contiguous block of structures (``parallel.structure_shard``).
+"""
+import time
+
+import numpy as np
+
+from . import _abi, parallel
+from .astep import Population
+from .kernel import MStepBatch, info_from_result
+
+
+def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, device=0, contact_range=2.0,
+                  k_hic=1.0, seeds=None, bond_prefactor=1.0, violations=False, tol=0.05):
+    """crd_local: float32 [n_bead][S_local][3] (host).  genome: object with chrom, copy_off, copy_beads.
+    template: PackedSystem of the shared particles and restraints (Steric, Envelope, Polymer).
+    pairs: (pair_i, pair_j, pwish, plast) haploid pairs kept at this sigma -- identical on every rank.
+    -> dict(coordinates [n_bead][S_local][3], infos [S_local], rows (row, col, dist, prob), timings,
+            violations = per-structure (n_imposed, n_violated) of the harmonic restraints if asked)."""
+    import torch
+    rank, ws = parallel.world()
+    n_bead, S = crd_local.shape[0], crd_local.shape[1]
+    t0 = time.perf_counter()
+    dev = "cuda:%d" % device
+    local_t = torch.from_numpy(np.ascontiguousarray(crd_local, dtype=np.float32)).to(dev)
+    slab_t = parallel.all_gather_slab(local_t)
+    pi, pj, pw, pl = pairs
+    with Population(slab_t.shape[1], radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popg:
+        popg.attach(slab_t)
+        rows = parallel.distributed_actdist(lambda a, b, c, d: popg.actdist(a, b, c, d, contact_range), pi, pj, pw, pl,
+                                            genome.chrom, genome.copy_off, device=dev)
+    row, col, dist, prob = rows
+    with Population(S, radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popl:
+        popl.attach(local_t)
+        bits = popl.assign(row, col, dist)
+    t_astep = time.perf_counter() - t0
+    r0 = (contact_range * (radii[row] + radii[col])).astype(np.float64)      # float32 product like inter_hic.py:55
+    protocol = _abi.make_protocol(optimizer_options, bond_prefactor=bond_prefactor)
+    out = {"rows": rows, "timings": {"astep_s": t_astep}}
+    with MStepBatch(device) as batch:
+        batch.submit_population(template, crd_local, n_bead, row, col, r0, k_hic, bits, seeds=seeds)
+        t_build = time.perf_counter() - t0 - t_astep
+        batch.run(protocol)
+        new = np.empty((n_bead, S, 3), dtype=np.float32)
+        infos = []
+        for k in range(S):
+            xyz, res = batch.fetch(k)
+            if res.status != 0 or not np.isfinite(res.final_energy):
+                raise RuntimeError("b200 kernel produced non-finite coordinates or energy (structure %d of rank %d)" % (k, rank))
+            new[:, k, :] = xyz[:n_bead]
+            infos.append(info_from_result(res))
+        if violations:
+            v = []
+            for k in range(S):
+                br, _ = batch.violation_ratios(k)
+                v.append((br.size, int(np.count_nonzero(br > tol))))
+            out["violations"] = v
+        md_ms, cg_ms, h2d = batch.last_timings()
+    out["coordinates"], out["infos"] = new, infos
+    out["timings"].update({"bond_build_and_submit_s": t_build, "md_kernel_ms": md_ms, "cg_kernel_ms": cg_ms,
+                           "h2d_bytes": h2d, "total_s": time.perf_counter() - t0})
+    return out
