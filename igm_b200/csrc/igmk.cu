@@ -415,7 +415,7 @@ static int md2_pick_K(int max_atoms)
 // gets a similar amount of bond work and the atoms of one warp-slot have similar row lengths.
 static void md2_build(igmk_handle* h)
 {
-    const int K = h->md2_K, np = K * MD2_T, G = K * 32;
+    const int K = h->md2_K, np = K * MD2_T, NW = MD2_NW, G = K * NW;
     const size_t ns = h->desc.size();
     h->md2_desc.assign(ns, Md2Desc());
     h->md2_perm.assign(ns * (size_t)np, MD2_NONE);
@@ -431,9 +431,9 @@ static void md2_build(igmk_handle* h)
         for (int a = 0; a < n; a++) order[a] = a;
         std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return bp[a + 1] - bp[a] > bp[b + 1] - bp[b]; });
         uint16_t* perm = h->md2_perm.data() + s * (size_t)np;
-        auto slot_of_group = [&](int g) { const int k = g / 32, r = g % 32; return k * 32 + ((k & 1) ? 31 - r : r); };
+        auto slot_of_group = [&](int g) { const int k = g / NW, r = g % NW; return k * NW + ((k & 1) ? NW - 1 - r : r); };
         for (int g = 0; g < G; g++) {
-            const int gi = slot_of_group(g), k = gi / 32, w = gi % 32;
+            const int gi = slot_of_group(g), k = gi / NW, w = gi % NW;
             for (int l = 0; l < 32; l++) {
                 const int q = g * 32 + l;
                 if (q >= n) break;
@@ -448,7 +448,7 @@ static void md2_build(igmk_handle* h)
         int32_t* eoff = h->md2_ell_off.data() + m.ell_desc_off;
         std::vector<uint32_t>& out = items[s];
         for (int gi = 0; gi < G; gi++) {           // blocks in (slot, warp) order = the order the kernel indexes them
-            const int k = gi / 32, w = gi % 32;
+            const int k = gi / NW, w = gi % NW;
             int cols = 0;
             for (int l = 0; l < 32; l++) {
                 const int a = perm[k * MD2_T + w * 32 + l];

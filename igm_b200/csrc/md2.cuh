@@ -17,7 +17,11 @@
 
 namespace igmk {
 
-constexpr int MD2_T = 1024;           // threads per CTA
+#ifndef MD2_THREADS
+#define MD2_THREADS 1024
+#endif
+constexpr int MD2_T = MD2_THREADS;    // threads per CTA
+constexpr int MD2_NW = MD2_T / 32;    // warps per CTA
 constexpr int MD2_KMAX = 8;           // slots per thread supported (n_atoms <= 8192 on the 1-CTA path)
 constexpr int MD2_NLW0 = 256;         // initial neighbour-table width (columns)
 constexpr uint16_t MD2_NONE = 0xffffu;
@@ -63,7 +67,7 @@ __host__ __device__ inline size_t md2_smem_bytes(int K)
     b += np * 2 * 2;                          // cell_atoms, cell_of
     b += 2 * 32 * 8 * 4;                      // reduction scratch
     b += IGMK_MAX_ENVELOPES * 4 * 4;          // envelope parameters
-    b += (size_t)K * 32 * 4;                  // active bond batches per warp-slot
+    b += (size_t)K * MD2_NW * 4;              // active bond batches per warp-slot
     return (b + 255) / 256 * 256;
 }
 
@@ -117,7 +121,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             emask[k] = B.envmask[d->atom_off + a];
         }
         x[p] = q;
-        const int g = k * 32 + warp;
+        const int g = k * MD2_NW + warp;
         boff[k] = eoff[g];
         bcols[k] = (eoff[g + 1] - eoff[g]) >> 5;
         vx[k] = vy[k] = vz[k] = 0.f; fx[k] = fy[k] = fz[k] = 0.f; ncnt[k] = 0;
@@ -139,7 +143,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         v = warp_sum(v);
         if (lane == 0) buf[warp] = v;
         __syncthreads();
-        return warp_sum(buf[lane]);          // MD2_T / 32 == 32 partials: one per lane, same tree in every warp
+        return warp_sum(lane < MD2_NW ? buf[lane] : 0.f);     // <= 32 partials: one per lane, same tree in every warp
     };
 
     auto set_stage = [&](double ev_scale, double env_scale) {
@@ -176,7 +180,9 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         for (int c = tid; c <= MAX_CELLS; c += MD2_T) cell_start[c] = 0;
         __syncthreads();
 #pragma unroll
-        for (int c = 0; c < 3; c++) { lo[c] = warp_min(rb[lane * 6 + c]); hi[c] = warp_max(rb[lane * 6 + 3 + c]); }
+        for (int c = 0; c < 3; c++) {
+            lo[c] = warp_min(lane < MD2_NW ? rb[lane * 6 + c] : 1e30f); hi[c] = warp_max(lane < MD2_NW ? rb[lane * 6 + 3 + c] : -1e30f);
+        }
         const float rlist = 2.f * d->maxrad + skin;
         int dim[3]; float inv[3];
 #pragma unroll
@@ -352,7 +358,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 // converged population most restraints are satisfied with room to spare.
                 const bool build = bond_build;
                 const uint4* it = (const uint4*)((build ? eitems : eact) + boff[k]) + lane;   // [batch][lane][4 items]
-                const int nb4 = build ? (bcols[k] >> 2) : bact[k * 32 + warp];
+                const int nb4 = build ? (bcols[k] >> 2) : bact[k * MD2_NW + warp];
                 uint32_t* out = eact + boff[k] + (lane << 2);
                 int ccnt = 0;
                 uint4 nxt = nb4 > 0 ? it[0] : make_uint4(0, 0, 0, 0);
@@ -382,7 +388,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 if (build) {
                     const int most = warp_max((ccnt + 3) >> 2);
                     for (int cc = ccnt; cc < (most << 2); cc++) out[((cc >> 2) << 7) + (cc & 3)] = (uint32_t)p;   // self-bond padding
-                    if (lane == 0) bact[k * 32 + warp] = most;
+                    if (lane == 0) bact[k * MD2_NW + warp] = most;
                 }
             }
             // fix ellipsoidalenvelope

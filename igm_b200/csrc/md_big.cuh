@@ -80,7 +80,7 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
         v = warp_sum(v);
         if (lane == 0) buf[warp] = v;
         __syncthreads();
-        return warp_sum(buf[lane]);
+        return warp_sum(lane < MD2_NW ? buf[lane] : 0.f);
     };
     auto mobile = [](uint32_t m) { const uint32_t kd = m & 0xffu; return kd == IGMK_KIND_BEAD || kd == IGMK_KIND_CENTROID; };
 
@@ -114,7 +114,9 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
         for (int c = tid; c < BIG_MAX_CELLS + 2; c += MD2_T) cell_start[c] = 0;
         __syncthreads();
 #pragma unroll
-        for (int c = 0; c < 3; c++) { lo[c] = warp_min(rb[lane * 6 + c]); hi[c] = warp_max(rb[lane * 6 + 3 + c]); }
+        for (int c = 0; c < 3; c++) {
+            lo[c] = warp_min(lane < MD2_NW ? rb[lane * 6 + c] : 1e30f); hi[c] = warp_max(lane < MD2_NW ? rb[lane * 6 + 3 + c] : -1e30f);
+        }
         const float rlist = 2.f * d->maxrad + skin;
         int dim[3]; float inv[3];
 #pragma unroll
@@ -242,7 +244,7 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
                 }
             }
             {
-                const int g = k * 32 + warp;
+                const int g = k * MD2_NW + warp;
                 const int bo = eoff[g], nb4 = (eoff[g + 1] - bo) >> 7;
                 const uint4* it = (const uint4*)(eitems + bo) + lane;
                 for (int c = 0; c < nb4; c++) {
