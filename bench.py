@@ -360,6 +360,11 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
+        traffic = {}
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        except Exception:
+            pass
         hbm = peaks.get("hbm_gbs", 6650.0)
         which = "measured" if "hbm_gbs" in peaks else "fallback"
         feval = flops_per_eval(systems, coords)
@@ -390,7 +395,12 @@ def main():
                                      "bond build + submit, annealing MD + CG, coordinates back on the host"},
             "clocks": clocks,
             "roofline": {"bound": "fp32", "kernel": "k_md", "achieved": md_tflops, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
-                         "frac": md_tflops / FP32_PEAK_TFLOPS, "traffic": None, "flops_per_force_eval": feval,
+                         "frac": md_tflops / FP32_PEAK_TFLOPS,
+                         "traffic": (traffic["k_md2<3>"]["dram_bytes"] / traffic["k_md2<3>"]["structures"] / traffic["k_md2<3>"]["force_evals"]
+                                     * S * evals) if "k_md2<3>" in traffic else None,
+                         "traffic_note": "scaled from a short ncu --set full capture (profiles/r01_traffic.json): bytes per structure and "
+                                         "force evaluation x this launch",
+                         "flops_per_force_eval": feval,
                          "kernel_ms": md_t * 1e3, "cg_kernel_ms": float(np.mean(cg_ms)),
                          "peak_source": "derived: 148 SM x 128 lanes x 2 x 1.965 GHz (non-tensor FP32; not in MEASURED_PEAKS.json)"},
             "astep": {"metric": "A-step haploid pairs/sec", "pairs": a["pairs_total"], "rows": a["rows"],
@@ -399,7 +409,11 @@ def main():
                       "actdist_kernel_ms": ad_k, "actdist_e2e_ms": ad_e, "assign_kernel_ms": as_k, "assign_e2e_ms": as_e,
                       "assign_rows_x_structures_per_s": a["rows"] * float(S) / (as_k * 1e-3)},
             "roofline_astep": {"bound": "hbm", "kernel": "k_actdist", "achieved": ad_gbs, "peak": hbm, "unit": "GB/s",
-                               "frac": ad_gbs / hbm, "traffic": None, "peak_source": which + " copy bandwidth",
+                               "frac": ad_gbs / hbm,
+                               "traffic": (traffic["k_actdist_reg<4>"]["dram_bytes"] / traffic["k_actdist_reg<4>"]["pairs"] * a["pairs_local"])
+                               if ("k_actdist_reg<4>" in traffic and S * world == 1000) else None,
+                               "traffic_note": "ncu --set full capture at 1000 structures scaled by pairs; the slab is L2 resident",
+                               "peak_source": which + " copy bandwidth",
                                "assign_achieved": as_gbs, "assign_frac": as_gbs / hbm},
         }
         if not args.no_cpu_baseline and world == 1:
