@@ -429,7 +429,11 @@ static void md2_build(igmk_handle* h)
         const uint32_t* bi = h->bond_items.data() + d.bond_item_off;
         order.resize(n); pos.assign(n, -1);
         for (int a = 0; a < n; a++) order[a] = a;
-        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return bp[a + 1] - bp[a] > bp[b + 1] - bp[b]; });
+        // Large structures (state in global memory) keep the sequence order: consecutive beads are neighbours in
+        // space, so the position gathers of a warp fall into fewer L2 sectors; small ones (state in shared memory)
+        // are ordered by bond count, which minimises the padding of the sliced-ELL blocks.
+        if (!h->md_big)
+            std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return bp[a + 1] - bp[a] > bp[b + 1] - bp[b]; });
         uint16_t* perm = h->md2_perm.data() + s * (size_t)np;
         auto slot_of_group = [&](int g) { const int k = g / NW, r = g % NW; return k * NW + ((k & 1) ? NW - 1 - r : r); };
         for (int g = 0; g < G; g++) {
