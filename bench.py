@@ -120,7 +120,7 @@ def build_workload(args, rank, world, device, log):
     import torch
     import torch.distributed as dist
     from igm_b200.kernel import MStepBatch
-    from igm_b200.astep import Population, unpack_bits
+    from igm_b200.astep import Population
 
     S = args.structures
     g = synth.genome_2mb()

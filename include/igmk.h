@@ -17,7 +17,9 @@
  * the row formatting/parsing at :39,:219-222,:241 and the contact-assignment
  * predicate of igm/restraints/inter_hic.py:49-64 / intra_hic.py:50-65):
  *     igmk_pop_create -> igmk_pop_upload -> igmk_pop_actdist
- *     -> igmk_pop_assign -> (igmk_pop_mstep) -> igmk_pop_download
+ *     -> igmk_pop_assign -> igmk_submit_population (M-step of the assigned population)
+ * and the sibling A-steps igmk_pop_damid_actdist / igmk_pop_damid_assign / igmk_pop_fish_ranks /
+ * igmk_pop_sprite_rg2 on the same population.
  */
 #ifndef IGMK_H
 #define IGMK_H

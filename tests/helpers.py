@@ -2,7 +2,7 @@
 import numpy as np
 
 from igm_b200 import synth
-from igm_b200._abi import PackedSystem, KIND_BEAD, KIND_STATIC, KIND_CENTROID, BOND_UPPER, BOND_LOWER
+from igm_b200._abi import PackedSystem, KIND_BEAD, KIND_STATIC, KIND_CENTROID, BOND_UPPER
 
 
 def demo_structure(ff_golden, k, n_extra_bonds=4000, seed=0, with_damid=True, with_centroid=True, evfactor=1.0,

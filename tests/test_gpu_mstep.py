@@ -4,7 +4,7 @@ arithmetic is deterministic: a run repeated on the GPU must reproduce itself bit
 import numpy as np
 import pytest
 
-from igm_b200 import synth, _abi
+from igm_b200 import synth
 from igm_b200.kernel import MStepBatch, optimize, optimize_population
 from oracle import ff
 from helpers import small_system, short_protocol, demo_structure

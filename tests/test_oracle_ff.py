@@ -4,7 +4,7 @@ run (demo/demo_sample_outputs/igm-model.hss.T -> tests/golden/ff_golden.npz)."""
 import numpy as np
 import pytest
 
-from igm_b200 import synth, _abi
+from igm_b200 import synth
 from oracle import ff
 from helpers import demo_structure, small_system, short_protocol
 

@@ -6,7 +6,6 @@ import socket
 import sys
 
 import numpy as np
-import pytest
 
 from conftest import ROOT
 from igm_b200 import parallel, synth
