@@ -282,3 +282,27 @@ def test_controller_batches_real_optimize_calls():
     infos = optimize_population(models, cfg)
     for (xyz, e), m, info in zip(out, models, infos):
         assert np.array_equal(xyz, np.array([p.pos for p in m.particles])) and e == info["final-energy"]
+
+
+@pytest.mark.parametrize("uniform", [True, False])
+def test_short_trajectory_matches_oracle(uniform):
+    """same Park-Miller velocity draws, same integrator: after a few steps of the first stage the float32
+    GPU trajectory still sits on the float64 oracle trajectory (both radius code paths of the MD kernel)"""
+    g, rad, systems = small_system(seed=51, n_struct=2)
+    if not uniform:
+        for ps in systems:
+            ps.radius[:len(g):3] *= np.float32(0.8)
+            ps.radius[1:len(g):5] *= np.float32(1.15)
+    prot = short_protocol(md=6, relax=0)
+    prot.n_stage = 1
+    prot.skip_minimize = 1
+    with MStepBatch(0) as b:
+        slots = [b.submit(ps) for ps in systems]
+        b.run(prot)
+        for ps, slot in zip(systems, slots):
+            xyz, res = b.fetch(slot)
+            x_ref, r_ref = ff.optimize(ps, prot)
+            moved = np.abs(x_ref - ps.xyz).max()
+            assert moved > 50.0                                     # T = 5000: the beads really travelled
+            assert np.abs(xyz - x_ref).max() <= 2e-3 * moved
+            assert res.temperature == pytest.approx(r_ref.temperature, rel=1e-3)
