@@ -22,6 +22,7 @@ __host__ __device__ inline size_t md_big_smem_bytes(int K)
     size_t b = ((size_t)BIG_MAX_CELLS + 2) * 4;   // cell_start
     b += np * 2 * 2;                              // cell_atoms, cell_of
     b += 2 * 256 * 4 + IGMK_MAX_ENVELOPES * 4 * 4;
+    b += (size_t)K * MD2_NW * 4;                   // active bond batches per warp-slot
     return (b + 255) / 256 * 256;
 }
 
@@ -40,7 +41,9 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
     uint16_t* cell_of = cell_atoms + np;
     float* rbuf = (float*)(cell_of + np);
     float* envp = rbuf + 2 * 256;
+    int* bact = (int*)(envp + IGMK_MAX_ENVELOPES * 4);
     int rb_par = 0;
+    bool bond_build = true;
 
     float* base = gstate + (size_t)md.perm_off * BIG_FLOATS_PER_POS;
     float4* x = (float4*)base;
@@ -54,6 +57,7 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
     const uint16_t* perm = V.perm + md.perm_off;
     const int32_t* eoff = V.ell_off + md.ell_desc_off;
     const uint32_t* eitems = V.ell_items + md.ell_item_off;
+    uint32_t* eact = V.ell_act + md.ell_item_off;
     uint16_t* nl = V.nl + (size_t)md.perm_off * V.nl_width;
     const int nlw = V.nl_width;
     const float2* btype = B.btype_f + d->btype_off;
@@ -214,6 +218,7 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
             ncnt[p] = (uint32_t)cnt;
         }
         overflow |= __syncthreads_or(ovf);
+        bond_build = true;        // the next force evaluation also refreshes the bond candidate list (see md2.cuh)
         n_rebuild++;
     };
 
@@ -245,8 +250,11 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
             }
             {
                 const int g = k * MD2_NW + warp;
-                const int bo = eoff[g], nb4 = (eoff[g + 1] - bo) >> 7;
-                const uint4* it = (const uint4*)(eitems + bo) + lane;
+                const bool build = bond_build;
+                const int bo = eoff[g], nb4 = build ? ((eoff[g + 1] - bo) >> 7) : bact[g];
+                const uint4* it = (const uint4*)((build ? eitems : eact) + bo) + lane;
+                uint32_t* out = eact + bo + (lane << 2);
+                int ccnt = 0;
                 for (int c = 0; c < nb4; c++) {
                     const uint4 cur = it[c * 32];
                     const uint32_t v[4] = {cur.x, cur.y, cur.z, cur.w};
@@ -263,7 +271,16 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
                         float fb = -bond_pref2 * fabsf(t.y) * (1.f - t.x * fast_rsqrt(r2));
                         fb = act ? fb : 0.f;
                         ax += dx * fb; ay += dy * fb; az += dz * fb;
+                        if (build) {
+                            const float lo = fmaxf(t.x - skin, 0.f), hi = t.x + skin;
+                            if (t.y > 0.f ? (r2 > lo * lo) : (r2 < hi * hi)) { out[((ccnt >> 2) << 7) + (ccnt & 3)] = v[u]; ccnt++; }
+                        }
                     }
+                }
+                if (build) {
+                    const int most = warp_max((ccnt + 3) >> 2);
+                    for (int cc = ccnt; cc < (most << 2); cc++) out[((cc >> 2) << 7) + (cc & 3)] = (uint32_t)p;
+                    if (lane == 0) bact[g] = most;
                 }
             }
             uint32_t m = m0 >> 8;
@@ -280,6 +297,7 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
             if (!mobile(m0)) { ax = 0.f; ay = 0.f; az = 0.f; }
             fx[p] = ax; fy[p] = ay; fz[p] = az;
         }
+        bond_build = false;
     };
 
     rebuild();
