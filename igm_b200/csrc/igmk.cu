@@ -672,17 +672,17 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
     V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.ell_act = h->d_md2_ell_act;
     V.prof = nullptr;
     const bool prof = getenv("IGMK_PROF") != nullptr;
-    if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 4 * sizeof(long long))); CU(cudaMemset(V.prof, 0, (size_t)ns * 4 * sizeof(long long))); }
+    if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 8 * sizeof(long long))); CU(cudaMemset(V.prof, 0, (size_t)ns * 8 * sizeof(long long))); }
     k_md2<K><<<ns, MD2_T, sm>>>(B, V, h->d_md2_desc, P);
     CU(cudaGetLastError());
     if (prof) {                  // diagnostics only: per-phase SM cycles of thread 0, averaged over the structures
-        std::vector<long long> t((size_t)ns * 4);
+        std::vector<long long> t((size_t)ns * 8);
         CU(cudaMemcpy(t.data(), V.prof, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
         cudaFree(V.prof);
-        double a[4] = {0, 0, 0, 0};
-        for (int s = 0; s < ns; s++) for (int k = 0; k < 4; k++) a[k] += (double)t[4 * (size_t)s + k] / ns;
-        fprintf(stderr, "[igmk prof] k_md2 mean cycles per structure: forces %.3g, rebuild-search %.3g, rebuilds %.3g, n_rebuilds %.1f\n",
-                a[0], a[1], a[2], a[3]);
+        double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int s = 0; s < ns; s++) for (int k = 0; k < 8; k++) a[k] += (double)t[8 * (size_t)s + k] / ns;
+        fprintf(stderr, "[igmk prof] k_md2 mean cycles per structure: forces %.3g, rebuild-search %.3g, rebuilds %.3g, n_rebuilds %.1f; "
+                "stages %.3g %.3g %.3g %.3g\n", a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7]);
     }
     return 0;
 }

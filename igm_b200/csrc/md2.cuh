@@ -33,7 +33,8 @@ struct Md2View {
     uint32_t*       ell_act;   // same size: the items that can be active before the next rebuild (k_md2 scratch)
     uint16_t*       nl;        // [sum np * nl_width] column-major per structure
     int32_t         nl_width;
-    long long*      prof;      // optional [n_struct][4] SM cycles: force loops, integration, rebuilds, total (IGMK_PROF=1)
+    long long*      prof;      // optional [n_struct][8] SM cycles (IGMK_PROF=1): force loops, rebuild search, rebuilds,
+                               // number of rebuilds, then cycles of annealing stages 0..3
 };
 
 struct Md2Desc {               // per structure
@@ -418,7 +419,9 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     const float dof = 3.f * (float)d->n_nonfixed - 3.f;
     float last_temp = 0.f;
 
+    long long t_stage[4] = {0, 0, 0, 0};
     for (int st = 0; st < pr.n_stage; st++) {
+        const long long ts_stage = clock64();
         set_stage(pr.evfactor[st], pr.envfactor[st]);
         for (int sub = (pr.relax_mdsteps > 0 ? 0 : 1); sub < 2; sub++) {
             const int nsteps = sub == 0 ? pr.relax_mdsteps : pr.mdsteps[st];
@@ -513,6 +516,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 t_integ += tc1 - tc0;
             }
         }
+        if (st < 4) t_stage[st] = clock64() - ts_stage;
     }
     // results: coordinates back in the original atom order (float32 like Particle.pos)
     int bad = 0;
@@ -533,8 +537,9 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         r->n_rebuilds = n_rebuild;
         B.flags[blockIdx.x] = (overflow ? 1 : 0) | (bad ? 2 : 0);
         if (V.prof) {
-            long long* o = V.prof + 4 * (size_t)blockIdx.x;
+            long long* o = V.prof + 8 * (size_t)blockIdx.x;
             o[0] = t_force; o[1] = t_search; o[2] = t_build; o[3] = n_rebuild;
+            for (int k = 0; k < 4; k++) o[4 + k] = t_stage[k];
         }
     }
 }
