@@ -185,18 +185,9 @@ def violation_histogram(v, nbins=100, vmax=1):
     return np.concatenate([H, [over]]), np.concatenate([edges, [np.inf]])
 
 
-def optimize_population(models, cfg, device=None):
-    """Optimise every model of ``models`` in one launch sequence; returns the list of info dicts."""
-    models = list(models)
-    if not models:
-        return []
-    kopts = kernel_opts(cfg)
-    run_opts = dict(_cfg_get(cfg, "optimization/optimizer_options"))
-    run_opts.update(kopts)                                                        # lammps.py:433 (carries `seed`)
-    step_no = (_cfg_get(cfg, "runtime/step_no", 1) or 0) + 2                     # lammps.py:435
-    protocol = _abi.make_protocol(run_opts, bond_prefactor=kopts["bond_prefactor"])
-    with MStepBatch(kopts["device"] if device is None else device) as batch:
-        slots = [batch.submit(pack_model(m, seed=script_seed(run_opts, m.id, step_no))) for m in models]
+def _optimize_on_device(models, seeds, protocol, device):
+    with MStepBatch(device) as batch:
+        slots = [batch.submit(pack_model(m, seed=sd)) for m, sd in zip(models, seeds)]
         batch.run(protocol)
         infos = []
         for m, slot in zip(models, slots):
@@ -207,6 +198,43 @@ def optimize_population(models, cfg, device=None):
                 p.pos = xyz[i]                                                    # lammps.py:464-465
             infos.append(info_from_result(res))
     return infos
+
+
+def _devices(kopts, device):
+    if device is not None:
+        return [int(device)]
+    devs = kopts.get("devices", None)
+    if devs is None:
+        return [int(kopts["device"])]
+    if devs == "all":
+        return list(range(_abi.load().igmk_device_count()))
+    return [int(d) for d in devs]
+
+
+def optimize_population(models, cfg, device=None):
+    """Optimise every model of ``models`` in one launch sequence per GPU; returns the list of info dicts.
+    ``kernel_opts/b200/devices`` (a list of ordinals or "all") spreads the structures over several GPUs of
+    the box from this one process: contiguous blocks, one host thread and one batch per device, no
+    communication (structures are independent, igm/steps/ModelingStep.py:97)."""
+    models = list(models)
+    if not models:
+        return []
+    kopts = kernel_opts(cfg)
+    run_opts = dict(_cfg_get(cfg, "optimization/optimizer_options"))
+    run_opts.update(kopts)                                                        # lammps.py:433 (carries `seed`)
+    step_no = (_cfg_get(cfg, "runtime/step_no", 1) or 0) + 2                     # lammps.py:435
+    protocol = _abi.make_protocol(run_opts, bond_prefactor=kopts["bond_prefactor"])
+    seeds = [script_seed(run_opts, m.id, step_no) for m in models]
+    devs = _devices(kopts, device)[:len(models)]
+    if len(devs) <= 1:
+        return _optimize_on_device(models, seeds, protocol, devs[0] if devs else 0)
+    from concurrent.futures import ThreadPoolExecutor
+    from .parallel import structure_shard
+    blocks = [structure_shard(len(models), r, len(devs)) for r in range(len(devs))]
+    with ThreadPoolExecutor(max_workers=len(devs)) as ex:
+        parts = list(ex.map(lambda rb: _optimize_on_device(models[rb[1][0]:rb[1][1]], seeds[rb[1][0]:rb[1][1]], protocol, devs[rb[0]]),
+                            enumerate(blocks)))
+    return [info for part in parts for info in part]
 
 
 def optimize(model, cfg):

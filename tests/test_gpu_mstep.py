@@ -306,3 +306,23 @@ def test_short_trajectory_matches_oracle(uniform):
             assert moved > 50.0                                     # T = 5000: the beads really travelled
             assert np.abs(xyz - x_ref).max() <= 2e-3 * moved
             assert res.temperature == pytest.approx(r_ref.temperature, rel=1e-3)
+
+
+def test_optimize_population_over_all_devices():
+    """kernel_opts/b200/devices = "all": the same results as on one device, whatever the split
+    (one GPU on the test box: the code path still runs; several: contiguous blocks per device)"""
+    opts = synth.demo_protocol_options()
+    opts["custom_annealing_protocol"]["mdsteps"] = [60, 60, 60, 60]
+    opts["custom_annealing_protocol"]["relax"]["mdsteps"] = 10
+    base = {"optimizer_options": opts, "kernel": "b200"}
+    cfg1 = {"optimization": dict(base, kernel_opts={"b200": {"seed": 5}}), "runtime": {"step_no": 0}}
+    cfgn = {"optimization": dict(base, kernel_opts={"b200": {"seed": 5, "devices": "all"}}), "runtime": {"step_no": 0}}
+    cfg2 = {"optimization": dict(base, kernel_opts={"b200": {"seed": 5, "devices": [0, 0, 0]}}), "runtime": {"step_no": 0}}
+    ref = [_toy_model(i + 1, seed=60 + i)[0] for i in range(7)]
+    want = optimize_population(ref, cfg1)
+    for cfg in (cfgn, cfg2):
+        ms = [_toy_model(i + 1, seed=60 + i)[0] for i in range(7)]
+        got = optimize_population(ms, cfg)
+        assert [g["final-energy"] for g in got] == [w["final-energy"] for w in want]
+        for a, b in zip(ms, ref):
+            assert np.array_equal(np.array([p.pos for p in a.particles]), np.array([p.pos for p in b.particles]))
