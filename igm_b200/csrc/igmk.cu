@@ -10,6 +10,7 @@
 #include <map>
 #include <tuple>
 #include <algorithm>
+#include <chrono>
 #include <thread>
 #include <cuda_runtime.h>
 
@@ -36,19 +37,30 @@ static const int IGMK_NL_OVERFLOW = 100;   // internal: retry with a wider neigh
         }                                                                                     \
     } while (0)
 
+// copy on a stream and wait for it: unlike cudaMemcpy this never touches the legacy default stream, so batches
+// running on other handles' streams are not serialised behind it
+static cudaError_t copy_on(cudaStream_t st, void* dst, const void* src, size_t bytes, cudaMemcpyKind kind)
+{
+    cudaError_t e = cudaMemcpyAsync(dst, src, bytes, kind, st);
+    return e != cudaSuccess ? e : cudaStreamSynchronize(st);
+}
+
 template <typename T>
-static cudaError_t dev_alloc_copy(T** dptr, const std::vector<T>& h)
+static cudaError_t dev_alloc_copy(T** dptr, const std::vector<T>& h, cudaStream_t st)
 {
     size_t bytes = std::max<size_t>(h.size(), 1) * sizeof(T);
     cudaError_t e = cudaMalloc((void**)dptr, bytes);
     if (e != cudaSuccess) return e;
-    if (!h.empty()) e = cudaMemcpy(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+    if (!h.empty()) e = copy_on(st, *dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
     return e;
 }
 
 struct igmk_handle {
     int device = 0;
     int smem_optin = 0;
+    cudaStream_t stream = nullptr;      // non-blocking: batches of different handles overlap on one device
+    cudaStream_t stream_hi = nullptr;   // same, highest priority: the short CG launch that ends a batch overtakes the queued MD
+                                        // CTAs of other batches, so a finished chunk leaves the device while the others still run
     // host staging
     std::vector<StructDesc> desc;
     std::vector<float4>   xyzr;         // current coordinates (results land here)
@@ -134,6 +146,10 @@ extern "C" int igmk_create(int device, igmk_handle_t** out)
         if (f >= 0.05f && f <= 4.0f) h->skin_factor = f;
     }
 
+    CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    int prio_lo = 0, prio_hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CU(cudaStreamCreateWithPriority(&h->stream_hi, cudaStreamNonBlocking, prio_hi));
     *out = h;
     return 0;
 }
@@ -143,6 +159,8 @@ extern "C" int igmk_destroy(igmk_handle_t* h)
     if (!h) return 0;
     cudaSetDevice(h->device);
     h->free_device();
+    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->stream_hi) cudaStreamDestroy(h->stream_hi);
     delete h;
     return 0;
 }
@@ -500,15 +518,15 @@ static int upload(igmk_handle* h)
     if (!h->dirty) return 0;
     h->free_device();
     const size_t na = h->xyzr.size(), ns = h->desc.size();
-    CU(dev_alloc_copy(&h->d_desc, h->desc));
-    CU(dev_alloc_copy(&h->d_xyzr, h->xyzr));
-    CU(dev_alloc_copy(&h->d_xyzr0, h->xyzr0));
-    CU(dev_alloc_copy(&h->d_kind, h->kind));
-    CU(dev_alloc_copy(&h->d_envmask, h->envmask));
-    CU(dev_alloc_copy(&h->d_bond_ptr, h->bond_ptr));
-    CU(dev_alloc_copy(&h->d_bond_items, h->bond_items));
-    CU(dev_alloc_copy(&h->d_btype_f, h->btype_f));
-    CU(dev_alloc_copy(&h->d_btype_d, h->btype_d));
+    CU(dev_alloc_copy(&h->d_desc, h->desc, h->stream));
+    CU(dev_alloc_copy(&h->d_xyzr, h->xyzr, h->stream));
+    CU(dev_alloc_copy(&h->d_xyzr0, h->xyzr0, h->stream));
+    CU(dev_alloc_copy(&h->d_kind, h->kind, h->stream));
+    CU(dev_alloc_copy(&h->d_envmask, h->envmask, h->stream));
+    CU(dev_alloc_copy(&h->d_bond_ptr, h->bond_ptr, h->stream));
+    CU(dev_alloc_copy(&h->d_bond_items, h->bond_items, h->stream));
+    CU(dev_alloc_copy(&h->d_btype_f, h->btype_f, h->stream));
+    CU(dev_alloc_copy(&h->d_btype_d, h->btype_d, h->stream));
     CU(cudaMalloc((void**)&h->d_nl, std::max<size_t>(na, 1) * h->nl_width * sizeof(uint16_t)));
     CU(cudaMalloc((void**)&h->d_nl_cnt, std::max<size_t>(na, 1) * sizeof(uint16_t)));
     CU(cudaMalloc((void**)&h->d_xd, std::max<size_t>(na, 1) * 3 * sizeof(double)));
@@ -516,8 +534,8 @@ static int upload(igmk_handle* h)
     CU(cudaMalloc((void**)&h->d_work, std::max<size_t>(na, 1) * 12 * sizeof(double)));
     CU(cudaMalloc((void**)&h->d_res, std::max<size_t>(ns, 1) * sizeof(igmk_result_t)));
     CU(cudaMalloc((void**)&h->d_flags, std::max<size_t>(ns, 1) * sizeof(int32_t)));
-    CU(cudaMemset(h->d_res, 0, std::max<size_t>(ns, 1) * sizeof(igmk_result_t)));
-    CU(cudaMemset(h->d_flags, 0, std::max<size_t>(ns, 1) * sizeof(int32_t)));
+    CU(cudaMemsetAsync(h->d_res, 0, std::max<size_t>(ns, 1) * sizeof(igmk_result_t), h->stream));
+    CU(cudaMemsetAsync(h->d_flags, 0, std::max<size_t>(ns, 1) * sizeof(int32_t), h->stream));
     h->md2_K = md2_pick_K(h->max_atoms);
     h->md_big = h->md2_K == 0 || getenv("IGMK_FORCE_BIG") != nullptr;   // the variable routes small batches through md_big.cuh (tests)
     if (h->md_big) {                                   // > 8192 atoms: state in global memory (md_big.cuh)
@@ -530,10 +548,10 @@ static int upload(igmk_handle* h)
         CU(cudaMalloc((void**)&h->d_big, (na + 32 * ns) * 10 * sizeof(double)));
     if (h->md2_K > 0) {
         md2_build(h);
-        CU(dev_alloc_copy(&h->d_md2_desc, h->md2_desc));
-        CU(dev_alloc_copy(&h->d_md2_perm, h->md2_perm));
-        CU(dev_alloc_copy(&h->d_md2_ell_off, h->md2_ell_off));
-        CU(dev_alloc_copy(&h->d_md2_ell_items, h->md2_ell_items));
+        CU(dev_alloc_copy(&h->d_md2_desc, h->md2_desc, h->stream));
+        CU(dev_alloc_copy(&h->d_md2_perm, h->md2_perm, h->stream));
+        CU(dev_alloc_copy(&h->d_md2_ell_off, h->md2_ell_off, h->stream));
+        CU(dev_alloc_copy(&h->d_md2_ell_items, h->md2_ell_items, h->stream));
         CU(cudaMalloc((void**)&h->d_md2_ell_act, std::max<size_t>(h->md2_ell_items.size(), 1) * sizeof(uint32_t)));
         CU(cudaMalloc((void**)&h->d_md2_nl, h->md2_perm.size() * (size_t)h->md2_nlw * sizeof(uint16_t)));
     }
@@ -576,19 +594,19 @@ extern "C" int igmk_violation_ratios(igmk_handle_t* h, int32_t slot, double* bon
         const int64_t nb = (int64_t)h->sub_bonds.size(), ne = (int64_t)h->sub_env.size();
         h->viol_bond.assign((size_t)nb, 0.0); h->viol_env.assign((size_t)ne, 0.0);
         SubBond* d_b = nullptr; int32_t* d_o = nullptr; EnvMember* d_e = nullptr; double* d_r = nullptr;
-        cudaError_t e = dev_alloc_copy(&d_b, h->sub_bonds);
-        if (e == cudaSuccess) e = dev_alloc_copy(&d_o, h->sub_bond_atom_off);
-        if (e == cudaSuccess) e = dev_alloc_copy(&d_e, h->sub_env);
+        cudaError_t e = dev_alloc_copy(&d_b, h->sub_bonds, h->stream);
+        if (e == cudaSuccess) e = dev_alloc_copy(&d_o, h->sub_bond_atom_off, h->stream);
+        if (e == cudaSuccess) e = dev_alloc_copy(&d_e, h->sub_env, h->stream);
         if (e == cudaSuccess) e = cudaMalloc((void**)&d_r, (size_t)std::max<int64_t>(std::max(nb, ne), 1) * sizeof(double));
         if (e == cudaSuccess && nb > 0) {
-            k_bond_violations<<<(int)std::min<int64_t>((nb + 255) / 256, 148 * 16), 256>>>(h->d_xyzr, d_b, d_o, nb, d_r);
+            k_bond_violations<<<(int)std::min<int64_t>((nb + 255) / 256, 148 * 16), 256, 0, h->stream>>>(h->d_xyzr, d_b, d_o, nb, d_r);
             e = cudaGetLastError();
-            if (e == cudaSuccess) e = cudaMemcpy(h->viol_bond.data(), d_r, (size_t)nb * sizeof(double), cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess) e = copy_on(h->stream, h->viol_bond.data(), d_r, (size_t)nb * sizeof(double), cudaMemcpyDeviceToHost);
         }
         if (e == cudaSuccess && ne > 0) {
-            k_env_violations<<<(int)std::min<int64_t>((ne + 255) / 256, 148 * 16), 256>>>(h->d_xyzr, d_e, ne, d_r);
+            k_env_violations<<<(int)std::min<int64_t>((ne + 255) / 256, 148 * 16), 256, 0, h->stream>>>(h->d_xyzr, d_e, ne, d_r);
             e = cudaGetLastError();
-            if (e == cudaSuccess) e = cudaMemcpy(h->viol_env.data(), d_r, (size_t)ne * sizeof(double), cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess) e = copy_on(h->stream, h->viol_env.data(), d_r, (size_t)ne * sizeof(double), cudaMemcpyDeviceToHost);
         }
         cudaFree(d_b); cudaFree(d_o); cudaFree(d_e); cudaFree(d_r);
         CU(e);
@@ -617,7 +635,7 @@ extern "C" int igmk_reset_coordinates(igmk_handle_t* h)
     h->xyzr = h->xyzr0;
     if (!h->dirty && h->d_xyzr) {
         CU(cudaSetDevice(h->device));
-        CU(cudaMemcpy(h->d_xyzr, h->d_xyzr0, h->xyzr0.size() * sizeof(float4), cudaMemcpyDeviceToDevice));
+        CU(copy_on(h->stream, h->d_xyzr, h->d_xyzr0, h->xyzr0.size() * sizeof(float4), cudaMemcpyDeviceToDevice));
     }
     return 0;
 }
@@ -637,7 +655,7 @@ static int collect(igmk_handle* h, const char* what)
 {
     const size_t ns = h->desc.size();
     h->res.resize(ns); h->flags.resize(ns);
-    CU(cudaMemcpy(h->flags.data(), h->d_flags, ns * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    CU(copy_on(h->stream, h->flags.data(), h->d_flags, ns * sizeof(int32_t), cudaMemcpyDeviceToHost));
     for (size_t s = 0; s < ns; s++) {
         if (h->flags[s] & 1) {
             char msg[256];
@@ -647,8 +665,8 @@ static int collect(igmk_handle* h, const char* what)
             return IGMK_NL_OVERFLOW;      // host staging still holds the submitted coordinates
         }
     }
-    CU(cudaMemcpy(h->res.data(), h->d_res, ns * sizeof(igmk_result_t), cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(h->xyzr.data(), h->d_xyzr, h->xyzr.size() * sizeof(float4), cudaMemcpyDeviceToHost));
+    CU(copy_on(h->stream, h->res.data(), h->d_res, ns * sizeof(igmk_result_t), cudaMemcpyDeviceToHost));
+    CU(copy_on(h->stream, h->xyzr.data(), h->d_xyzr, h->xyzr.size() * sizeof(float4), cudaMemcpyDeviceToHost));
     for (size_t s = 0; s < ns; s++) h->res[s].status = (h->flags[s] & 2) ? 1 : 0;
     return 0;
 }
@@ -672,12 +690,12 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
     V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.ell_act = h->d_md2_ell_act;
     V.prof = nullptr;
     const bool prof = getenv("IGMK_PROF") != nullptr;
-    if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 8 * sizeof(long long))); CU(cudaMemset(V.prof, 0, (size_t)ns * 8 * sizeof(long long))); }
-    k_md2<K><<<ns, MD2_T, sm>>>(B, V, h->d_md2_desc, P);
+    if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 8 * sizeof(long long))); CU(cudaMemsetAsync(V.prof, 0, (size_t)ns * 8 * sizeof(long long), h->stream)); }
+    k_md2<K><<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
     CU(cudaGetLastError());
     if (prof) {                  // diagnostics only: per-phase SM cycles of thread 0, averaged over the structures
         std::vector<long long> t((size_t)ns * 8);
-        CU(cudaMemcpy(t.data(), V.prof, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+        CU(copy_on(h->stream, t.data(), V.prof, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
         cudaFree(V.prof);
         double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         for (int s = 0; s < ns; s++) for (int k = 0; k < 8; k++) a[k] += (double)t[8 * (size_t)s + k] / ns;
@@ -695,7 +713,7 @@ static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
         Md2View V;
         V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
         V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.prof = nullptr; V.ell_act = h->d_md2_ell_act;
-        k_md_big<<<ns, MD2_T, sm>>>(B, V, h->d_md2_desc, P, h->d_big_state);
+        k_md_big<<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P, h->d_big_state);
         CU(cudaGetLastError());
         return 0;
     }
@@ -721,24 +739,32 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
     const size_t sm_cg = ctx_smem_bytes<double>(h->max_atoms, false);
     CU(cudaFuncSetAttribute(k_cg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_cg));
     float ms = 0.f;
+    const bool trace = getenv("IGMK_TRACE") != nullptr;     // wall-clock marks of this call on stderr (pipeline diagnostics)
+    auto now_ms = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_enter = now_ms();
     for (;;) {
         if (int rc = upload(h)) return rc;
+        const double t_up = now_ms();
         Batch B = make_batch(h);
-        CU(cudaMemset(h->d_flags, 0, ns * sizeof(int32_t)));
+        CU(cudaMemsetAsync(h->d_flags, 0, ns * sizeof(int32_t), h->stream));
         cudaEvent_t e0, e1, e2;
         CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
-        CU(cudaEventRecord(e0));
+        CU(cudaEventRecord(e0, h->stream));
         MdParams P; P.prot = *prot; P.skin_factor = h->skin_factor;
         if (int rc = launch_md2(h, B, P, ns)) return rc;
-        CU(cudaEventRecord(e1));
-        k_cg<<<ns, MD_THREADS, sm_cg>>>(B, *prot);
+        CU(cudaEventRecord(e1, h->stream));
+        CU(cudaStreamWaitEvent(h->stream_hi, e1, 0));
+        k_cg<<<ns, MD_THREADS, sm_cg, h->stream_hi>>>(B, *prot);
         CU(cudaGetLastError());
-        CU(cudaEventRecord(e2));
+        CU(cudaEventRecord(e2, h->stream_hi));
         CU(cudaEventSynchronize(e2));
         float ms_md = 0.f, ms_cg = 0.f;
         CU(cudaEventElapsedTime(&ms_md, e0, e1));
         CU(cudaEventElapsedTime(&ms_cg, e1, e2));
         ms = ms_md + ms_cg; h->md_ms = ms_md; h->cg_ms = ms_cg;
+        if (trace)
+            fprintf(stderr, "[igmk trace] run of %d structures (first id %lld): enter %.1f, uploaded +%.1f, device done +%.1f (md %.1f, cg %.1f)\n",
+                    ns, (long long)h->struct_id[0], t_enter, t_up - t_enter, now_ms() - t_enter, ms_md, ms_cg);
         cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
         const int rc = collect(h, "igmk_run");
         if (rc == IGMK_NL_OVERFLOW) {                                  // either table may have overflowed
@@ -769,17 +795,17 @@ static int single_point_impl(igmk_handle* h, double ev_scale, double env_scale, 
     for (;;) {
         if (int rc = upload(h)) return rc;
         Batch B = make_batch(h);
-        CU(cudaMemset(h->d_flags, 0, h->desc.size() * sizeof(int32_t)));
-        k_single_point<T><<<(int)h->desc.size(), MD_THREADS, sm>>>(B, ev_scale, env_scale, bond_prefactor);
+        CU(cudaMemsetAsync(h->d_flags, 0, h->desc.size() * sizeof(int32_t), h->stream));
+        k_single_point<T><<<(int)h->desc.size(), MD_THREADS, sm, h->stream>>>(B, ev_scale, env_scale, bond_prefactor);
         CU(cudaGetLastError());
-        CU(cudaDeviceSynchronize());
+        CU(cudaStreamSynchronize(h->stream));
         const int rc = collect(h, "igmk_single_point");
         if (rc == IGMK_NL_OVERFLOW && widen_neighbour_table(h)) continue;
         if (rc) return 1;
         break;
     }
     h->forces.resize(h->xyzr.size() * 3);
-    CU(cudaMemcpy(h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    CU(copy_on(h->stream, h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
     h->have_forces = true;
     return 0;
 }
@@ -808,6 +834,26 @@ extern "C" int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out, igmk_r
     return 0;
 }
 
+extern "C" int igmk_fetch_population(igmk_handle_t* h, int32_t n_bead, int32_t n_struct_total, int32_t s_begin, float* crd,
+                                     igmk_result_t* res)
+{
+    if (!h || !crd) return fail("igmk_fetch_population: NULL argument");
+    const int ns = (int)h->desc.size();
+    if (h->res.size() != h->desc.size()) return fail("igmk_fetch_population: nothing has been run");
+    if (n_bead < 1 || s_begin < 0 || s_begin + ns > n_struct_total) return fail("igmk_fetch_population: bad structure range");
+    for (int s = 0; s < ns; s++)
+        if (h->desc[s].n_atoms < n_bead) return fail("igmk_fetch_population: a structure has fewer than n_bead atoms");
+    for (int a = 0; a < n_bead; a++) {                      // bead-major like the .hss dataset: contiguous runs of ns structures
+        float* dst = crd + ((size_t)a * n_struct_total + s_begin) * 3;
+        for (int s = 0; s < ns; s++) {
+            const float4 p = h->xyzr[h->desc[s].atom_off + a];
+            dst[3 * s] = p.x; dst[3 * s + 1] = p.y; dst[3 * s + 2] = p.z;
+        }
+    }
+    if (res) memcpy(res, h->res.data(), (size_t)ns * sizeof(igmk_result_t));
+    return 0;
+}
+
 extern "C" int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out)
 {
     if (!h || !f_out) return fail("igmk_fetch_forces: NULL argument");
@@ -816,7 +862,7 @@ extern "C" int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out)
     if (h->forces.size() != h->xyzr.size() * 3) {
         CU(cudaSetDevice(h->device));
         h->forces.resize(h->xyzr.size() * 3);
-        CU(cudaMemcpy(h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
+        CU(copy_on(h->stream, h->forces.data(), h->d_fd, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
     }
     const StructDesc& d = h->desc[slot];
     memcpy(f_out, h->forces.data() + (size_t)d.atom_off * 3, (size_t)d.n_atoms * 3 * sizeof(double));

@@ -7,7 +7,7 @@ do for a population (bin/igm-run:99-131), minus the file system.
       -> all-gather of the rows (= actdist.hdf5)                    ActivationDistanceStep.reduce :226-290
       -> contact assignment for this rank's structures              inter/intraHiC._apply  inter_hic.py:49-64
       -> structures = template + slab + assigned bonds              ModelingStep.task             :184-264
-      -> annealing MD + CG for all of them in one launch sequence   Model.optimize -> lammps.optimize
+      -> annealing MD + CG, chunk by chunk behind the assembly      Model.optimize -> lammps.optimize
       -> optimised coordinates, per-structure info, violation stats ModelingStep.task :341-382
 
 Single process: ranks = 1.  Several GPUs: one process per GPU under torch.distributed (NCCL); every
@@ -19,7 +19,7 @@ import numpy as np
 
 from . import _abi, parallel
 from .astep import Population
-from .kernel import MStepBatch, info_from_result
+from .kernel import info_from_result, run_population
 
 
 def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, device=0, contact_range=2.0,
@@ -49,26 +49,17 @@ def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, 
     r0 = (contact_range * (radii[row] + radii[col])).astype(np.float64)      # float32 product like inter_hic.py:55
     protocol = _abi.make_protocol(optimizer_options, bond_prefactor=bond_prefactor)
     out = {"rows": rows, "timings": {"astep_s": t_astep}}
-    with MStepBatch(device) as batch:
-        batch.submit_population(template, crd_local, n_bead, row, col, r0, k_hic, bits, seeds=seeds)
-        t_build = time.perf_counter() - t0 - t_astep
-        batch.run(protocol)
-        new = np.empty((n_bead, S, 3), dtype=np.float32)
-        infos = []
-        for k in range(S):
-            xyz, res = batch.fetch(k)
-            if res.status != 0 or not np.isfinite(res.final_energy):
-                raise RuntimeError("b200 kernel produced non-finite coordinates or energy (structure %d of rank %d)" % (k, rank))
-            new[:, k, :] = xyz[:n_bead]
-            infos.append(info_from_result(res))
-        if violations:
-            v = []
-            for k in range(S):
-                br, _ = batch.violation_ratios(k)
-                v.append((br.size, int(np.count_nonzero(br > tol))))
-            out["violations"] = v
-        md_ms, cg_ms, h2d = batch.last_timings()
+    new, results, viol, tim = run_population(template, crd_local, n_bead, row, col, r0, k_hic, bits, protocol, device=device,
+                                             seeds=seeds, violations_tol=tol if violations else None)
+    infos = []
+    for k, res in enumerate(results):
+        if res.status != 0 or not np.isfinite(res.final_energy):
+            raise RuntimeError("b200 kernel produced non-finite coordinates or energy (structure %d of rank %d)" % (k, rank))
+        infos.append(info_from_result(res))
+    if violations:
+        out["violations"] = viol
+    md_ms, cg_ms, h2d = tim["md_kernel_ms"], tim["cg_kernel_ms"], tim["h2d_bytes"]
     out["coordinates"], out["infos"] = new, infos
-    out["timings"].update({"bond_build_and_submit_s": t_build, "md_kernel_ms": md_ms, "cg_kernel_ms": cg_ms,
+    out["timings"].update({"mstep_s": time.perf_counter() - t0 - t_astep, "md_kernel_ms": md_ms, "cg_kernel_ms": cg_ms,
                            "h2d_bytes": h2d, "total_s": time.perf_counter() - t0})
     return out

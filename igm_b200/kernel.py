@@ -82,11 +82,14 @@ class MStepBatch(object):
         self._packed.append(packed)
         return slot.value
 
-    def submit_population(self, template, crd, n_bead, row, col, row_r0, row_k, bits, s_begin=0, n_struct=None, seeds=None):
+    def submit_population(self, template, crd, n_bead, row, col, row_r0, row_k, bits, s_begin=0, n_struct=None, seeds=None,
+                          bits_word0=0):
         """Submit structures ``s_begin .. s_begin+n_struct-1`` of the .hss-layout slab ``crd``
         ([n_bead][S][3] float32): every structure = ``template`` (a PackedSystem: shared particles and
         restraints) with the slab's coordinates and a HarmonicUpperBound per actdist row whose bit is set
-        in ``bits`` (the matrix Population.assign returned for exactly these structures).  -> first slot."""
+        in ``bits`` (the matrix Population.assign returned for exactly these structures; ``bits_word0`` =
+        word of every row that holds the bit of structure ``s_begin``, for a matrix that covers more
+        structures than this call submits).  -> first slot."""
         crd = np.ascontiguousarray(crd, dtype=np.float32)
         S = crd.shape[1]
         if n_struct is None:
@@ -95,12 +98,15 @@ class MStepBatch(object):
         c = np.ascontiguousarray(col, dtype=np.int32)
         r0 = np.ascontiguousarray(row_r0, dtype=np.float64)
         b = np.ascontiguousarray(bits, dtype=np.uint32).reshape(r.size, -1) if r.size else np.zeros((0, 1), dtype=np.uint32)
+        if r.size and (bits_word0 < 0 or (b.shape[1] - bits_word0) * 32 < n_struct):
+            raise ValueError("bit matrix does not cover structures %d..%d from word %d" % (s_begin, s_begin + n_struct, bits_word0))
         sd = None if seeds is None else np.ascontiguousarray(seeds, dtype=np.int64)
         first = C.c_int32(-1)
         _abi.check(self._lib.igmk_submit_population(
             self._h, C.byref(template.c), int(n_bead), int(S), int(s_begin), int(n_struct), crd.ctypes.data_as(_abi.c_f32p),
             r.size, r.ctypes.data_as(_abi.c_i32p), c.ctypes.data_as(_abi.c_i32p), r0.ctypes.data_as(_abi.c_f64p), float(row_k),
-            b.ctypes.data_as(_abi.c_u32p), int(b.shape[1]), None if sd is None else sd.ctypes.data_as(_abi.c_i64p),
+            C.cast(b.ctypes.data + 4 * int(bits_word0), _abi.c_u32p), int(b.shape[1]),
+            None if sd is None else sd.ctypes.data_as(_abi.c_i64p),
             C.byref(first)), "igmk_submit_population")
         self._packed.extend([template] * n_struct)        # sizes for fetch(); bond arrays differ per structure
         return first.value
@@ -130,6 +136,16 @@ class MStepBatch(object):
         res = _abi.Result()
         _abi.check(self._lib.igmk_fetch(self._h, slot, xyz.ctypes.data_as(_abi.c_f32p), C.byref(res)), "igmk_fetch")
         return xyz, res
+
+    def fetch_population(self, crd, s_begin=0):
+        """Write every structure of the batch into the slab ``crd`` (float32 [n_bead][S][3], C-contiguous, in
+        place) at structures ``s_begin ..``; -> ctypes array of Result, one per structure."""
+        if crd.dtype != np.float32 or not crd.flags.c_contiguous or crd.ndim != 3 or crd.shape[2] != 3:
+            raise ValueError("crd must be a C-contiguous float32 [n_bead][S][3] array")
+        res = (_abi.Result * max(len(self), 1))()
+        _abi.check(self._lib.igmk_fetch_population(self._h, crd.shape[0], crd.shape[1], int(s_begin),
+                                                   crd.ctypes.data_as(_abi.c_f32p), res), "igmk_fetch_population")
+        return res
 
     def violation_ratios(self, slot):
         """-> (bond_ratio f8 [n_bonds] in submit order, env_u f8 [sum of envelope members]) at the
@@ -185,18 +201,114 @@ def violation_histogram(v, nbins=100, vmax=1):
     return np.concatenate([H, [over]]), np.concatenate([edges, [np.inf]])
 
 
-def _optimize_on_device(models, seeds, protocol, device):
-    with MStepBatch(device) as batch:
-        slots = [batch.submit(pack_model(m, seed=sd)) for m, sd in zip(models, seeds)]
-        batch.run(protocol)
-        infos = []
-        for m, slot in zip(models, slots):
-            xyz, res = batch.fetch(slot)
-            if res.status != 0 or not np.isfinite(res.final_energy):
-                raise RuntimeError("b200 kernel produced non-finite coordinates or energy (modelid: %d)" % m.id)
-            for i, p in enumerate(m.particles):
-                p.pos = xyz[i]                                                    # lammps.py:464-465
-            infos.append(info_from_result(res))
+PIPELINE_CHUNK = 128     # structures per launch sequence of run_population: a multiple of 32 (bit-matrix words), just under one wave of 148 SMs
+
+
+def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protocol, device=0, seeds=None,
+                   chunk=PIPELINE_CHUNK, violations_tol=None):
+    """M-step of a whole assigned population, host buffers in, host buffers out: the population-wide
+    form of ``ModelingStep.task`` (igm/steps/ModelingStep.py:184-264 build, :266 optimize, :341-382 results).
+
+    The structures go to the GPU in chunks of ``chunk``: this thread assembles chunk c+1
+    (``igmk_submit_population``, multi-threaded C++) while worker threads upload, run and fetch the
+    chunks before it, each batch on its own stream -- the SMs always have CTAs of some chunk to run, so
+    the host-side assembly, the copies in and the copies out disappear behind the MD kernel.
+
+    -> (coordinates float32 [n_bead][S][3], [Result] * S, violations or None, timings dict);
+    violations = per-structure (n_imposed, n_violated) of the harmonic restraints at ``violations_tol``."""
+    import threading
+    crd = np.ascontiguousarray(crd, dtype=np.float32)
+    S = crd.shape[1]
+    chunk = max(32, (int(chunk) + 31) // 32 * 32)
+    new = np.empty((n_bead, S, 3), dtype=np.float32)
+    results, viol = [None] * S, ([None] * S if violations_tol is not None else None)
+    errors, workers = [], []
+    tim = {"md_kernel_ms": 0.0, "cg_kernel_ms": 0.0, "h2d_bytes": 0, "chunks": 0}
+    lock = threading.Lock()
+
+    def finish(batch, lo, hi):
+        try:
+            batch.run(protocol)
+            res = batch.fetch_population(new, lo)
+            for k in range(hi - lo):
+                results[lo + k] = res[k]
+            md, cg, h2d = batch.last_timings()
+            with lock:
+                tim["md_kernel_ms"] += md; tim["cg_kernel_ms"] += cg; tim["h2d_bytes"] += h2d; tim["chunks"] += 1
+        except Exception as e:           # re-raised on the calling thread
+            errors.append(e)
+
+    # The batches stay open until every chunk is done: freeing device memory waits for the whole device
+    # (and holds up the other threads' launches while it does), which would stall the pipeline.
+    batches = []
+    try:
+        for lo in range(0, S, chunk):
+            hi = min(S, lo + chunk)
+            batches.append((MStepBatch(device), lo, hi))
+            batches[-1][0].submit_population(template, crd, n_bead, row, col, row_r0, row_k, bits, s_begin=lo, n_struct=hi - lo,
+                                             seeds=None if seeds is None else seeds[lo:hi], bits_word0=lo // 32)
+            w = threading.Thread(target=finish, args=batches[-1])
+            w.start()
+            workers.append(w)
+            if errors:
+                break
+        for w in workers:
+            w.join()
+        workers = []
+        if errors:
+            raise errors[0]
+        if viol is not None:
+            for batch, lo, hi in batches:
+                for k in range(hi - lo):
+                    br, _ = batch.violation_ratios(k)
+                    viol[lo + k] = (br.size, int(np.count_nonzero(br > violations_tol)))
+    finally:
+        for w in workers:
+            w.join()
+        for batch, _, _ in batches:
+            batch.close()
+    return new, results, viol, tim
+
+
+def _optimize_on_device(models, seeds, protocol, device, chunk=PIPELINE_CHUNK):
+    """Pack and submit ``chunk`` models at a time on this thread; a worker thread per chunk runs it and
+    writes the positions back, so packing (Python) overlaps the MD of the chunks before it."""
+    import threading
+    infos, errors, workers = [None] * len(models), [], []
+
+    def finish(batch, lo, slots):
+        try:
+            batch.run(protocol)
+            for k, slot in enumerate(slots):
+                m = models[lo + k]
+                xyz, res = batch.fetch(slot)
+                if res.status != 0 or not np.isfinite(res.final_energy):
+                    raise RuntimeError("b200 kernel produced non-finite coordinates or energy (modelid: %d)" % m.id)
+                for i, p in enumerate(m.particles):
+                    p.pos = xyz[i]                                                # lammps.py:464-465
+                infos[lo + k] = info_from_result(res)
+        except Exception as e:           # re-raised on the calling thread
+            errors.append(e)
+
+    batches = []                         # closed together at the end (see run_population)
+    try:
+        for lo in range(0, len(models), chunk):
+            hi = min(len(models), lo + chunk)
+            batch = MStepBatch(device)
+            batches.append(batch)
+            slots = [batch.submit(pack_model(m, seed=sd)) for m, sd in zip(models[lo:hi], seeds[lo:hi])]
+            w = threading.Thread(target=finish, args=(batch, lo, slots))
+            w.start()
+            workers.append(w)
+            if errors:
+                break
+    finally:
+        for w in workers:
+            w.join()
+        for batch in batches:
+            batch.close()
+    if errors:
+        raise errors[0]
     return infos
 
 

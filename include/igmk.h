@@ -162,6 +162,11 @@ int igmk_single_point_f32(igmk_handle_t* h, double ev_scale, double env_scale,
                           double bond_prefactor);
 int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out /* [n_atoms][3] */,
                igmk_result_t* res);
+/* every structure of the batch at once, back into the .hss-layout slab crd [n_bead][n_struct_total][3] at
+ * structures s_begin .. s_begin+n-1 (what ModelingStep.set_structure copies .hms by .hms into the master
+ * matrix, `self._hss_crd[:,i,:] = crd`, igm/steps/ModelingStep.py:429-441); res: n results or NULL */
+int igmk_fetch_population(igmk_handle_t* h, int32_t n_bead, int32_t n_struct_total, int32_t s_begin, float* crd,
+                          igmk_result_t* res);
 int igmk_fetch_forces(igmk_handle_t* h, int32_t slot, double* f_out /* [n_atoms][3] */);
 /*
  * Violation ratios of the structure's restraints at the batch's CURRENT coordinates (after igmk_run:

@@ -235,6 +235,49 @@ def test_submit_population_equals_per_structure_submits():
                 assert c.fetch(k)[1].final_energy == e_sp[20 + k]
 
 
+def test_run_population_pipeline_equals_one_batch():
+    """kernel.run_population (chunks of 32 on their own streams, assembly overlapping the MD) returns
+    bit-identical coordinates, energies and violation counts to one batch holding every structure"""
+    from igm_b200.astep import Population
+    from igm_b200.kernel import run_population
+    g = synth.Genome([14, 11, 8, 6], n_autosomes=3)
+    R = 1400.0
+    rad = synth.bead_radii(len(g), R, 0.3)
+    S = 75                                            # 32 + 32 + ragged 11
+    crd = synth.population_territories(g, S, R=R, seed=21)
+    pi, pj, pw = synth.hic_pairs(g, 0.004, seed=4)
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads) as pop:
+        pop.upload(crd)
+        row, col, dist, _ = pop.actdist(pi, pj, pw, np.zeros(pi.size), 2.0)
+        bits = pop.assign(row, col, dist)
+    r0 = (2.0 * (rad[row] + rad[col])).astype(np.float64)
+    tmpl = synth.pack_structure(np.zeros((len(g), 3), dtype=np.float32), rad, g, nucleus_radius=R, seed=0, struct_id=0)
+    seeds = np.arange(S, dtype=np.int64) + 9
+    prot = short_protocol(md=150, relax=30)
+    new, results, viol, tim = run_population(tmpl, crd, len(g), row, col, r0, 1.0, bits, prot, seeds=seeds, chunk=32,
+                                             violations_tol=0.05)
+    assert tim["chunks"] == 3 and new.shape == crd.shape and len(results) == S
+    with MStepBatch(0) as a:
+        a.submit_population(tmpl, crd, len(g), row, col, r0, 1.0, bits, seeds=seeds)
+        a.run(prot)
+        for s in range(S):
+            xa, ra = a.fetch(s)
+            assert np.array_equal(xa[:len(g)].view(np.uint32), new[:, s, :].view(np.uint32))
+            assert ra.final_energy == results[s].final_energy and results[s].status == 0
+            br, _ = a.violation_ratios(s)
+            assert viol[s] == (br.size, int(np.count_nonzero(br > 0.05)))
+        slab = np.zeros((len(g), S + 5, 3), dtype=np.float32)              # bulk fetch into a wider slab at an offset
+        res = a.fetch_population(slab, s_begin=5)
+        assert np.array_equal(slab[:, 5:, :].view(np.uint32), new.view(np.uint32)) and not slab[:, :5, :].any()
+        assert [r.final_energy for r in res] == [r.final_energy for r in results]
+        with pytest.raises(RuntimeError):
+            a.fetch_population(slab, s_begin=6)
+    assert not np.array_equal(new, crd)
+    with pytest.raises(ValueError):
+        with MStepBatch(0) as b:
+            b.submit_population(tmpl, crd, len(g), row, col, r0, 1.0, bits, s_begin=64, n_struct=11, bits_word0=3)
+
+
 def test_config3_restraint_set_through_md(ff_golden):
     """2 Mb structure with every restraint kind of BASELINE config 3 at once (Hi-C-like upper bounds, lower
     bounds, an ellipsoidal k<0 lamina envelope, bonds to the static centre as radial FISH uses them, a
