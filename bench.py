@@ -7,8 +7,8 @@ Workload (BASELINE.json configs[1]): 2 Mb diploid genome (3008 beads + the envel
 1000 structures PER GPU (weak scaling), spherical envelope, Hi-C restraints assigned at one
 sigma, the demo's full annealing protocol (4 x [relax 500 + 5k/15k/15k/10k MD steps] + CG).
 A "step" = one M-step over the rank's structures.  `value` = structures/s with everything
-resident in HBM; `e2e` = the same through the C ABI with host buffers (submit -> upload -> run
--> fetch).  The A-step (activation distances + assignment over all structures x pairs) is
+resident in HBM; `e2e` = the same from host buffers through igm_b200.kernel.run_population
+(chunked submit -> upload -> run -> fetch over the C ABI, chunks pipelined on streams).  The A-step (activation distances + assignment over all structures x pairs) is
 timed in the same run and reported under "astep".
 """
 import argparse
