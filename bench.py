@@ -97,21 +97,30 @@ def md_force_evals(prot):
     return n
 
 
-def flops_per_eval(systems, coords, sample=6):
-    """F_eval = 8 P_cand + 21 P_act + 20 B + 9 N_env + 36 N, with the pair counts
-    measured on the optimised coordinates of a few structures (full neighbour rows as the kernel
-    walks them: cutoff ri+rj+skin, skin = max radius)."""
+SKIN = 0.7            # neighbour skin of k_md2 in bead radii (igmk.cu: skin_factor)
+SMEM_PEAK_TBS = 148 * 128 * 1.965e9 / 1e12          # 128 B per clock and SM at max clock (derived)
+
+
+def work_per_eval(systems, coords, sample=6):
+    """Work of one force evaluation of one structure, counted on the optimised coordinates of a few structures.
+    -> (algorithmic flops, executed flops, executed shared-memory bytes)
+    algorithmic: SURVEY.md 8(d), F_eval = 8 P_cand + 21 P_act + 20 B + 9 N_env + 36 N with every pair and every
+      bond counted ONCE (half list; P_cand = pairs inside cutoff + the kernel's skin);
+    executed: k_md2 gathers, so it walks every pair and every bond from both ends (2 P_cand, 2 P_act, 2 B);
+    shared memory: one 16-byte position read per neighbour-table entry and per bond item, plus the atom's own."""
     from scipy.spatial import cKDTree
-    tot = []
+    alg, exe, smem = [], [], []
     for ps, xyz in list(zip(systems, coords))[:sample]:
         n = ps.n_atoms - 1
         r = float(ps.radius[0])
         t = cKDTree(xyz[:n].astype(np.float64))
-        p_cand = t.count_neighbors(t, 3.0 * r) - n          # ordered pairs within cutoff + skin (each visited by its owner)
-        p_act = t.count_neighbors(t, 2.0 * r) - n
-        b = 2 * ps.bond_i.size                              # every bond is evaluated from both ends
-        tot.append(8.0 * p_cand + 21.0 * p_act + 20.0 * b + 9.0 * n + 36.0 * n)
-    return float(np.mean(tot))
+        p_cand = (t.count_neighbors(t, (2.0 + SKIN) * r) - n) // 2     # unordered pairs within cutoff + skin
+        p_act = (t.count_neighbors(t, 2.0 * r) - n) // 2
+        b = ps.bond_i.size
+        alg.append(8.0 * p_cand + 21.0 * p_act + 20.0 * b + 9.0 * n + 36.0 * n)
+        exe.append(2 * (8.0 * p_cand + 21.0 * p_act + 20.0 * b) + 9.0 * n + 36.0 * n)
+        smem.append(16.0 * (2 * p_cand + 2 * b + n))
+    return float(np.mean(alg)), float(np.mean(exe)), float(np.mean(smem))
 
 
 # --------------------------------------------------------------------------------------
@@ -368,7 +377,7 @@ def main():
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
         which = "measured" if "hbm_gbs" in peaks else "fallback"
-        feval = flops_per_eval(systems, coords)
+        feval, feval_exec, smem_eval = work_per_eval(systems, coords)
         evals = md_force_evals(prot)
         md_t = float(np.mean(md_ms)) * 1e-3
         md_tflops = feval * evals * S / md_t / 1e12
@@ -402,6 +411,15 @@ def main():
                          "traffic_note": "scaled from a short ncu --set full capture (profiles/r01_traffic.json): bytes per structure and "
                                          "force evaluation x this launch",
                          "flops_per_force_eval": feval,
+                         "flops_note": "algorithmic = SURVEY 8(d) formula, every pair and bond counted once; the kernel gathers "
+                                       "(no floating-point atomics, deterministic sums) and so executes each from both ends",
+                         "executed": {"flops_per_force_eval": feval_exec,
+                                      "tflops": feval_exec * evals * S / md_t / 1e12,
+                                      "frac": feval_exec * evals * S / md_t / 1e12 / FP32_PEAK_TFLOPS},
+                         "smem": {"bytes_per_force_eval": smem_eval, "achieved": smem_eval * evals * S / md_t / 1e12,
+                                  "peak": SMEM_PEAK_TBS, "unit": "TB/s", "frac": smem_eval * evals * S / md_t / 1e12 / SMEM_PEAK_TBS,
+                                  "note": "16-byte position reads the force loops issue, before bank-conflict replays "
+                                          "(ncu: 2.3x on the gathers, LSU data pipe 54 % busy)"},
                          "kernel_ms": md_t * 1e3, "cg_kernel_ms": float(np.mean(cg_ms)),
                          "peak_source": "derived: 148 SM x 128 lanes x 2 x 1.965 GHz (non-tensor FP32; not in MEASURED_PEAKS.json)"},
             "astep": {"metric": "A-step haploid pairs/sec", "pairs": a["pairs_total"], "rows": a["rows"],

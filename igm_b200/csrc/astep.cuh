@@ -46,6 +46,28 @@ __device__ __forceinline__ float text_roundtrip4(double x) { return text_roundtr
 // order-preserving key for non-negative floats is the bit pattern itself
 __device__ __forceinline__ uint32_t fkey(float v) { return __float_as_uint(v); }
 
+// One step of the radix-256 order-statistic descent, shared by the two activation-distance kernels.
+// hist[bin] = number of live keys whose current digit is `bin` (filled with shared-memory atomics, one bin
+// per thread: AD_THREADS == 256).  Finds the bin that holds rank k, -> (digit, rank inside the bin, bin size)
+// for every thread, and leaves hist zeroed for its next use.  Two barriers.
+__device__ __forceinline__ void radix_pick(uint32_t* hist, uint32_t* wsum, uint32_t* pick, int tid, int lane, int warp,
+                                           uint32_t& k, uint32_t& digit, int& remaining)
+{
+    const uint32_t h = hist[tid];
+    hist[tid] = 0;
+    uint32_t incl = h;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+#pragma unroll
+    for (int w = 0; w < AD_THREADS / 32 - 1; w++) incl += (w < warp) ? wsum[w] : 0u;
+    const uint32_t excl = incl - h;
+    if (k >= excl && k < incl) { pick[0] = (uint32_t)tid; pick[1] = k - excl; pick[2] = h; }   // exactly one thread: k < sum of hist
+    __syncthreads();
+    digit = pick[0]; k = pick[1]; remaining = (int)pick[2];
+}
+
 // One CTA per haploid pair.  Shared memory holds the n_comb * n_struct squared distances.
 // Per-pair outputs: valid flag, activation distance and corrected probability (both already
 // through the text round trip), number of copy combinations emitted.
@@ -60,8 +82,11 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
     __shared__ uint32_t s_mm[2][AD_THREADS / 32];
     __shared__ uint32_t s_fin[32];
     __shared__ int s_nfin;
+    __shared__ uint32_t s_hist[2][AD_THREADS], s_wsum[2][AD_THREADS / 32], s_pick[2][3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = P.n_struct;
+    s_hist[0][tid] = 0; s_hist[1][tid] = 0;               // radix_pick leaves them zeroed again
+    __syncthreads();
 
     for (int64_t pidx = blockIdx.x; pidx < n_pairs; pidx += gridDim.x) {
         const int hi = pair_i[pidx], hj = pair_j[pidx];
@@ -124,38 +149,33 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
         long long o = (long long)rint(prod);
         if (o > (long long)total - 1) o = total - 1;
 
-        // ---- exact o-th smallest (A3): MSB-first descent over the float bit patterns.
-        //      All keys share the bits above the highest bit in which min and max differ.
-        //      The descent stops once the bucket holding the wanted rank has at most 32 members; one warp ranks those.
-        uint32_t prefix, k = (uint32_t)o;
-        int bit, remaining = total;
-        if (kmin == kmax) { prefix = kmin; bit = -1; }
-        else { bit = 31 - __clz(kmin ^ kmax); prefix = (bit == 31) ? 0u : (kmin >> (bit + 1)) << (bit + 1); }
-        int par = 1;
+        // ---- exact o-th smallest (A3): radix-256 descent over (bit pattern - smallest bit pattern), most
+        //      significant digit first; stops once the bin holding the wanted rank has at most 32 members,
+        //      which one warp then ranks directly.  Two or three passes instead of one per bit.
+        uint32_t prefix = 0, k = (uint32_t)o;
+        int remaining = total;
+        int bit = kmin == kmax ? -1 : 31 - __clz(kmax - kmin);        // highest bit any offset key has set
+        int par = 0;
         if (tid == 0) s_nfin = 0;
-        for (; bit >= 0 && remaining > 32; bit--) {
+        while (bit >= 0 && remaining > 32) {
+            const int shift = max(bit - 7, 0);
             const uint32_t hmask = (bit == 31) ? 0u : (0xffffffffu << (bit + 1));
-            int c0 = 0;                                   // keys matching the prefix with this bit clear
             for (int q = tid; q < total; q += AD_THREADS) {
-                const uint32_t key = fkey(dsq[q]);
-                c0 += ((key & hmask) == prefix) && !((key >> bit) & 1u);
+                const uint32_t key = fkey(dsq[q]) - kmin;
+                if ((key & hmask) == prefix) atomicAdd(&s_hist[par][(key - prefix) >> shift], 1u);
             }
-#pragma unroll
-            for (int o2 = 16; o2 > 0; o2 >>= 1) c0 += __shfl_xor_sync(0xffffffffu, c0, o2);
-            if (lane == 0) s_red[par][warp] = c0;
             __syncthreads();
-            c0 = 0;
-#pragma unroll
-            for (int w = 0; w < AD_THREADS / 32; w++) c0 += s_red[par][w];
+            uint32_t digit;
+            radix_pick(s_hist[par], s_wsum[par], s_pick[par], tid, lane, warp, k, digit, remaining);
+            prefix |= digit << shift;
+            bit = shift - 1;
             par ^= 1;
-            if (k >= (uint32_t)c0) { k -= (uint32_t)c0; prefix |= (1u << bit); remaining -= c0; }
-            else remaining = c0;
         }
         if (bit >= 0) {
             const uint32_t hmask = (bit == 31) ? 0u : (0xffffffffu << (bit + 1));
             __syncthreads();                              // s_nfin = 0 is visible
             for (int q = tid; q < total; q += AD_THREADS) {
-                const uint32_t key = fkey(dsq[q]);
+                const uint32_t key = fkey(dsq[q]) - kmin;
                 if ((key & hmask) == prefix) s_fin[atomicAdd(&s_nfin, 1)] = key;
             }
             __syncthreads();
@@ -171,6 +191,7 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
                 prefix = __shfl_sync(0xffffffffu, mine, __ffs(hit) - 1);
             }
         }
+        prefix += kmin;                                   // back to the bit pattern of the squared distance
         if (tid == 0) {
             const double ad = sqrt((double)__uint_as_float(prefix));            // :446
             out_dist[pidx] = text_roundtrip4(ad);
@@ -181,65 +202,139 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
     }
 }
 
+// GW consecutive structures of one bead row (3 GW floats at `row`), of which the first `nvalid` exist
+template <int GW>
+__device__ __forceinline__ void load_group(const float* __restrict__ row, int nvalid, bool vec, float (&v)[3 * GW])
+{
+    if constexpr (GW == 4) {
+        if (vec) {                                        // whole groups only: n_struct is a multiple of 4
+            if (nvalid > 0) {
+                const float4* r4 = reinterpret_cast<const float4*>(row);
+                const float4 q0 = __ldg(r4), q1 = __ldg(r4 + 1), q2 = __ldg(r4 + 2);
+                v[0] = q0.x; v[1] = q0.y; v[2] = q0.z; v[3] = q0.w; v[4] = q1.x; v[5] = q1.y; v[6] = q1.z; v[7] = q1.w;
+                v[8] = q2.x; v[9] = q2.y; v[10] = q2.z; v[11] = q2.w;
+            }
+            return;
+        }
+    }
+#pragma unroll
+    for (int w = 0; w < GW; w++)
+        if (w < nvalid) { v[3 * w] = __ldg(row + 3 * w); v[3 * w + 1] = __ldg(row + 3 * w + 1); v[3 * w + 2] = __ldg(row + 3 * w + 2); }
+}
+
 // Register-resident variant for populations of up to 256 * SPT structures (n_comb <= 4): every thread
-// keeps its 4 * SPT squared distances in registers, the bitwise descent stops as soon as the bucket
+// keeps its 4 * SPT squared distances in registers, the radix-256 descent stops as soon as the bin
 // that holds the wanted order statistic has at most 32 members, and one warp ranks those directly.
 // Same arithmetic, same results as k_actdist; roughly 4x fewer instructions per pair.
-#ifndef AD_REG_MIN_BLOCKS
-#define AD_REG_MIN_BLOCKS 4
-#endif
-template <int SPT>
-__global__ void __launch_bounds__(AD_THREADS, AD_REG_MIN_BLOCKS)
-k_actdist_reg(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const int32_t* __restrict__ pair_j,
-              const double* __restrict__ pwish, const double* __restrict__ plast, float contact_range_f32,
+// Everything k_actdist_reg needs to know about one pair, resolved once by k_actdist_meta: the chain
+// pair -> copy_off -> copy_beads -> radii is four dependent loads, too long to sit in front of every pair.
+struct __align__(16) PairMeta {
+    int32_t bi[4], bj[4];        // beads of combination c (copies of i and of j)
+    float   rcutsq;              // (contact_range * (ri + rj))^2 in float32, :368
+    int32_t ncomb;               // n_possible_contacts; 0: i == j, no row (:351-352)
+    int32_t pad[2];
+    double  pl, pw;              // plast, pwish
+};
+static_assert(sizeof(PairMeta) == 64, "PairMeta is four 16-byte loads");
+
+__global__ void __launch_bounds__(256)
+k_actdist_meta(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const int32_t* __restrict__ pair_j,
+               const double* __restrict__ pwish, const double* __restrict__ plast, float contact_range_f32,
+               PairMeta* __restrict__ meta)
+{
+    for (int64_t pidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; pidx < n_pairs; pidx += (int64_t)gridDim.x * blockDim.x) {
+        const int hi = pair_i[pidx], hj = pair_j[pidx];
+        PairMeta m;
+        for (int c = 0; c < 4; c++) { m.bi[c] = 0; m.bj[c] = 0; }
+        m.rcutsq = 0.f; m.ncomb = 0; m.pad[0] = m.pad[1] = 0; m.pl = plast[pidx]; m.pw = pwish[pidx];
+        if (hi != hj) {
+            const int io = P.copy_off[hi], jo = P.copy_off[hj];
+            const int ni = P.copy_off[hi + 1] - io, nj = P.copy_off[hj + 1] - jo;
+            const bool intra = P.chrom[hi] == P.chrom[hj];
+            m.ncomb = min(intra ? min(ni, nj) : ni * nj, 4);      // :384-385, :400-401 (the launcher guarantees <= 4)
+            for (int c = 0; c < m.ncomb; c++) {
+                m.bi[c] = P.copy_beads[io + (intra ? c : c / nj)];
+                m.bj[c] = P.copy_beads[jo + (intra ? c : c % nj)];
+            }
+            const float ri = P.radii[P.copy_beads[io]], rj = P.radii[P.copy_beads[jo]];
+            const float rc = __fmul_rn(contact_range_f32, __fadd_rn(ri, rj));
+            m.rcutsq = __fmul_rn(rc, rc);
+        }
+        meta[pidx] = m;
+    }
+}
+
+template <int SPT, int MINB>
+__global__ void __launch_bounds__(AD_THREADS, MINB)
+k_actdist_reg(PopView P, int64_t n_pairs, const PairMeta* __restrict__ meta,
               float* __restrict__ out_dist, float* __restrict__ out_prob, uint8_t* __restrict__ out_valid)
 {
+    // buffers indexed by the parity of the pair: no barrier at the end of a pair, the warps that do not
+    // take part in the final ranking go on to the loads of the next pair
     __shared__ int s_red[2][AD_THREADS / 32];
-    __shared__ uint32_t s_mm[2][AD_THREADS / 32];
-    __shared__ uint32_t s_fin[32];
-    __shared__ int s_nfin;
+    __shared__ uint32_t s_mm[2][2][AD_THREADS / 32];
+    __shared__ uint32_t s_fin[2][32];
+    __shared__ int s_nfin[2];
+    __shared__ uint32_t s_hist[2][AD_THREADS], s_wsum[2][AD_THREADS / 32], s_pick[2][3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = P.n_struct;
+    s_hist[0][tid] = 0; s_hist[1][tid] = 0;               // radix_pick leaves them zeroed again
+    __syncthreads();
+    // Thread t owns the structures GW * (t + 256 g) .. + GW - 1 of group g: GW consecutive structures are
+    // 3 GW consecutive floats of a bead row, fetched with three 16-byte loads when GW == 4 and the rows are
+    // 16-byte aligned (a warp still reads one contiguous run).
+    constexpr int GW = SPT < 4 ? SPT : 4, NG = SPT / GW;
+    const bool vec = GW == 4 && (S & 3) == 0 && (reinterpret_cast<uintptr_t>(P.crd) & 15) == 0;
+    int pp = 0;
 
     for (int64_t pidx = blockIdx.x; pidx < n_pairs; pidx += gridDim.x) {
-        const int hi = pair_i[pidx], hj = pair_j[pidx];
-        if (hi == hj) {                                   // :351-352
+        // the record is read piecewise where it is needed (L1 hits after the first touch): fewer live registers
+        const PairMeta* mp = meta + pidx;
+        if (pidx + gridDim.x < n_pairs && tid == 0)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(mp + gridDim.x));
+        const int2 head = __ldg(reinterpret_cast<const int2*>(&mp->rcutsq));
+        const int ncomb = head.y;
+        if (ncomb == 0) {                                 // :351-352
             if (tid == 0) out_valid[pidx] = 0;
             continue;
         }
-        const int io = P.copy_off[hi], jo = P.copy_off[hj];
-        const int ni = P.copy_off[hi + 1] - io, nj = P.copy_off[hj + 1] - jo;
-        const bool intra = P.chrom[hi] == P.chrom[hj];
-        const int ncomb = intra ? min(ni, nj) : ni * nj;
-        const float ri = P.radii[P.copy_beads[io]], rj = P.radii[P.copy_beads[jo]];
-        const float rc = __fmul_rn(contact_range_f32, __fadd_rn(ri, rj));
-        const float rcutsq = __fmul_rn(rc, rc);
+        const float rcutsq = __int_as_float(head.x);
         const int total = ncomb * S;
 
         uint32_t key[4 * SPT];                            // 0xffffffff: empty slot (never matches a prefix)
+#pragma unroll
+        for (int u = 0; u < 4 * SPT; u++) key[u] = 0xffffffffu;
         int cnt = 0;
         uint32_t kmin = 0xffffffffu, kmax = 0u;
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
-            const float *xi = nullptr, *xj = nullptr;
-            if (c < ncomb) {
-                xi = P.crd + (size_t)P.copy_beads[io + (intra ? c : c / nj)] * S * 3;
-                xj = P.crd + (size_t)P.copy_beads[jo + (intra ? c : c % nj)] * S * 3;
-            }
+        for (int g = 0; g < NG; g++) {
+            const int sbase = GW * (tid + AD_THREADS * g);
+            if (sbase < S) {
+                float xi[3 * GW], xj[3 * GW];
+                int bi_prev = -1;
 #pragma unroll
-            for (int w = 0; w < SPT; w++) {
-                const int sidx = tid + AD_THREADS * w;
-                uint32_t k = 0xffffffffu;
-                if (c < ncomb && sidx < S) {
-                    const float dx = __fsub_rn(xi[3 * sidx], xj[3 * sidx]);
-                    const float dy = __fsub_rn(xi[3 * sidx + 1], xj[3 * sidx + 1]);
-                    const float dz = __fsub_rn(xi[3 * sidx + 2], xj[3 * sidx + 2]);
-                    const float v = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-                    cnt += (v <= rcutsq);
-                    k = fkey(v);
-                    kmin = min(kmin, k); kmax = max(kmax, k);
+                for (int c = 0; c < 4; c++) {
+                    if (c < ncomb) {
+                        const int bic = __ldg(&mp->bi[c]), bjc = __ldg(&mp->bj[c]);
+                        if (c == 0 || bic != bi_prev)     // a copy of i that serves two combinations is loaded once
+                            load_group<GW>(P.crd + ((size_t)bic * S + sbase) * 3, S - sbase, vec, xi);
+                        bi_prev = bic;
+                        load_group<GW>(P.crd + ((size_t)bjc * S + sbase) * 3, S - sbase, vec, xj);
+#pragma unroll
+                        for (int w = 0; w < GW; w++) {
+                            if (vec || sbase + w < S) {   // vec: whole groups only
+                                const float dx = __fsub_rn(xi[3 * w], xj[3 * w]);
+                                const float dy = __fsub_rn(xi[3 * w + 1], xj[3 * w + 1]);
+                                const float dz = __fsub_rn(xi[3 * w + 2], xj[3 * w + 2]);
+                                const float v = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                                cnt += (v <= rcutsq);
+                                const uint32_t k = fkey(v);
+                                kmin = min(kmin, k); kmax = max(kmax, k);
+                                key[c * SPT + g * GW + w] = k;
+                            }
+                        }
+                    }
                 }
-                key[c * SPT + w] = k;
             }
         }
 #pragma unroll
@@ -248,47 +343,46 @@ k_actdist_reg(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, co
             kmin = min(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
             kmax = max(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
         }
-        if (lane == 0) { s_red[0][warp] = cnt; s_mm[0][warp] = kmin; s_mm[1][warp] = kmax; }
-        if (tid == 0) s_nfin = 0;
+        if (lane == 0) { s_red[pp][warp] = cnt; s_mm[pp][0][warp] = kmin; s_mm[pp][1][warp] = kmax; }
+        if (tid == 0) s_nfin[pp] = 0;
         __syncthreads();
         cnt = 0; kmin = 0xffffffffu; kmax = 0u;
 #pragma unroll
-        for (int w = 0; w < AD_THREADS / 32; w++) { cnt += s_red[0][w]; kmin = min(kmin, s_mm[0][w]); kmax = max(kmax, s_mm[1][w]); }
+        for (int w = 0; w < AD_THREADS / 32; w++) { cnt += s_red[pp][w]; kmin = min(kmin, s_mm[pp][0][w]); kmax = max(kmax, s_mm[pp][1][w]); }
+        const int pq = pp;
+        pp ^= 1;
 
         const double pnow = (double)cnt / (double)(ncomb * S);                  // :422
-        const double pl = plast[pidx], pw = pwish[pidx];
+        const double pl = __ldg(&mp->pl), pw = __ldg(&mp->pw);
         double t = pl < 1.0 ? (pnow - pl) / (1.0 - pl) : pnow; t = t > 0.0 ? t : 0.0;   // :430
         double p = t < 1.0 ? (pw - t) / (1.0 - t) : pw; p = p > 0.0 ? p : 0.0;          // :434
         if (!(p > 0.0)) {
             if (tid == 0) out_valid[pidx] = 0;
-            __syncthreads();
             continue;
         }
         const double prod = ((double)ncomb * p) * (double)S;                    // :443-444
         long long o = (long long)rint(prod);
         if (o > (long long)total - 1) o = total - 1;
 
-        // exact o-th smallest: MSB-first descent below the bits min and max share
-        uint32_t prefix, k = (uint32_t)o;
-        int bit, remaining = total;
-        if (kmin == kmax) { prefix = kmin; bit = -1; }
-        else { bit = 31 - __clz(kmin ^ kmax); prefix = (kmin >> (bit + 1)) << (bit + 1); }   // bit <= 30: keys are >= 0
-        int par = 1;
-        for (; bit >= 0 && remaining > 32; bit--) {
+        // exact o-th smallest: radix-256 descent over (bit pattern - smallest bit pattern), as in k_actdist
+#pragma unroll
+        for (int u = 0; u < 4 * SPT; u++) key[u] -= kmin;         // empty slots keep bit 31: kmin < 2^31
+        uint32_t prefix = 0, k = (uint32_t)o;
+        int remaining = total;
+        int bit = kmin == kmax ? -1 : 31 - __clz(kmax - kmin);        // <= 30: the keys are bit patterns of floats >= 0
+        int par = 0;
+        while (bit >= 0 && remaining > 32) {
+            const int shift = max(bit - 7, 0);
             const uint32_t hmask = 0xffffffffu << (bit + 1);
-            int c0 = 0;
 #pragma unroll
-            for (int u = 0; u < 4 * SPT; u++) c0 += ((key[u] & hmask) == prefix) && !((key[u] >> bit) & 1u);
-#pragma unroll
-            for (int o2 = 16; o2 > 0; o2 >>= 1) c0 += __shfl_xor_sync(0xffffffffu, c0, o2);
-            if (lane == 0) s_red[par][warp] = c0;
+            for (int u = 0; u < 4 * SPT; u++)
+                if ((key[u] & hmask) == prefix) atomicAdd(&s_hist[par][(key[u] - prefix) >> shift], 1u);
             __syncthreads();
-            c0 = 0;
-#pragma unroll
-            for (int w = 0; w < AD_THREADS / 32; w++) c0 += s_red[par][w];
+            uint32_t digit;
+            radix_pick(s_hist[par], s_wsum[par], s_pick[par], tid, lane, warp, k, digit, remaining);
+            prefix |= digit << shift;
+            bit = shift - 1;
             par ^= 1;
-            if (k >= (uint32_t)c0) { k -= (uint32_t)c0; prefix |= (1u << bit); remaining -= c0; }
-            else remaining = c0;
         }
         uint32_t answer = prefix;
         if (bit >= 0) {
@@ -296,27 +390,26 @@ k_actdist_reg(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, co
             const uint32_t hmask = 0xffffffffu << (bit + 1);
 #pragma unroll
             for (int u = 0; u < 4 * SPT; u++)
-                if ((key[u] & hmask) == prefix) s_fin[atomicAdd(&s_nfin, 1)] = key[u];
+                if ((key[u] & hmask) == prefix) s_fin[pq][atomicAdd(&s_nfin[pq], 1)] = key[u];
             __syncthreads();
             if (warp == 0) {
-                const uint32_t mine = lane < remaining ? s_fin[lane] : 0xffffffffu;
+                const uint32_t mine = lane < remaining ? s_fin[pq][lane] : 0xffffffffu;
                 int rank = 0;
 #pragma unroll
-                for (int m = 0; m < 32; m++) {
-                    const uint32_t other = __shfl_sync(0xffffffffu, mine, m);
-                    rank += (other < mine) || (other == mine && m < lane);
+                for (int mm = 0; mm < 32; mm++) {
+                    const uint32_t other = __shfl_sync(0xffffffffu, mine, mm);
+                    rank += (other < mine) || (other == mine && mm < lane);
                 }
                 const uint32_t hit = __ballot_sync(0xffffffffu, rank == (int)k && lane < remaining);
                 answer = __shfl_sync(0xffffffffu, mine, __ffs(hit) - 1);
             }
         }
         if (tid == 0) {
-            const double ad = sqrt((double)__uint_as_float(answer));            // :446
+            const double ad = sqrt((double)__uint_as_float(answer + kmin));     // :446; + kmin: back to the bit pattern
             out_dist[pidx] = text_roundtrip4(ad);
             out_prob[pidx] = text_roundtrip4(p);
             out_valid[pidx] = 1;
         }
-        __syncthreads();
     }
 }
 

@@ -903,7 +903,7 @@ struct igmk_pop {
     int64_t n_pairs = 0;
     std::vector<int32_t> h_pi, h_pj;
     DevBuf<int32_t> d_pi, d_pj; DevBuf<double> d_pw, d_pl;
-    DevBuf<float> d_dist, d_prob; DevBuf<uint8_t> d_valid; DevBuf<double> d_den;
+    DevBuf<float> d_dist, d_prob; DevBuf<uint8_t> d_valid; DevBuf<double> d_den; DevBuf<PairMeta> d_meta;
     std::vector<float> radii;
     bool actdist_done = false;
     // staged actdist rows (assignment)
@@ -923,7 +923,7 @@ struct igmk_pop {
         if (own_crd) cudaFree(d_crd);
         cudaFree(d_radii); cudaFree(d_chrom); cudaFree(d_copy_off); cudaFree(d_copy_beads);
         d_pi.release(); d_pj.release(); d_pw.release(); d_pl.release(); d_dist.release(); d_prob.release();
-        d_valid.release(); d_den.release(); d_row.release(); d_col.release(); d_rdist.release(); d_bits.release();
+        d_valid.release(); d_den.release(); d_meta.release(); d_row.release(); d_col.release(); d_rdist.release(); d_bits.release();
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -1055,17 +1055,25 @@ extern "C" int igmk_pop_actdist_launch(igmk_pop_t* p, double contact_range)
     if (p->n_pairs == 0) { p->actdist_done = true; return 0; }
     CU(cudaSetDevice(p->device));
     const int spt = (p->n_struct + AD_THREADS - 1) / AD_THREADS;       // structures per thread
-    if (spt <= 8 && !getenv("IGMK_ACTDIST_SMEM")) {
+    if (spt <= 8 && p->max_copies * p->max_copies <= 4 && !getenv("IGMK_ACTDIST_SMEM")) {   // the kernel holds 4 combinations
         // register-resident selection (up to 2048 structures)
-        void (*kern)(PopView, int64_t, const int32_t*, const int32_t*, const double*, const double*, float, float*, float*, uint8_t*) =
-            spt <= 1 ? k_actdist_reg<1> : spt <= 2 ? k_actdist_reg<2> : spt <= 4 ? k_actdist_reg<4> : k_actdist_reg<8>;
+        void (*kern)(PopView, int64_t, const PairMeta*, float*, float*, uint8_t*) =
+            spt <= 1 ? k_actdist_reg<1, 4> : spt <= 2 ? k_actdist_reg<2, 4> : spt <= 4 ? k_actdist_reg<4, 4> : k_actdist_reg<8, 3>;   // measured: 16 keys/thread want 4 CTAs per SM, 32 keys 3
+        if (const char* e = getenv("IGMK_ACTDIST_MINB")) {       // resident CTAs per SM the kernel is compiled for (tuning aid)
+            const int m = atoi(e);
+            if (spt > 2 && spt <= 4) kern = m == 3 ? k_actdist_reg<4, 3> : m == 2 ? k_actdist_reg<4, 2> : kern;
+            if (spt > 4) kern = m == 4 ? k_actdist_reg<8, 4> : m == 2 ? k_actdist_reg<8, 2> : kern;
+        }
         int per_sm = 1;
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, AD_THREADS, 0));
         if (per_sm < 1) per_sm = 1;
         const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * per_sm);
+        CU(p->d_meta.reserve((size_t)p->n_pairs));
         CU(cudaEventRecord(p->ev0, p->stream));
-        kern<<<(int)grid, AD_THREADS, 0, p->stream>>>(p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, p->d_pw.p, p->d_pl.p,
-                                                      (float)contact_range, p->d_dist.p, p->d_prob.p, p->d_valid.p);
+        k_actdist_meta<<<(int)std::min<int64_t>((p->n_pairs + 255) / 256, (int64_t)p->sm_count * 8), 256, 0, p->stream>>>(
+            p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, p->d_pw.p, p->d_pl.p, (float)contact_range, p->d_meta.p);
+        CU(cudaGetLastError());
+        kern<<<(int)grid, AD_THREADS, 0, p->stream>>>(p->view(), p->n_pairs, p->d_meta.p, p->d_dist.p, p->d_prob.p, p->d_valid.p);
     } else {
         const size_t smem = (size_t)p->max_copies * p->max_copies * p->n_struct * sizeof(float);
         if ((long long)smem + 1024 > (long long)p->smem_optin) {
