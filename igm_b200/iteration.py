@@ -63,3 +63,24 @@ def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, 
     out["timings"].update({"mstep_s": time.perf_counter() - t0 - t_astep, "md_kernel_ms": md_ms, "cg_kernel_ms": cg_ms,
                            "h2d_bytes": h2d, "total_s": time.perf_counter() - t0})
     return out
+
+
+def relax_init(crd_local, template, optimizer_options, device=0, seeds=None, bond_prefactor=1.0):
+    """What ``RelaxInit.task`` does for every structure of a freshly generated population
+    (igm/steps/RelaxInit.py:86-178: Steric + Envelope + Polymer only, then ``model.optimize``), for this
+    rank's block of structures at once.  crd_local: float32 [n_bead][S_local][3] (``generate_territories``
+    output, RandomInit.py:69-102); template: PackedSystem with those three restraints.
+    -> (relaxed coordinates, same layout; [info dict] * S_local)."""
+    rank, _ = parallel.world()
+    crd_local = np.ascontiguousarray(crd_local, dtype=np.float32)
+    n_bead = crd_local.shape[0]
+    none_i = np.zeros(0, dtype=np.int32)
+    protocol = _abi.make_protocol(optimizer_options, bond_prefactor=bond_prefactor)
+    new, results, _, _ = run_population(template, crd_local, n_bead, none_i, none_i, np.zeros(0), 1.0,
+                                        np.zeros((0, 1), dtype=np.uint32), protocol, device=device, seeds=seeds)
+    infos = []
+    for k, res in enumerate(results):
+        if res.status != 0 or not np.isfinite(res.final_energy):
+            raise RuntimeError("b200 kernel produced non-finite coordinates or energy (structure %d of rank %d)" % (k, rank))
+        infos.append(info_from_result(res))
+    return new, infos

@@ -54,3 +54,40 @@ def test_am_iteration_statistics_match_cpu():
     assert np.median(e_gpu) <= 10 * np.median(e_cpu) + 1.0 and np.median(e_cpu) <= 10 * np.median(e_gpu) + 1.0
     # every bead ends inside the nucleus
     assert (np.linalg.norm(out["coordinates"], axis=2) + rad[:, None] <= R * 1.02).all()
+
+
+def test_relax_init_removes_overlaps_and_keeps_the_polymer():
+    """RelaxInit.task for a block of structures (RelaxInit.py:86-178): territories in, relaxed
+    coordinates out -- inside the envelope, consecutive beads within the polymer bond length, the
+    excluded-volume energy far below where it started; identical to the same structures submitted one
+    by one (the population path only changes who assembles them)."""
+    from igm_b200.iteration import relax_init
+    from igm_b200.kernel import MStepBatch
+    from igm_b200 import _abi
+    g = synth.Genome([16, 12, 9, 6], n_autosomes=3)
+    R = 1500.0
+    rad = synth.bead_radii(len(g), R, 0.3)
+    S = 9
+    crd = synth.population_territories(g, S, R=R, seed=31)
+    opts = synth.demo_protocol_options()
+    opts["custom_annealing_protocol"]["mdsteps"] = [300, 600, 600, 400]
+    opts["custom_annealing_protocol"]["relax"]["mdsteps"] = 50
+    template = synth.pack_structure(np.zeros((len(g), 3), dtype=np.float32), rad, g, nucleus_radius=R, seed=0, struct_id=0)
+    seeds = np.arange(S, dtype=np.int64) + 11
+    new, infos = relax_init(crd, template, opts, seeds=seeds)
+    assert new.shape == crd.shape and len(infos) == S and np.isfinite(new).all()
+    assert (np.linalg.norm(new, axis=2) + rad[:, None] <= R * 1.02).all()
+    with MStepBatch(0) as b:
+        for s in range(S):
+            b.submit(synth.pack_structure(crd[:, s, :], rad, g, nucleus_radius=R, seed=int(seeds[s]), struct_id=s))
+        b.single_point()
+        e0 = [b.fetch(s)[1].pair_energy for s in range(S)]
+        b.run(_abi.make_protocol(opts))
+        for s in range(S):
+            xyz, res = b.fetch(s)
+            assert np.array_equal(xyz[:len(g)].view(np.uint32), new[:, s, :].view(np.uint32))
+            assert infos[s]["final-energy"] == res.final_energy
+            assert res.pair_energy < 0.05 * e0[s] + 1.0
+    # polymer bonds of the template hold: consecutive beads of a chain no further apart than r0 (+5 %)
+    d = np.linalg.norm(new[template.bond_i] - new[template.bond_j], axis=2)
+    assert (d <= template.bond_r0[:, None] * 1.05).all()
