@@ -48,44 +48,47 @@ __device__ __forceinline__ uint32_t fkey(float v) { return __float_as_uint(v); }
 
 // One step of the radix-256 order-statistic descent, shared by the two activation-distance kernels.
 // hist[bin] = number of live keys whose current digit is `bin` (filled with shared-memory atomics, one bin
-// per thread: AD_THREADS == 256).  Finds the bin that holds rank k, -> (digit, rank inside the bin, bin size)
+// per thread of the first AD_THREADS == 256).  Finds the bin that holds rank k, -> (digit, rank inside the bin, bin size)
 // for every thread, and leaves hist zeroed for its next use.  Two barriers.
 __device__ __forceinline__ void radix_pick(uint32_t* hist, uint32_t* wsum, uint32_t* pick, int tid, int lane, int warp,
                                            uint32_t& k, uint32_t& digit, int& remaining)
 {
-    const uint32_t h = hist[tid];
-    hist[tid] = 0;
+    uint32_t h = 0;
+    if (tid < AD_THREADS) { h = hist[tid]; hist[tid] = 0; }    // CTAs of more than 256 threads: the others only keep the barriers
     uint32_t incl = h;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-    if (lane == 31) wsum[warp] = incl;
+    if (lane == 31 && warp < AD_THREADS / 32) wsum[warp] = incl;
     __syncthreads();
 #pragma unroll
     for (int w = 0; w < AD_THREADS / 32 - 1; w++) incl += (w < warp) ? wsum[w] : 0u;
     const uint32_t excl = incl - h;
-    if (k >= excl && k < incl) { pick[0] = (uint32_t)tid; pick[1] = k - excl; pick[2] = h; }   // exactly one thread: k < sum of hist
+    if (k >= excl && k < incl) { pick[0] = (uint32_t)tid; pick[1] = k - excl; pick[2] = h; }   // exactly one thread: k < sum of hist, h > 0
     __syncthreads();
     digit = pick[0]; k = pick[1]; remaining = (int)pick[2];
 }
 
-// One CTA per haploid pair.  Shared memory holds the n_comb * n_struct squared distances.
+// One CTA of NT threads per haploid pair.  Shared memory holds the n_comb * n_struct squared distances; when
+// that leaves room for fewer than three 256-thread CTAs per SM the launcher takes NT = 1024, so that enough
+// coordinate loads are in flight to stream from HBM (the slab no longer fits L2 at these sizes).
 // Per-pair outputs: valid flag, activation distance and corrected probability (both already
 // through the text round trip), number of copy combinations emitted.
-__global__ void __launch_bounds__(AD_THREADS)
+template <int NT>
+__global__ void __launch_bounds__(NT)
 k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const int32_t* __restrict__ pair_j,
           const double* __restrict__ pwish, const double* __restrict__ plast, float contact_range_f32,
           float* __restrict__ out_dist, float* __restrict__ out_prob, uint8_t* __restrict__ out_valid)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* dsq = (float*)smem_raw;
-    __shared__ int s_red[2][AD_THREADS / 32];
-    __shared__ uint32_t s_mm[2][AD_THREADS / 32];
+    __shared__ int s_red[2][NT / 32];
+    __shared__ uint32_t s_mm[2][NT / 32];
     __shared__ uint32_t s_fin[32];
     __shared__ int s_nfin;
     __shared__ uint32_t s_hist[2][AD_THREADS], s_wsum[2][AD_THREADS / 32], s_pick[2][3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = P.n_struct;
-    s_hist[0][tid] = 0; s_hist[1][tid] = 0;               // radix_pick leaves them zeroed again
+    if (tid < AD_THREADS) { s_hist[0][tid] = 0; s_hist[1][tid] = 0; }   // radix_pick leaves them zeroed again
     __syncthreads();
 
     for (int64_t pidx = blockIdx.x; pidx < n_pairs; pidx += gridDim.x) {
@@ -111,7 +114,7 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
             const int bj = P.copy_beads[jo + (intra ? c : c % nj)];
             const float* xi = P.crd + (size_t)bi * S * 3;
             const float* xj = P.crd + (size_t)bj * S * 3;
-            for (int s = tid; s < S; s += AD_THREADS) {
+            for (int s = tid; s < S; s += NT) {
                 const float dx = __fsub_rn(xi[3 * s], xj[3 * s]);
                 const float dy = __fsub_rn(xi[3 * s + 1], xj[3 * s + 1]);
                 const float dz = __fsub_rn(xi[3 * s + 2], xj[3 * s + 2]);
@@ -132,7 +135,7 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
         __syncthreads();
         cnt = 0; kmin = 0xffffffffu; kmax = 0u;
 #pragma unroll
-        for (int w = 0; w < AD_THREADS / 32; w++) { cnt += s_red[0][w]; kmin = min(kmin, s_mm[0][w]); kmax = max(kmax, s_mm[1][w]); }
+        for (int w = 0; w < NT / 32; w++) { cnt += s_red[0][w]; kmin = min(kmin, s_mm[0][w]); kmax = max(kmax, s_mm[1][w]); }
 
         // ---- probability correction (A4), float64 exactly as the host does it ----
         const double pnow = (double)cnt / (double)(ncomb * S);                  // :422
@@ -160,7 +163,7 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
         while (bit >= 0 && remaining > 32) {
             const int shift = max(bit - 7, 0);
             const uint32_t hmask = (bit == 31) ? 0u : (0xffffffffu << (bit + 1));
-            for (int q = tid; q < total; q += AD_THREADS) {
+            for (int q = tid; q < total; q += NT) {
                 const uint32_t key = fkey(dsq[q]) - kmin;
                 if ((key & hmask) == prefix) atomicAdd(&s_hist[par][(key - prefix) >> shift], 1u);
             }
@@ -174,7 +177,7 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
         if (bit >= 0) {
             const uint32_t hmask = (bit == 31) ? 0u : (0xffffffffu << (bit + 1));
             __syncthreads();                              // s_nfin = 0 is visible
-            for (int q = tid; q < total; q += AD_THREADS) {
+            for (int q = tid; q < total; q += NT) {
                 const uint32_t key = fkey(dsq[q]) - kmin;
                 if ((key & hmask) == prefix) s_fin[atomicAdd(&s_nfin, 1)] = key;
             }

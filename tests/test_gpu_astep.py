@@ -45,12 +45,14 @@ def test_download_roundtrip(astep_golden):
 
 
 @pytest.mark.parametrize("n_struct,seed,force_smem", [(1, 1, False), (33, 2, False), (257, 3, False), (1000, 4, False),
-                                                      (1500, 5, False), (2100, 6, False), (1000, 7, True)])
+                                                      (1500, 5, False), (2100, 6, False), (1000, 7, True), (777, 8, "wide")])
 def test_actdist_and_assign_vs_oracle_synthetic(n_struct, seed, force_smem, monkeypatch):
     """ragged structure counts (not multiples of 32 / 256), X/Y single-copy bins, plast in {0, <1, 1};
     covers the register-resident kernel (<= 2048 structures) and the shared-memory one"""
     if force_smem:
         monkeypatch.setenv("IGMK_ACTDIST_SMEM", "1")
+    if force_smem == "wide":                          # the 1024-thread form of the shared-memory kernel
+        monkeypatch.setenv("IGMK_ACTDIST_NT", "1024")
     g = synth.Genome([9, 7, 6, 4, 3], n_autosomes=3)
     rad = synth.bead_radii(len(g), 1500.0, 0.3)
     crd = synth.population_territories(g, n_struct, R=1500.0, seed=seed)
