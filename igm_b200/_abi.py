@@ -188,6 +188,7 @@ _SIGNATURES = {
     "igmk_single_point_f32": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double]),
     "igmk_fetch": (C.c_int, [_vp, C.c_int32, c_f32p, C.POINTER(Result)]),
     "igmk_fetch_forces": (C.c_int, [_vp, C.c_int32, c_f64p]),
+    "igmk_layout_stats": (C.c_int, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),
     "igmk_fetch_population": (C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, c_f32p, C.POINTER(Result)]),
     "igmk_violation_ratios": (C.c_int, [_vp, C.c_int32, c_f64p, c_f64p]),
     "igmk_last_timings": (C.c_int, [_vp, c_f64p, c_f64p, c_i64p]),

@@ -128,6 +128,13 @@ extern "C" int igmk_device_count(void)
 extern "C" int igmk_create(int device, igmk_handle_t** out)
 {
     if (!out) return fail("igmk_create: out is NULL");
+    if (device == IGMK_STAGING_ONLY) {          // host staging without a GPU: submit / slot_sizes / layout_stats only
+        igmk_handle* h = new igmk_handle();
+        h->device = IGMK_STAGING_ONLY;
+        h->smem_optin = 227 * 1024;             // the B200 opt-in limit, for the same size checks as on the device
+        *out = h;
+        return 0;
+    }
     int n = 0;
     CU(cudaGetDeviceCount(&n));
     if (device < 0 || device >= n) return fail("igmk_create: no such CUDA device");
@@ -157,6 +164,7 @@ extern "C" int igmk_create(int device, igmk_handle_t** out)
 extern "C" int igmk_destroy(igmk_handle_t* h)
 {
     if (!h) return 0;
+    if (h->device < 0) { delete h; return 0; }
     cudaSetDevice(h->device);
     h->free_device();
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -168,8 +176,10 @@ extern "C" int igmk_destroy(igmk_handle_t* h)
 extern "C" int igmk_clear(igmk_handle_t* h)
 {
     if (!h) return fail("igmk_clear: NULL handle");
-    cudaSetDevice(h->device);
-    h->free_device();
+    if (h->device >= 0) {
+        cudaSetDevice(h->device);
+        h->free_device();
+    }
     h->desc.clear(); h->xyzr.clear(); h->xyzr0.clear(); h->kind.clear(); h->envmask.clear(); h->bond_ptr.clear();
     h->bond_items.clear(); h->btype_f.clear(); h->btype_d.clear(); h->struct_id.clear();
     h->sub_bonds.clear(); h->sub_bond_atom_off.clear(); h->sub_bond_start.clear(); h->sub_env.clear(); h->sub_env_start.clear();
@@ -315,26 +325,55 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
 }
 
 // ---- whole population from a template + the assignment bit matrix ---------------------------
-static void append_handle(igmk_handle* dst, igmk_handle* src)
+// Append the staged structures of `parts` (in this order) to dst: the destination vectors grow once, then
+// every part copies its slice on its own thread, rebasing its offsets.
+template <typename T>
+static size_t grow(std::vector<T>& v, size_t n) { const size_t at = v.size(); v.resize(at + n); return at; }
+
+static void append_parts(igmk_handle* dst, const std::vector<igmk_handle*>& parts)
 {
-    const int32_t A = (int32_t)dst->xyzr.size(), BP = (int32_t)dst->bond_ptr.size(), BT = (int32_t)dst->btype_f.size();
-    const int64_t BI = (int64_t)dst->bond_items.size(), SB = (int64_t)dst->sub_bonds.size(), SE = (int64_t)dst->sub_env.size();
-    for (auto d : src->desc) { d.atom_off += A; d.bond_ptr_off += BP; d.bond_item_off += BI; d.btype_off += BT; dst->desc.push_back(d); }
-    for (auto v : src->sub_bond_atom_off) dst->sub_bond_atom_off.push_back(v + A);
-    for (auto m : src->sub_env) { m.atom += A; dst->sub_env.push_back(m); }
-    for (auto v : src->sub_bond_start) dst->sub_bond_start.push_back(v + SB);
-    for (auto v : src->sub_env_start) dst->sub_env_start.push_back(v + SE);
-    dst->xyzr.insert(dst->xyzr.end(), src->xyzr.begin(), src->xyzr.end());
-    dst->xyzr0.insert(dst->xyzr0.end(), src->xyzr0.begin(), src->xyzr0.end());
-    dst->kind.insert(dst->kind.end(), src->kind.begin(), src->kind.end());
-    dst->envmask.insert(dst->envmask.end(), src->envmask.begin(), src->envmask.end());
-    dst->bond_ptr.insert(dst->bond_ptr.end(), src->bond_ptr.begin(), src->bond_ptr.end());
-    dst->bond_items.insert(dst->bond_items.end(), src->bond_items.begin(), src->bond_items.end());
-    dst->btype_f.insert(dst->btype_f.end(), src->btype_f.begin(), src->btype_f.end());
-    dst->btype_d.insert(dst->btype_d.end(), src->btype_d.begin(), src->btype_d.end());
-    dst->struct_id.insert(dst->struct_id.end(), src->struct_id.begin(), src->struct_id.end());
-    dst->sub_bonds.insert(dst->sub_bonds.end(), src->sub_bonds.begin(), src->sub_bonds.end());
-    dst->max_atoms = std::max(dst->max_atoms, src->max_atoms);
+    struct Base { size_t desc, atoms, bptr, bitems, btype, sbond, senv; };
+    std::vector<Base> base(parts.size());
+    Base tot = {0, 0, 0, 0, 0, 0, 0};
+    for (size_t t = 0; t < parts.size(); t++) {
+        const igmk_handle* p = parts[t];
+        base[t] = tot;
+        tot.desc += p->desc.size(); tot.atoms += p->xyzr.size(); tot.bptr += p->bond_ptr.size(); tot.bitems += p->bond_items.size();
+        tot.btype += p->btype_f.size(); tot.sbond += p->sub_bonds.size(); tot.senv += p->sub_env.size();
+        dst->max_atoms = std::max(dst->max_atoms, p->max_atoms);
+    }
+    const Base at = {grow(dst->desc, tot.desc), grow(dst->xyzr, tot.atoms), grow(dst->bond_ptr, tot.bptr), grow(dst->bond_items, tot.bitems),
+                     grow(dst->btype_f, tot.btype), grow(dst->sub_bonds, tot.sbond), grow(dst->sub_env, tot.senv)};
+    grow(dst->xyzr0, tot.atoms); grow(dst->kind, tot.atoms); grow(dst->envmask, tot.atoms); grow(dst->btype_d, tot.btype);
+    grow(dst->struct_id, tot.desc); grow(dst->sub_bond_start, tot.desc); grow(dst->sub_env_start, tot.desc);
+    grow(dst->sub_bond_atom_off, tot.sbond);
+    std::vector<std::thread> pool;
+    for (size_t t = 0; t < parts.size(); t++)
+        pool.emplace_back([&, t]() {
+            const igmk_handle* p = parts[t];
+            const Base o = {at.desc + base[t].desc, at.atoms + base[t].atoms, at.bptr + base[t].bptr, at.bitems + base[t].bitems,
+                            at.btype + base[t].btype, at.sbond + base[t].sbond, at.senv + base[t].senv};
+            for (size_t k = 0; k < p->desc.size(); k++) {
+                StructDesc d = p->desc[k];
+                d.atom_off += (int32_t)o.atoms; d.bond_ptr_off += (int32_t)o.bptr; d.bond_item_off += (int64_t)o.bitems; d.btype_off += (int32_t)o.btype;
+                dst->desc[o.desc + k] = d;
+                dst->struct_id[o.desc + k] = p->struct_id[k];
+                dst->sub_bond_start[o.desc + k] = p->sub_bond_start[k] + (int64_t)o.sbond;
+                dst->sub_env_start[o.desc + k] = p->sub_env_start[k] + (int64_t)o.senv;
+            }
+            std::copy(p->xyzr.begin(), p->xyzr.end(), dst->xyzr.begin() + o.atoms);
+            std::copy(p->xyzr0.begin(), p->xyzr0.end(), dst->xyzr0.begin() + o.atoms);
+            std::copy(p->kind.begin(), p->kind.end(), dst->kind.begin() + o.atoms);
+            std::copy(p->envmask.begin(), p->envmask.end(), dst->envmask.begin() + o.atoms);
+            std::copy(p->bond_ptr.begin(), p->bond_ptr.end(), dst->bond_ptr.begin() + o.bptr);
+            std::copy(p->bond_items.begin(), p->bond_items.end(), dst->bond_items.begin() + o.bitems);
+            std::copy(p->btype_f.begin(), p->btype_f.end(), dst->btype_f.begin() + o.btype);
+            std::copy(p->btype_d.begin(), p->btype_d.end(), dst->btype_d.begin() + o.btype);
+            std::copy(p->sub_bonds.begin(), p->sub_bonds.end(), dst->sub_bonds.begin() + o.sbond);
+            for (size_t k = 0; k < p->sub_bond_atom_off.size(); k++) dst->sub_bond_atom_off[o.sbond + k] = p->sub_bond_atom_off[k] + (int32_t)o.atoms;
+            for (size_t k = 0; k < p->sub_env.size(); k++) { EnvMember m = p->sub_env[k]; m.atom += (int32_t)o.atoms; dst->sub_env[o.senv + k] = m; }
+        });
+    for (auto& th : pool) th.join();
     dst->dirty = true; dst->viol_valid = false;
 }
 
@@ -348,23 +387,40 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
     if (n_struct < 0 || s_begin < 0 || s_begin + n_struct > n_struct_total) return fail("igmk_submit_population: bad structure range");
     if (n_rows > 0 && (!row || !col || !row_r0 || !bits)) return fail("igmk_submit_population: NULL row arguments");
     if (n_rows > 0 && bits_words * 32 < n_struct) return fail("igmk_submit_population: bit matrix narrower than the structure range");
-    for (int64_t r = 0; r < n_rows; r++)
-        if (row[r] < 0 || row[r] >= n_bead || col[r] < 0 || col[r] >= n_bead) return fail("igmk_submit_population: row bead index out of range");
     if (first_slot_out) *first_slot_out = (int32_t)h->desc.size();
     if (n_struct == 0) return 0;
-    // rows of every structure, in row order: one pass over the set bits (bit s of word s/32 = local structure s)
-    std::vector<std::vector<int32_t>> mine((size_t)n_struct);
-    for (int64_t r = 0; r < n_rows; r++) {
-        const uint32_t* w = bits + (size_t)r * bits_words;
-        for (int k = 0; k * 32 < n_struct; k++) {
-            uint32_t m = w[k];
-            while (m) {
-                const int b = __builtin_ctz(m); m &= m - 1;
-                const int sl = k * 32 + b;
-                if (sl < n_struct) mine[sl].push_back((int32_t)r);
-            }
-        }
+    const bool trace_sp = getenv("IGMK_TRACE") != nullptr;
+    auto tnow = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double tsp0 = tnow();
+    // Rows of every structure, in row order (bit s of word s/32 = local structure s).  The row range is cut into
+    // one slice per thread; each thread validates its rows and lists them per structure; the slices are then
+    // concatenated in slice order, which is row order.
+    const int nscan = (int)std::max<int64_t>(1, std::min<int64_t>(std::thread::hardware_concurrency(), n_rows / 65536 + 1));
+    std::vector<std::vector<std::vector<int32_t>>> found((size_t)nscan, std::vector<std::vector<int32_t>>((size_t)n_struct));
+    std::vector<int> bad((size_t)nscan, 0);
+    {
+        std::vector<std::thread> scan;
+        for (int t = 0; t < nscan; t++)
+            scan.emplace_back([&, t]() {
+                const int64_t r0 = n_rows * t / nscan, r1 = n_rows * (t + 1) / nscan;
+                auto& mine_t = found[t];
+                for (int64_t r = r0; r < r1; r++) {
+                    if (row[r] < 0 || row[r] >= n_bead || col[r] < 0 || col[r] >= n_bead) { bad[t] = 1; return; }
+                    const uint32_t* w = bits + (size_t)r * bits_words;
+                    for (int k = 0; k * 32 < n_struct; k++) {
+                        uint32_t m = w[k];
+                        while (m) {
+                            const int b = __builtin_ctz(m); m &= m - 1;
+                            const int sl = k * 32 + b;
+                            if (sl < n_struct) mine_t[sl].push_back((int32_t)r);
+                        }
+                    }
+                }
+            });
+        for (auto& th : scan) th.join();
     }
+    for (int t = 0; t < nscan; t++) if (bad[t]) return fail("igmk_submit_population: row bead index out of range");
+    const double tsp1 = tnow();
     const int nthr = (int)std::max(1u, std::min(std::thread::hardware_concurrency(), (unsigned)n_struct));
     std::vector<igmk_handle*> part((size_t)nthr, nullptr);
     std::vector<std::string> errs((size_t)nthr);
@@ -377,6 +433,15 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
             const int na = tmpl->n_atoms;
             std::vector<float> xyz((size_t)na * 3);
             std::vector<int32_t> bi, bj; std::vector<double> bk, br; std::vector<uint8_t> bs;
+            {                                             // this thread's share of the staging vectors, allocated once
+                size_t nb = 0;
+                for (int sl = lo; sl < hi; sl++) { nb += (size_t)tmpl->n_bonds; for (int q = 0; q < nscan; q++) nb += found[q][sl].size(); }
+                igmk_handle* ph = part[t];
+                const size_t nat = (size_t)(hi - lo) * na;
+                ph->xyzr.reserve(nat); ph->xyzr0.reserve(nat); ph->kind.reserve(nat); ph->envmask.reserve(nat);
+                ph->bond_ptr.reserve((size_t)(hi - lo) * (na + 1)); ph->bond_items.reserve(2 * nb);
+                ph->sub_bonds.reserve(nb); ph->sub_bond_atom_off.reserve(nb);
+            }
             for (int sl = lo; sl < hi; sl++) {
                 const int sg = s_begin + sl;
                 for (int a = 0; a < n_bead; a++) {
@@ -387,9 +452,10 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
                 bi.assign(tmpl->bond_i, tmpl->bond_i + tmpl->n_bonds); bj.assign(tmpl->bond_j, tmpl->bond_j + tmpl->n_bonds);
                 bk.assign(tmpl->bond_k, tmpl->bond_k + tmpl->n_bonds); br.assign(tmpl->bond_r0, tmpl->bond_r0 + tmpl->n_bonds);
                 bs.assign(tmpl->bond_style, tmpl->bond_style + tmpl->n_bonds);
-                for (int32_t r : mine[sl]) {           // HarmonicUpperBound((row, col), r0, k), inter_hic.py:55-62
-                    bi.push_back(row[r]); bj.push_back(col[r]); bk.push_back(row_k); br.push_back(row_r0[r]); bs.push_back(IGMK_BOND_UPPER);
-                }
+                for (int q = 0; q < nscan; q++)
+                    for (int32_t r : found[q][sl]) {   // HarmonicUpperBound((row, col), r0, k), inter_hic.py:55-62
+                        bi.push_back(row[r]); bj.push_back(col[r]); bk.push_back(row_k); br.push_back(row_r0[r]); bs.push_back(IGMK_BOND_UPPER);
+                    }
                 igmk_system_t sys = *tmpl;
                 sys.xyz = xyz.data();
                 sys.n_bonds = (int32_t)bi.size();
@@ -401,21 +467,14 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
         });
     }
     for (auto& th : pool) th.join();
+    const double tsp2 = tnow();
     int rc = 0;
     for (int t = 0; t < nthr; t++) if (!errs[t].empty() && !rc) rc = fail(errs[t]);
-    if (!rc) {
-        size_t a = 0, bp = 0, bi = 0, sb = 0, se = 0;            // grow the destination once
-        for (int t = 0; t < nthr; t++) {
-            a += part[t]->xyzr.size(); bp += part[t]->bond_ptr.size(); bi += part[t]->bond_items.size();
-            sb += part[t]->sub_bonds.size(); se += part[t]->sub_env.size();
-        }
-        h->xyzr.reserve(h->xyzr.size() + a); h->xyzr0.reserve(h->xyzr0.size() + a); h->kind.reserve(h->kind.size() + a);
-        h->envmask.reserve(h->envmask.size() + a); h->bond_ptr.reserve(h->bond_ptr.size() + bp);
-        h->bond_items.reserve(h->bond_items.size() + bi); h->sub_bonds.reserve(h->sub_bonds.size() + sb);
-        h->sub_bond_atom_off.reserve(h->sub_bond_atom_off.size() + sb); h->sub_env.reserve(h->sub_env.size() + se);
-        for (int t = 0; t < nthr; t++) append_handle(h, part[t]);
-    }
+    if (!rc) append_parts(h, part);
     for (int t = 0; t < nthr; t++) delete part[t];
+    if (trace_sp)
+        fprintf(stderr, "[igmk trace] submit_population of %d: bit scan %.1f ms, per-structure submits %.1f ms, merge %.1f ms\n",
+                n_struct, tsp1 - tsp0, tsp2 - tsp1, tnow() - tsp2);
     return rc;
 }
 
@@ -515,6 +574,7 @@ static void md2_build(igmk_handle* h)
 
 static int upload(igmk_handle* h)
 {
+    if (h->device < 0) return fail("igmk: this handle was created with IGMK_STAGING_ONLY and cannot touch a GPU");
     if (!h->dirty) return 0;
     h->free_device();
     const size_t na = h->xyzr.size(), ns = h->desc.size();
@@ -568,8 +628,30 @@ extern "C" int igmk_upload(igmk_handle_t* h)
 {
     if (!h) return fail("igmk_upload: NULL handle");
     if (h->desc.empty()) return fail("igmk_upload: nothing submitted");
+    if (h->device < 0) return upload(h);
     CU(cudaSetDevice(h->device));
     return upload(h);
+}
+
+extern "C" int igmk_layout_stats(igmk_handle_t* h, int32_t* slots_per_thread, int64_t* bond_items, int64_t* ell_items,
+                                 double* build_seconds)
+{
+    if (!h) return fail("igmk_layout_stats: NULL handle");
+    if (h->desc.empty()) return fail("igmk_layout_stats: nothing submitted");
+    int K = md2_pick_K(h->max_atoms);
+    if (K == 0) K = (h->max_atoms + MD2_T - 1) / MD2_T;           // global-memory path (md_big.cuh): same layout, more slots
+    const int keep_K = h->md2_K;
+    h->md2_K = K;
+    const auto t0 = std::chrono::steady_clock::now();
+    md2_build(h);
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    h->md2_K = keep_K;
+    h->dirty = true;                                              // the next upload rebuilds for its own K / path
+    if (slots_per_thread) *slots_per_thread = K;
+    if (bond_items) *bond_items = (int64_t)h->bond_items.size();
+    if (ell_items) *ell_items = (int64_t)h->md2_ell_items.size();
+    if (build_seconds) *build_seconds = dt;
+    return 0;
 }
 
 extern "C" int igmk_slot_sizes(igmk_handle_t* h, int32_t slot, int32_t* n_atoms, int64_t* n_bonds, int64_t* n_env_members)
@@ -588,6 +670,7 @@ extern "C" int igmk_violation_ratios(igmk_handle_t* h, int32_t slot, double* bon
 {
     if (!h) return fail("igmk_violation_ratios: NULL handle");
     if (slot < 0 || slot >= (int)h->desc.size()) return fail("igmk_violation_ratios: bad slot");
+    if (h->device < 0) return upload(h);
     CU(cudaSetDevice(h->device));
     if (!h->viol_valid) {
         if (int rc = upload(h)) return rc;
@@ -734,6 +817,7 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
     if (h->desc.empty()) return fail("igmk_run: nothing submitted");
     if (prot->n_stage < 0 || prot->n_stage > IGMK_MAX_STAGES) return fail("igmk_run: bad n_stage");
     if (!(prot->timestep > 0.0)) return fail("igmk_run: timestep must be > 0");
+    if (h->device < 0) return upload(h);
     CU(cudaSetDevice(h->device));
     const int ns = (int)h->desc.size();
     const size_t sm_cg = ctx_smem_bytes<double>(h->max_atoms, false);
@@ -789,6 +873,7 @@ static int single_point_impl(igmk_handle* h, double ev_scale, double env_scale, 
 {
     if (!h) return fail("igmk_single_point: NULL handle");
     if (h->desc.empty()) return fail("igmk_single_point: nothing submitted");
+    if (h->device < 0) return upload(h);
     CU(cudaSetDevice(h->device));
     const size_t sm = ctx_smem_bytes<T>(h->max_atoms, false);
     CU(cudaFuncSetAttribute(k_single_point<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));

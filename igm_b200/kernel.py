@@ -45,6 +45,9 @@ def kernel_opts(cfg):
     return opts
 
 
+STAGING_ONLY = -1       # MStepBatch(STAGING_ONLY): host staging without a GPU (submit*, slot_sizes, layout_stats); no compute
+
+
 class MStepBatch(object):
     """Thin owner of one ``igmk_handle_t`` (one device)."""
 
@@ -123,6 +126,12 @@ class MStepBatch(object):
     def single_point(self, ev_scale=1.0, env_scale=1.0, bond_prefactor=1.0, f32=False):
         fn = self._lib.igmk_single_point_f32 if f32 else self._lib.igmk_single_point
         _abi.check(fn(self._h, float(ev_scale), float(env_scale), float(bond_prefactor)), "igmk_single_point")
+
+    def layout_stats(self):
+        """-> (slots per thread K, bond items, items after sliced-ELL padding, host seconds of the layout build)"""
+        k, b, e, t = C.c_int32(0), C.c_int64(0), C.c_int64(0), C.c_double(0.0)
+        _abi.check(self._lib.igmk_layout_stats(self._h, C.byref(k), C.byref(b), C.byref(e), C.byref(t)), "igmk_layout_stats")
+        return k.value, b.value, e.value, t.value
 
     def slot_sizes(self, slot):
         """-> (n_atoms, n_bonds, n_envelope_members) of a submitted structure"""

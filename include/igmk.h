@@ -121,6 +121,10 @@ int  igmk_version(void);
 int  igmk_device_count(void);
 
 /* ---- M-step: per-structure submit / run / fetch -------------------------------- */
+/* device: a CUDA ordinal, or IGMK_STAGING_ONLY for a handle that only stages on the host (submit, submit_population,
+ * slot_sizes, layout_stats -- what pack + create_lammps_data do before any LAMMPS process exists, lammps.py:429-431);
+ * every call that needs the GPU fails on such a handle.  There is no CPU compute path. */
+#define IGMK_STAGING_ONLY (-1)
 int igmk_create(int device, igmk_handle_t** out);
 int igmk_destroy(igmk_handle_t* h);
 int igmk_clear(igmk_handle_t* h);
@@ -142,6 +146,10 @@ int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t 
                            int64_t n_rows, const int32_t* row, const int32_t* col, const double* row_r0,
                            double row_k, const uint32_t* bits, int32_t bits_words, const int64_t* seeds,
                            int32_t* first_slot_out);
+/* builds the MD kernel's host-side layout (atom order + sliced-ELL bond blocks) for what is submitted and reports
+ * it: slots per thread, bond items (both ends), items after padding, seconds the build took (any pointer may be NULL) */
+int igmk_layout_stats(igmk_handle_t* h, int32_t* slots_per_thread, int64_t* bond_items, int64_t* ell_items,
+                      double* build_seconds);
 /* sizes of a submitted structure (any pointer may be NULL) */
 int igmk_slot_sizes(igmk_handle_t* h, int32_t slot, int32_t* n_atoms, int64_t* n_bonds, int64_t* n_env_members);
 /* host -> device copy of everything submitted (what writing + re-reading the .data
