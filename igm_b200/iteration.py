@@ -84,3 +84,41 @@ def relax_init(crd_local, template, optimizer_options, device=0, seeds=None, bon
             raise RuntimeError("b200 kernel produced non-finite coordinates or energy (structure %d of rank %d)" % (k, rank))
         infos.append(info_from_result(res))
     return new, infos
+
+
+def hic_iteration_files(hss_in, hcs_path, hss_out, actdist_out, optimizer_options, intra_sigma, inter_sigma,
+                        last_actdist=None, contact_range=2.0, nucleus_radius=None, semiaxes=None, evfactor=1.0,
+                        k_hic=1.0, k_poly=1.0, k_env=1.0, device=0, seeds=None, tol=0.05, bond_prefactor=1.0):
+    """One Hi-C A/M iteration file to file, single process: population .hss + contact matrix .hcs (+ the actdist
+    file of the previous iteration) in; actdist.hdf5 and the new population .hss out -- what
+    ``ActivationDistanceStep`` (setup :106-189, task :192-222, reduce :226-290) followed by ``ModelingStep``
+    (task :151-391, set_structure :429-501, teardown_poller :503-527) leave on disk, with the restraint set of
+    ``ModelingStep.task`` for a Hi-C run: Steric, Envelope (sphere of `nucleus_radius`, default the file's
+    ``envelope/params``; or ellipsoid `semiaxes`), Polymer, inter/intra Hi-C.
+    -> the dict of ``hic_iteration`` plus ``summary`` (n_imposed, n_violations over the harmonic restraints)."""
+    import json
+    from . import files, synth
+    pop = files.read_hss(hss_in)
+    hcs = files.read_hcs(hcs_path)
+    idx = pop["index"]
+    if hcs["n"] != idx.n_hap:
+        raise ValueError("%s has %d haploid bins, the population's index %d" % (hcs_path, hcs["n"], idx.n_hap))
+    last = files.read_actdist(last_actdist) if last_actdist else None
+    pairs = files.hic_pairs_from_matrix(hcs, intra_sigma, inter_sigma, last)
+    if nucleus_radius is None and semiaxes is None:
+        nucleus_radius = float(np.asarray(pop["tree"]["envelope"]["params"]).ravel()[0])
+    rad = pop["radii"]
+    template = synth.pack_structure(np.zeros((idx.n_bead, 3), dtype=np.float32), rad, idx, nucleus_radius=nucleus_radius or 0.0,
+                                    semiaxes=semiaxes, contact_range=contact_range, evfactor=evfactor, k_poly=k_poly, k_env=k_env,
+                                    seed=0, struct_id=0)
+    out = hic_iteration(pop["coordinates"], idx, rad, template, pairs, optimizer_options, device=device,
+                        contact_range=contact_range, k_hic=k_hic, seeds=seeds, bond_prefactor=bond_prefactor,
+                        violations=True, tol=tol)
+    files.write_actdist(actdist_out, *out["rows"])
+    n_imp = int(sum(v[0] for v in out["violations"]))
+    n_vio = int(sum(v[1] for v in out["violations"]))
+    summary = {"n_imposed": n_imp, "n_violations": n_vio}                    # harmonic restraints only (envelope: M10, violation_ratios)
+    files.write_hss(hss_out, pop["tree"], coordinates=out["coordinates"], summary=json.dumps(summary),
+                    violation=(n_vio / n_imp) if n_imp else 0.0)            # ModelingStep.py:509-519
+    out["summary"] = summary
+    return out

@@ -91,3 +91,61 @@ def test_relax_init_removes_overlaps_and_keeps_the_polymer():
     # polymer bonds of the template hold: consecutive beads of a chain no further apart than r0 (+5 %)
     d = np.linalg.norm(new[template.bond_i] - new[template.bond_j], axis=2)
     assert (d <= template.bond_r0[:, None] * 1.05).all()
+
+
+def test_file_to_file_iteration(tmp_path):
+    """population .hss + matrix .hcs -> actdist.hdf5 + new .hss (ActivationDistanceStep + ModelingStep on disk):
+    the actdist file holds exactly the oracle's rows, a second iteration picks up its probabilities as plast,
+    the population file carries the new coordinates, nstruct/nbead and the violation summary."""
+    import json
+    from igm_b200 import files, h5lite
+    from igm_b200.iteration import hic_iteration_files
+    g = synth.Genome([16, 12, 9, 6], n_autosomes=3)
+    R = 1500.0
+    rad = synth.bead_radii(len(g), R, 0.3)
+    S = 12
+    crd = synth.population_territories(g, S, R=R, seed=41)
+    pi, pj, pw = synth.hic_pairs(g, 0.004, seed=6)
+    # the matrix as a .hcs: CSR of the upper triangle over haploid bins (pairs arrive in row-major order)
+    indptr = np.zeros(g.n_hap + 1, dtype=np.int32)
+    np.add.at(indptr, pi + 1, 1)
+    hcs_tree = {"matrix": {"data": pw.astype(np.float32), "indices": pj.astype(np.int32), "indptr": np.cumsum(indptr).astype(np.int32),
+                           "diagonal": np.zeros(g.n_hap, dtype=np.float32)},
+                "index": {"chrom": g.chrom[:g.n_hap], "copy": np.zeros(g.n_hap, dtype=np.int32),
+                          "copy_index": json.dumps({str(h): [h] for h in range(g.n_hap)})}}
+    hss_tree = {"coordinates": crd, "radii": rad, "summary": "{}",
+                "index": {"chrom": g.chrom, "copy": g.copy, "copy_index": json.dumps({str(h): [int(b) for b in v] for h, v in g.copy_index.items()})},
+                "envelope": {"shape": "sphere", "params": np.int64(R)},
+                h5lite.ATTRS: {"nbead": np.int64(len(g)), "nstruct": np.int64(S), "violation": np.float64(0), "version": np.int32(2)}}
+    hss_in, hcs, hss_out, ad1, ad2 = (str(tmp_path / n) for n in ("in.hss", "m.hcs", "out.hss", "actdist1.hdf5", "actdist2.hdf5"))
+    h5lite.write(hcs, hcs_tree)
+    h5lite.write(hss_in, hss_tree)
+    opts = synth.demo_protocol_options()
+    opts["custom_annealing_protocol"]["mdsteps"] = [200, 300, 300, 200]
+    opts["custom_annealing_protocol"]["relax"]["mdsteps"] = 30
+    sigma = float(np.sort(pw)[pw.size // 2])
+    out = hic_iteration_files(hss_in, hcs, hss_out, ad1, opts, sigma, sigma, seeds=np.arange(S, dtype=np.int64) + 1)
+    keep = pw.astype(np.float32) >= np.float32(sigma)
+    want = ao.actdist_rows(pi[keep], pj[keep], pw[keep].astype(np.float32).astype(np.float64), np.zeros(int(keep.sum())),
+                           crd, rad, g.chrom, g.copy_index, 2.0)
+    got = files.read_actdist(ad1)
+    assert all(np.array_equal(a.view(np.uint32), b.view(np.uint32)) for a, b in zip(got, want)) and got[0].size > 20
+    new = files.read_hss(hss_out)
+    assert new["nstruct"] == S and new["nbead"] == len(g) and np.array_equal(new["coordinates"], out["coordinates"])
+    assert np.isfinite(new["coordinates"]).all() and not np.array_equal(new["coordinates"], crd)
+    summary = json.loads(new["tree"]["summary"])
+    mask = ao.assign(crd, *got[:3])
+    n_poly = synth.polymer_bonds(g, rad)[0].size
+    assert summary["n_imposed"] == S * n_poly + int(mask.sum())
+    assert new["tree"][h5lite.ATTRS]["violation"] == summary["n_violations"] / summary["n_imposed"]
+    # second iteration at a lower sigma: plast comes from the first actdist file (rows between first copies)
+    sigma2 = float(np.sort(pw)[pw.size // 4])
+    hic_iteration_files(hss_out, hcs, str(tmp_path / "out2.hss"), ad2, opts, sigma2, sigma2, last_actdist=ad1,
+                        seeds=np.arange(S, dtype=np.int64) + 1)
+    keep2 = pw.astype(np.float32) >= np.float32(sigma2)
+    pl = files.hic_pairs_from_matrix(files.read_hcs(hcs), sigma2, sigma2, got)[3]
+    assert pl.size == int(keep2.sum()) and np.count_nonzero(pl) > 5
+    want2 = ao.actdist_rows(pi[keep2], pj[keep2], pw[keep2].astype(np.float32).astype(np.float64), pl,
+                            new["coordinates"], rad, g.chrom, g.copy_index, 2.0)
+    got2 = files.read_actdist(ad2)
+    assert all(np.array_equal(a.view(np.uint32), b.view(np.uint32)) for a, b in zip(got2, want2))
