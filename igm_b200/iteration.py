@@ -88,14 +88,16 @@ def relax_init(crd_local, template, optimizer_options, device=0, seeds=None, bon
 
 def hic_iteration_files(hss_in, hcs_path, hss_out, actdist_out, optimizer_options, intra_sigma, inter_sigma,
                         last_actdist=None, contact_range=2.0, nucleus_radius=None, semiaxes=None, evfactor=1.0,
-                        k_hic=1.0, k_poly=1.0, k_env=1.0, device=0, seeds=None, tol=0.05, bond_prefactor=1.0):
+                        k_hic=1.0, k_poly=1.0, k_env=1.0, device=0, seeds=None, tol=0.05, bond_prefactor=1.0,
+                        plast_override=None):
     """One Hi-C A/M iteration file to file, single process: population .hss + contact matrix .hcs (+ the actdist
     file of the previous iteration) in; actdist.hdf5 and the new population .hss out -- what
     ``ActivationDistanceStep`` (setup :106-189, task :192-222, reduce :226-290) followed by ``ModelingStep``
     (task :151-391, set_structure :429-501, teardown_poller :503-527) leave on disk, with the restraint set of
     ``ModelingStep.task`` for a Hi-C run: Steric, Envelope (sphere of `nucleus_radius`, default the file's
     ``envelope/params``; or ellipsoid `semiaxes`), Polymer, inter/intra Hi-C.
-    -> the dict of ``hic_iteration`` plus ``summary`` (n_imposed, n_violations over the harmonic restraints)."""
+    -> the dict of ``hic_iteration`` plus ``summary`` (n_imposed, n_violations over envelope, polymer and Hi-C
+    restraints, as ModelingStep counts them, :449-470)."""
     import json
     from . import files, synth
     pop = files.read_hss(hss_in)
@@ -105,6 +107,8 @@ def hic_iteration_files(hss_in, hcs_path, hss_out, actdist_out, optimizer_option
         raise ValueError("%s has %d haploid bins, the population's index %d" % (hcs_path, hcs["n"], idx.n_hap))
     last = files.read_actdist(last_actdist) if last_actdist else None
     pairs = files.hic_pairs_from_matrix(hcs, intra_sigma, inter_sigma, last)
+    if plast_override is not None:         # diagnostics (tools/run_demo.py --no-correction): the same plast for every pair
+        pairs = pairs[:3] + (np.full(pairs[0].size, float(plast_override)),)
     if nucleus_radius is None and semiaxes is None:
         nucleus_radius = float(np.asarray(pop["tree"]["envelope"]["params"]).ravel()[0])
     rad = pop["radii"]
@@ -115,9 +119,14 @@ def hic_iteration_files(hss_in, hcs_path, hss_out, actdist_out, optimizer_option
                         contact_range=contact_range, k_hic=k_hic, seeds=seeds, bond_prefactor=bond_prefactor,
                         violations=True, tol=tol)
     files.write_actdist(actdist_out, *out["rows"])
-    n_imp = int(sum(v[0] for v in out["violations"]))
-    n_vio = int(sum(v[1] for v in out["violations"]))
-    summary = {"n_imposed": n_imp, "n_violations": n_vio}                    # harmonic restraints only (envelope: M10, violation_ratios)
+    v = np.array(out["violations"], dtype=np.int64).reshape(-1, 4)
+    n_poly = int(template.bond_i.size)
+    hic_imp = int(v[:, 0].sum()) - n_poly * v.shape[0]
+    summary = {"n_imposed": int(v[:, 0].sum() + v[:, 2].sum()), "n_violations": int(v[:, 1].sum() + v[:, 3].sum()),
+               "byrestraint": {"Envelope": {"n_imposed": int(v[:, 2].sum()), "n_violations": int(v[:, 3].sum())},
+                               "Polymer+HiC": {"n_imposed": int(v[:, 0].sum()), "n_violations": int(v[:, 1].sum()),
+                                               "n_imposed_polymer": n_poly * v.shape[0], "n_imposed_hic": hic_imp}}}
+    n_imp, n_vio = summary["n_imposed"], summary["n_violations"]
     files.write_hss(hss_out, pop["tree"], coordinates=out["coordinates"], summary=json.dumps(summary),
                     violation=(n_vio / n_imp) if n_imp else 0.0)            # ModelingStep.py:509-519
     out["summary"] = summary

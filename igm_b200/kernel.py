@@ -224,7 +224,8 @@ def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protoco
     the host-side assembly, the copies in and the copies out disappear behind the MD kernel.
 
     -> (coordinates float32 [n_bead][S][3], [Result] * S, violations or None, timings dict);
-    violations = per-structure (n_imposed, n_violated) of the harmonic restraints at ``violations_tol``."""
+    violations = per-structure (n_imposed, n_violated) of the harmonic restraints and (n_imposed, n_violated) of the
+    envelope restraints (one per member, scale = 0.1 * mean semi-axis, envelope.py:51) at ``violations_tol``."""
     import threading
     crd = np.ascontiguousarray(crd, dtype=np.float32)
     S = crd.shape[1]
@@ -269,8 +270,15 @@ def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protoco
         if viol is not None:
             for batch, lo, hi in batches:
                 for k in range(hi - lo):
-                    br, _ = batch.violation_ratios(k)
-                    viol[lo + k] = (br.size, int(np.count_nonzero(br > violations_tol)))
+                    br, eu = batch.violation_ratios(k)
+                    n_env = n_env_vio = 0
+                    for e in range(template.env_abck.shape[0]):      # Envelope restraints: EllipticEnvelope per member
+                        a, b, c, ke = (float(v) for v in template.env_abck[e])
+                        u = eu[template.env_off[e]:template.env_off[e + 1]]
+                        n_env += u.size
+                        if ke != 0.0:
+                            n_env_vio += int(np.count_nonzero(envelope_ratios(u, ke, 0.1 * (a + b + c) / 3.0) > violations_tol))   # envelope.py:51
+                    viol[lo + k] = (br.size, int(np.count_nonzero(br > violations_tol)), n_env, n_env_vio)
     finally:
         for w in workers:
             w.join()

@@ -136,7 +136,8 @@ def test_file_to_file_iteration(tmp_path):
     summary = json.loads(new["tree"]["summary"])
     mask = ao.assign(crd, *got[:3])
     n_poly = synth.polymer_bonds(g, rad)[0].size
-    assert summary["n_imposed"] == S * n_poly + int(mask.sum())
+    assert summary["n_imposed"] == S * n_poly + int(mask.sum()) + S * len(g)         # polymer + Hi-C + one envelope term per bead
+    assert summary["byrestraint"]["Polymer+HiC"]["n_imposed_hic"] == int(mask.sum())
     assert new["tree"][h5lite.ATTRS]["violation"] == summary["n_violations"] / summary["n_imposed"]
     # second iteration at a lower sigma: plast comes from the first actdist file (rows between first copies)
     sigma2 = float(np.sort(pw)[pw.size // 4])

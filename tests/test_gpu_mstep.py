@@ -265,7 +265,7 @@ def test_run_population_pipeline_equals_one_batch():
             assert np.array_equal(xa[:len(g)].view(np.uint32), new[:, s, :].view(np.uint32))
             assert ra.final_energy == results[s].final_energy and results[s].status == 0
             br, _ = a.violation_ratios(s)
-            assert viol[s] == (br.size, int(np.count_nonzero(br > 0.05)))
+            assert viol[s][:2] == (br.size, int(np.count_nonzero(br > 0.05))) and viol[s][2] == len(g) and viol[s][3] <= 2
         slab = np.zeros((len(g), S + 5, 3), dtype=np.float32)              # bulk fetch into a wider slab at an offset
         res = a.fetch_population(slab, s_begin=5)
         assert np.array_equal(slab[:, 5:, :].view(np.uint32), new.view(np.uint32)) and not slab[:, :5, :].any()
