@@ -98,3 +98,22 @@ def test_plast_lookup_sums_duplicates_and_ignores_second_copies():
     assert pi.tolist() == [0, 1] and pj.tolist() == [1, 2] and pw.tolist() == [0.5, float(np.float32(0.3))]
     assert pl.tolist() == [0.375, 0.0625]            # (0,1) twice among first copies: summed (coo -> lil); (4,5) ignored
     assert files.hic_pairs_from_matrix(hcs, False, 0.01)[0].tolist() == [0, 1]          # inter only: (0,3) and (1,2)
+
+
+@needs_demo
+def test_recorded_demo_output_counts_are_the_uncorrected_probability():
+    """the Hi-C restraint counts in the reference's recorded demo output (sigma 0.02) equal, to 1.5 %,
+    the sum over the kept pairs of round(pwish n S) + 1 -- what p = pwish imposes -- per class."""
+    pop = files.read_hss(os.path.join(DEMO, "demo_sample_outputs", "igm-model.hss.T"))
+    cfg = json.loads(pop["tree"]["config_data"])
+    assert cfg["runtime"]["Hi-C"]["intra_sigma"] == 0.02 and cfg["runtime"]["Hi-C"]["inter_sigma"] == 0.02
+    rec = {k.split("[")[0]: v["n_imposed"] for k, v in json.loads(pop["tree"]["summary"])["byrestraint"].items()}
+    hcs = files.read_hcs(os.path.join(DEMO, "WTC11_HiC_2Mb.hcs"))
+    pi, pj, pw, _ = files.hic_pairs_from_matrix(hcs, 0.02, 0.02)
+    nc = np.diff(pop["index"].copy_off)
+    same = hcs["index"].chrom[pi] == hcs["index"].chrom[pj]
+    ncomb = np.where(same, np.minimum(nc[pi], nc[pj]), nc[pi] * nc[pj])
+    S = pop["nstruct"]
+    o = np.minimum(ncomb * S - 1, np.rint(ncomb * pw * S)) + 1
+    assert abs(o[same].sum() / rec["intraHiC"] - 1) < 0.015 and abs(o[~same].sum() / rec["interHiC"] - 1) < 0.02
+    assert rec["Envelope"] == pop["nbead"] * S and rec["Polymer"] == 2962 * S
