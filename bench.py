@@ -27,6 +27,7 @@ sys.path.insert(0, ROOT)
 from igm_b200 import _abi, synth, parallel          # noqa: E402
 
 NUCLEUS_R = 5500.0
+REF_HIC_BONDS = 27588          # Hi-C bonds per structure of the GPU arm's default workload (its config.hic_bonds_per_structure)
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # non-tensor FP32 FMA peak at max clock (derived)
 
 
@@ -254,10 +255,20 @@ def run_reference(args, rank, world):
     opts, prot = protocol(args.md_scale)
     cores = os.cpu_count() or 1
     n_sample = args.cpu_sample or cores
+    # The GPU arm derives its Hi-C restraints from a relaxed population with its own kernels; this arm may not touch
+    # them, so every structure gets the same NUMBER of Hi-C upper bounds (what the GPU arm reports as
+    # hic_bonds_per_structure at its default size) between bead pairs that are within contact range in the starting
+    # territories -- like assigned contacts, satisfied when imposed.  Same beads, envelope, polymer, protocol.
+    from scipy.spatial import cKDTree
     systems = []
     for s in range(n_sample):
-        xyz = synth.territories(g, NUCLEUS_R, np.random.default_rng(1234 + s))
-        systems.append(synth.pack_structure(xyz, rad, g, nucleus_radius=NUCLEUS_R, seed=1 + s, struct_id=s))
+        rng = np.random.default_rng(1234 + s)
+        xyz = synth.territories(g, NUCLEUS_R, rng)
+        near = cKDTree(xyz.astype(np.float64)).query_pairs(2.0 * 2.0 * float(rad[0]) * 0.95, output_type="ndarray")
+        pick = near[rng.choice(near.shape[0], min(REF_HIC_BONDS, near.shape[0]), replace=False)]
+        r0 = 2.0 * (rad[pick[:, 0]] + rad[pick[:, 1]]).astype(np.float64)
+        systems.append(synth.pack_structure(xyz, rad, g, pick[:, 0], pick[:, 1], r0, nucleus_radius=NUCLEUS_R, seed=1 + s, struct_id=s))
+    n_hic = int(np.mean([ps.bond_i.size for ps in systems])) - int(synth.polymer_bonds(g, rad)[0].size)
     times = []
     for it in range(args.warmup + args.steps):
         v, dt, _ = cpu_mstep_baseline(systems, prot, n_sample, cores)
@@ -265,13 +276,17 @@ def run_reference(args, rank, world):
             times.append(dt)
     ms = 1e3 * float(np.mean(times))
     value = n_sample / (ms / 1e3)
-    sample = "%d structures per step (one per host thread), polymer+steric+envelope restraints, full protocol" % n_sample
+    sample = ("%d structures per step (one per host thread), steric + envelope + polymer + %d Hi-C upper bounds per structure, "
+              "full protocol" % (n_sample, n_hic))
     print(json.dumps({
         "impl": "reference", "metric": "optimised structures/sec at 2Mb diploid", "value": value, "unit": "structures/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "2Mb diploid (3008 beads), CPU restatement of the lammpgen script (oracle/ff_oracle.c); "
-                               "lmp_serial itself is not installable offline", "structures_per_step": n_sample},
+        "config": {"workload": "configs[1]: 2 Mb diploid Hi-C (3008 beads, spherical envelope, full demo annealing protocol + CG, "
+                               "%d Hi-C bonds per structure between beads in contact range of the starting territories); CPU "
+                               "restatement of the lammpgen script (oracle/ff_oracle.c) -- lmp_serial itself is not installable "
+                               "offline" % n_hic, "beads": 3008, "structures_per_step": n_sample, "hic_bonds_per_structure": n_hic,
+                   "md_scale": args.md_scale},
         "cpu_baseline": {"value": value, "unit": "structures/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "structures/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
