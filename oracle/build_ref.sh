@@ -2,7 +2,7 @@
 # Compiles the reference's OWN native SPRITE A-step code (Cython + C++,
 # igm/cython_compiled/{sprite.pyx,cpp_sprite_assignment.cpp,.h}) from the sources
 # where they lie under /root/reference into oracle/_ref/ (git-ignored; travels to
-# the GPU box with the snapshot).  Nothing is copied into the repo: the generated
+# the GPU box with the snapshot), and copies the demo's data files next to it.  No source is copied into the repo: the generated
 # .cpp and the objects live in a temp dir.  No-op when the reference tree is absent.
 set -e
 REF=${IGM_REFERENCE_ROOT:-/root/reference}/igm/cython_compiled
@@ -10,6 +10,15 @@ HERE=$(cd "$(dirname "$0")" && pwd)
 [ -f "$REF/sprite.pyx" ] || { echo "reference tree not present: skipping oracle/_ref"; exit 0; }
 OUT="$HERE/_ref"
 mkdir -p "$OUT"
+# The reference's demo inputs and its recorded demo output (data, not sources): tests/test_gpu_demo.py runs the demo on
+# the GPU box against them, tools/run_demo.py takes them as arguments.
+DEMO=${IGM_REFERENCE_ROOT:-/root/reference}/demo
+if [ -f "$DEMO/WTC11_HiC_2Mb.hcs" ]; then
+    mkdir -p "$OUT/demo"
+    for f in "$DEMO/WTC11_HiC_2Mb.hcs" "$DEMO/demo_sample_outputs/igm-model.hss.randomInit" "$DEMO/demo_sample_outputs/igm-model.hss.T"; do
+        [ -f "$OUT/demo/$(basename "$f")" ] || cp "$f" "$OUT/demo/"
+    done
+fi
 TMP=$(mktemp -d)
 PY=${PYTHON:-python}
 EXT=$($PY -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")
