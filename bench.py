@@ -27,8 +27,9 @@ sys.path.insert(0, ROOT)
 from igm_b200 import _abi, synth, parallel          # noqa: E402
 
 NUCLEUS_R = 5500.0
-REF_HIC_BONDS = 27588          # Hi-C bonds per structure of the GPU arm's default workload (its config.hic_bonds_per_structure)
-FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # non-tensor FP32 FMA peak at max clock (derived)
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # non-tensor FP32 FMA peak at max clock (derived; fallback when the probe fails)
+FIXTURE = os.path.join(ROOT, "tests", "golden", "bench_c2_structures.npz")
+N_FIXTURE = 32                 # structures of the default workload kept as a fixture: the reference arm's sample
 
 
 def parse_args():
@@ -44,7 +45,44 @@ def parse_args():
     ap.add_argument("--relax-md-scale", type=float, default=None, help="mdsteps scale of the untimed RelaxInit pass (profiling aid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", type=int, default=0, help="structures in the CPU baseline sample (0: one per core)")
+    ap.add_argument("--write-fixture", default=None,
+                    help="write the first %d structures of the workload (M-step inputs: coordinates + assigned Hi-C bonds) to this "
+                         ".npz; commit it as tests/golden/bench_c2_structures.npz" % N_FIXTURE)
+    ap.add_argument("--no-plugin", action="store_true", help="skip the e2e_plugin leg (B200Controller + optimize(model, cfg))")
     return ap.parse_args()
+
+
+def workload_config(args, evals):
+    """The `config` object of the JSON line.  Both arms print exactly this (the driver compares them): it holds only what
+    DEFINES the workload; what a run measures about it (sigma, bonds per structure, ...) goes to `workload_stats`."""
+    return {"workload": "configs[1]: 2 Mb diploid Hi-C, %d structures per GPU, spherical envelope (R = 5500), full demo annealing "
+                        "protocol + CG; Hi-C matrix = contact frequencies of the relaxed synthetic population of rank 0, "
+                        "thresholded to keep %d haploid pairs (the demo matrix keeps 614140 at its last sigma, 0.01)"
+                        % (args.structures, args.pairs),
+            "beads": 3008, "structures_per_gpu": args.structures, "hic_pairs": args.pairs, "md_force_evals": evals,
+            "md_scale": args.md_scale,
+            "fixture": "tests/golden/bench_c2_structures.npz = M-step inputs (relaxed coordinates + assigned Hi-C bonds) of "
+                       "structures 0..%d of this workload; the reference arm and cpu_baseline run those" % (N_FIXTURE - 1),
+            "l2_policy": "working set per step (bond lists + neighbour tables, >400 MB) exceeds L2; the A-step slab is L2 "
+                         "resident at 1000 structures (36 MB): roofline_astep says so"}
+
+
+def load_fixture():
+    if not os.path.isfile(FIXTURE):
+        return None
+    z = np.load(FIXTURE)
+    return {k: z[k] for k in z.files}
+
+
+def fixture_systems(fx, g, rad, n):
+    """PackedSystems of the first n fixture structures, assembled like the GPU arm's (same seeds, same bond order)."""
+    out = []
+    for s in range(min(n, fx["crd"].shape[1])):
+        lo, hi = int(fx["bond_off"][s]), int(fx["bond_off"][s + 1])
+        bi, bj = fx["bond_i"][lo:hi].astype(np.int32), fx["bond_j"][lo:hi].astype(np.int32)
+        r0 = (2.0 * (rad[bi] + rad[bj])).astype(np.float64)
+        out.append(synth.pack_structure(fx["crd"][:, s, :], rad, g, bi, bj, r0, nucleus_radius=NUCLEUS_R, seed=7 + s, struct_id=s))
+    return out
 
 
 # --------------------------------------------------------------------------------------
@@ -159,14 +197,19 @@ def build_workload(args, rank, world, device, log):
     slab = parallel.all_gather_slab(local)            # NCCL all-gather on the structure axis
     S_tot = S * world
     astep = {}
+    # Synthetic Hi-C matrix that is geometrically consistent with the population (a random matrix
+    # collapses the genome into a globule): the contact frequency of every haploid pair in the relaxed
+    # structures of RANK 0 is the "experiment" (the same matrix, sigma and pair list whatever the number of
+    # GPUs, so the restraint load per structure does not drift with N); the iteration wishes 10 % more
+    # contacts than are present (pwish = 1.1 f) and the previous iteration is taken to have imposed f (plast).
+    iu, ju = np.triu_indices(g.n_hap, 1)
+    rank0 = slab[:, :S, :].contiguous()
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop0:
+        pop0.attach(rank0)
+        freq = pop0.contact_freq(iu.astype(np.int32), ju.astype(np.int32), 2.0)
+    del rank0
     with Population(S_tot, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop:
         pop.attach(slab)
-        # Synthetic Hi-C matrix that is geometrically consistent with the population (a random matrix
-        # collapses the genome into a globule): the contact frequency of every haploid pair in the relaxed
-        # population is the "experiment"; the iteration wishes 10 % more contacts than are present
-        # (pwish = 1.1 f) and the previous iteration is taken to have imposed f (plast).
-        iu, ju = np.triu_indices(g.n_hap, 1)
-        freq = pop.contact_freq(iu.astype(np.int32), ju.astype(np.int32), 2.0)
         pw_all = np.minimum(np.float32(1.0), np.float32(1.1) * freq).astype(np.float32)
         sigma = float(np.partition(pw_all, pw_all.size - args.pairs)[pw_all.size - args.pairs]) if args.pairs < pw_all.size else 0.0
         keep = pw_all >= np.float32(sigma)
@@ -208,12 +251,41 @@ def build_workload(args, rank, world, device, log):
     # done for the whole population by igmk_submit_population; a few structures are also packed here in
     # Python for the CPU baseline and the flop count
     r0_all = (2.0 * (rad[row] + rad[col])).astype(np.float64)
-    n_py = min(S, max(os.cpu_count() or 1, 16))
-    systems = []
+    n_py = min(S, max(os.cpu_count() or 1, N_FIXTURE))
+    systems, masks = [], []
     for s in range(n_py):
         m = ((bits[:, s >> 5] >> np.uint32(s & 31)) & np.uint32(1)).astype(bool)
+        masks.append(m)
         systems.append(synth.pack_structure(crd[:, s, :], rad, g, row[m], col[m], r0_all[m], nucleus_radius=NUCLEUS_R,
                                             seed=7 + rank * S + s, struct_id=rank * S + s))
+    # ---- the fixture the reference arm runs: M-step inputs of this rank-0 workload's first structures ----
+    fixture_check = None
+    if rank == 0:
+        nf = min(N_FIXTURE, n_py)
+        if args.write_fixture:
+            off = np.concatenate([[0], np.cumsum([int(m.sum()) for m in masks[:nf]])]).astype(np.int64)
+            np.savez_compressed(args.write_fixture, crd=crd[:, :nf, :].copy(), bond_off=off,
+                                bond_i=np.concatenate([row[m] for m in masks[:nf]]).astype(np.uint16),
+                                bond_j=np.concatenate([col[m] for m in masks[:nf]]).astype(np.uint16),
+                                structures=np.int64(S), pairs=np.int64(args.pairs), sigma=np.float64(sigma))
+            log("fixture written: %s (%d structures)" % (args.write_fixture, nf))
+        fx = load_fixture()
+        if fx is None:
+            fixture_check = {"present": False}
+        else:
+            nf = min(nf, fx["crd"].shape[1])
+            same_crd = int(sum(np.array_equal(fx["crd"][:, s, :], crd[:, s, :]) for s in range(nf)))
+            same_bonds, fx_counts = 0, []
+            for s in range(nf):
+                lo, hi = int(fx["bond_off"][s]), int(fx["bond_off"][s + 1])
+                fx_counts.append(hi - lo)
+                same_bonds += int(np.array_equal(fx["bond_i"][lo:hi], row[masks[s]].astype(np.uint16)) and
+                                  np.array_equal(fx["bond_j"][lo:hi], col[masks[s]].astype(np.uint16)))
+            mine = [int(m.sum()) for m in masks[:nf]]
+            fixture_check = {"present": True, "structures": nf, "coordinates_bit_identical": same_crd, "bond_lists_identical": same_bonds,
+                             "hic_bonds_fixture_mean": float(np.mean(fx_counts)), "hic_bonds_this_run_mean": float(np.mean(mine)),
+                             "comparable": bool(int(fx["structures"]) == S and int(fx["pairs"]) == args.pairs and world >= 1)}
+            log("fixture check: %s" % json.dumps(fixture_check))
     nbonds = float(np.bitwise_count(bits).sum()) / S if hasattr(np, "bitwise_count") else float(np.unpackbits(bits.view(np.uint8)).sum()) / S
     log("A-step: %d pairs -> %d rows; actdist %.2f ms, assign %.2f ms (kernels); %.0f Hi-C bonds/structure"
         % (pi.size, row.size, astep["actdist_kernel_ms"], astep["assign_kernel_ms"], nbonds))
@@ -228,7 +300,7 @@ def build_workload(args, rank, world, device, log):
     seeds = (7 + rank * S + np.arange(S)).astype(np.int64)
     return {"genome": g, "radii": rad, "systems": systems, "crd": crd, "astep": astep, "prot": prot, "opts": opts,
             "template": template, "seeds": seeds, "rows": (row, col, dst, r0_all), "bits": bits, "pairs": (pi, pj, pw, pl),
-            "sigma": sigma}
+            "sigma": sigma, "fixture_check": fixture_check, "slab_structures": S_tot}
 
 
 def cpu_mstep_baseline(systems, prot, n_sample, threads):
@@ -244,9 +316,54 @@ def cpu_mstep_baseline(systems, prot, n_sample, threads):
     return len(sample) / dt, dt, res
 
 
+def cpu_astep_baseline(wl, n_pairs=2000, budget_s=12.0):
+    """The A-step restatement (oracle/astep_oracle.py = get_actdist + the text round trip, the reference's numpy code
+    line for line) on the host, on a bounded sample of the bench's own pair list over the same population:
+    one core, then all cores (one process per core, like the reference's ipyparallel map over batches)."""
+    from concurrent.futures import ProcessPoolExecutor
+    from oracle import astep_oracle
+    g, rad, crd = wl["genome"], wl["radii"], wl["crd"]
+    pi, pj, pw, pl = wl["pairs"]
+    sel = np.linspace(0, pi.size - 1, min(n_pairs, pi.size)).astype(np.int64)      # spread over the list: intra and inter pairs
+    a = (pi[sel], pj[sel], pw[sel], pl[sel])
+    t0 = time.perf_counter()
+    n1 = 0
+    for lo in range(0, sel.size, 100):                                              # single core, until the budget is spent
+        astep_oracle.actdist_rows(a[0][lo:lo + 100], a[1][lo:lo + 100], a[2][lo:lo + 100], a[3][lo:lo + 100], crd, rad,
+                                  g.chrom, g.copy_index, 2.0)
+        n1 += min(100, sel.size - lo)
+        if time.perf_counter() - t0 > budget_s / 2:
+            break
+    one = n1 / (time.perf_counter() - t0)
+    cores = os.cpu_count() or 1
+    _ASTEP_SHARED.update(crd=crd, rad=rad, chrom=g.chrom, ci=g.copy_index)
+    n_all = int(max(sel.size, min(pi.size, one * cores * budget_s / 2)))            # about budget_s / 2 seconds on all cores
+    sel2 = np.linspace(0, pi.size - 1, min(n_all, pi.size)).astype(np.int64)
+    chunks = [sel2[k::cores] for k in range(cores)]
+    import multiprocessing as mp
+    t0 = time.perf_counter()
+    with ProcessPoolExecutor(max_workers=cores, mp_context=mp.get_context("fork")) as ex:
+        list(ex.map(_astep_chunk, [(pi[c], pj[c], pw[c], pl[c]) for c in chunks]))
+    dt = time.perf_counter() - t0
+    return {"value": sel2.size / dt, "unit": "pairs/s", "cores": cores, "kind": "port", "one_core": one,
+            "sample": "%d of the %d haploid pairs over all %d structures on %d processes (%.1f s); one core: %d pairs (%.0f pairs/s)"
+                      % (sel2.size, pi.size, crd.shape[1], cores, dt, n1, one)}
+
+
+_ASTEP_SHARED = {}
+
+
+def _astep_chunk(a):
+    from oracle import astep_oracle
+    d = _ASTEP_SHARED
+    return astep_oracle.actdist_rows(a[0], a[1], a[2], a[3], d["crd"], d["rad"], d["chrom"], d["ci"], 2.0)[0].size
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the CPU restatement of the reference path (lmp_serial itself is not
-    installable here) on all host cores, same config / metric."""
+    """--impl reference: the CPU restatement of the reference path (lmp_serial itself is not installable here, see
+    DESIGN.md) on all host cores, on the GPU arm's own workload: every step optimises the fixture structures -- the
+    M-step inputs (relaxed coordinates + assigned Hi-C bonds) of the first structures of the default workload, written
+    by `bench.py --write-fixture` on a B200 -- one structure per host thread, full protocol."""
     if rank != 0:
         return
     g = synth.genome_2mb()
@@ -254,21 +371,15 @@ def run_reference(args, rank, world):
     rad = synth.bead_radii(n, NUCLEUS_R, 0.4)
     opts, prot = protocol(args.md_scale)
     cores = os.cpu_count() or 1
-    n_sample = args.cpu_sample or cores
-    # The GPU arm derives its Hi-C restraints from a relaxed population with its own kernels; this arm may not touch
-    # them, so every structure gets the same NUMBER of Hi-C upper bounds (what the GPU arm reports as
-    # hic_bonds_per_structure at its default size) between bead pairs that are within contact range in the starting
-    # territories -- like assigned contacts, satisfied when imposed.  Same beads, envelope, polymer, protocol.
-    from scipy.spatial import cKDTree
-    systems = []
-    for s in range(n_sample):
-        rng = np.random.default_rng(1234 + s)
-        xyz = synth.territories(g, NUCLEUS_R, rng)
-        near = cKDTree(xyz.astype(np.float64)).query_pairs(2.0 * 2.0 * float(rad[0]) * 0.95, output_type="ndarray")
-        pick = near[rng.choice(near.shape[0], min(REF_HIC_BONDS, near.shape[0]), replace=False)]
-        r0 = 2.0 * (rad[pick[:, 0]] + rad[pick[:, 1]]).astype(np.float64)
-        systems.append(synth.pack_structure(xyz, rad, g, pick[:, 0], pick[:, 1], r0, nucleus_radius=NUCLEUS_R, seed=1 + s, struct_id=s))
-    n_hic = int(np.mean([ps.bond_i.size for ps in systems])) - int(synth.polymer_bonds(g, rad)[0].size)
+    n_sample = min(args.cpu_sample or cores, N_FIXTURE)
+    fx = load_fixture()
+    if fx is None:
+        print(json.dumps({"impl": "reference", "unavailable": "tests/golden/bench_c2_structures.npz missing: run "
+                                                              "`bench.py --write-fixture` on a B200 first"}))
+        return
+    systems = fixture_systems(fx, g, rad, n_sample)
+    n_sample = len(systems)
+    n_hic = float(np.mean([ps.bond_i.size for ps in systems])) - float(synth.polymer_bonds(g, rad)[0].size)
     times = []
     for it in range(args.warmup + args.steps):
         v, dt, _ = cpu_mstep_baseline(systems, prot, n_sample, cores)
@@ -276,20 +387,82 @@ def run_reference(args, rank, world):
             times.append(dt)
     ms = 1e3 * float(np.mean(times))
     value = n_sample / (ms / 1e3)
-    sample = ("%d structures per step (one per host thread), steric + envelope + polymer + %d Hi-C upper bounds per structure, "
-              "full protocol" % (n_sample, n_hic))
+    sample = ("structures 0..%d of the workload (tests/golden/bench_c2_structures.npz: relaxed coordinates + %.0f assigned Hi-C "
+              "bonds per structure), one per host thread, full protocol; C restatement of the lammpgen script "
+              "(oracle/ff_oracle.c) -- lmp_serial is not installable offline" % (n_sample - 1, n_hic))
     print(json.dumps({
         "impl": "reference", "metric": "optimised structures/sec at 2Mb diploid", "value": value, "unit": "structures/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "configs[1]: 2 Mb diploid Hi-C (3008 beads, spherical envelope, full demo annealing protocol + CG, "
-                               "%d Hi-C bonds per structure between beads in contact range of the starting territories); CPU "
-                               "restatement of the lammpgen script (oracle/ff_oracle.c) -- lmp_serial itself is not installable "
-                               "offline" % n_hic, "beads": 3008, "structures_per_step": n_sample, "hic_bonds_per_structure": n_hic,
-                   "md_scale": args.md_scale},
+        "config": workload_config(args, md_force_evals(prot)),
+        "workload_stats": {"structures_per_step": n_sample, "hic_bonds_per_structure": n_hic},
         "cpu_baseline": {"value": value, "unit": "structures/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "structures/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+class _P(object):
+    """duck-typed igm.model.Particle / Force / Model (the attributes pack_model and the reference's LammpsModel read,
+    lammps_model.py:253-301)"""
+    __slots__ = ("pos", "r", "ptype")
+
+    def __init__(self, pos, r, ptype):
+        self.pos, self.r, self.ptype = pos, r, ptype
+
+
+class _F(object):
+    __slots__ = ("ftype", "i", "j", "d", "k", "shape", "semiaxes", "particle_ids")
+
+    def __init__(self, ftype, **kw):
+        self.ftype = ftype
+        for a, v in kw.items():
+            setattr(self, a, v)
+
+
+class _Model(object):
+    def __init__(self, uid):
+        self.id, self.particles, self.forces = uid, [], []
+
+
+def plugin_models(wl, n_models, rank, S):
+    """n_models structures of the workload as Model objects carrying the restraints ModelingStep.task applies
+    (igm/steps/ModelingStep.py:184-264): Steric, Envelope (with its dummy), Polymer, assigned Hi-C bonds."""
+    from igm_b200 import pack
+    g, rad, crd = wl["genome"], wl["radii"], wl["crd"]
+    row, col, dst, r0_all = wl["rows"]
+    bits = wl["bits"]
+    pb_i, pb_j, pb_r0 = synth.polymer_bonds(g, rad)
+    n = len(g)
+    models = []
+    for s in range(n_models):
+        m = _Model(rank * S + s)
+        m.particles = [_P(crd[k, s, :].copy(), rad[k], pack.NORMAL) for k in range(n)]
+        m.particles.append(_P(np.zeros(3, dtype=np.float32), 0.0, pack.DUMMY_STATIC))
+        m.forces.append(_F(pack.EXCLUDED_VOLUME, k=1.0, particle_ids=list(range(n))))
+        m.forces.append(_F(pack.ENVELOPE, shape="sphere", semiaxes=np.array([NUCLEUS_R] * 3), k=1.0, particle_ids=list(range(n))))
+        m.forces += [_F(pack.HARMONIC_UPPER_BOUND, i=int(a), j=int(b), d=float(d), k=1.0) for a, b, d in zip(pb_i, pb_j, pb_r0)]
+        sel = ((bits[:, s >> 5] >> np.uint32(s & 31)) & np.uint32(1)).astype(bool)
+        m.forces += [_F(pack.HARMONIC_UPPER_BOUND, i=int(a), j=int(b), d=float(d), k=1.0)
+                     for a, b, d in zip(row[sel], col[sel], r0_all[sel])]
+        models.append(m)
+    return models
+
+
+def plugin_e2e(wl, n_models, rank, S, device):
+    """The path IGM itself takes: controller.map(task) with one task per structure, every task calling
+    optimize(model, cfg) (ModelingStep.py:97, :335) -- B200Controller parks the calls and launches them together."""
+    from igm_b200 import kernel
+    from igm_b200.controller import B200Controller
+    models = plugin_models(wl, n_models, rank, S)
+    cfg = {"optimization": {"kernel": "b200", "optimizer_options": dict(wl["opts"], seed=7), "kernel_opts": {"b200": {"device": device}}},
+           "runtime": {"step_no": 1}}
+    ctl = B200Controller(max_threads=n_models)
+    t0 = time.perf_counter()
+    infos = ctl.map(lambda k: kernel.optimize(models[k], cfg), range(n_models))
+    dt = time.perf_counter() - t0
+    if not all(np.isfinite(i["final-energy"]) for i in infos):
+        raise RuntimeError("bench: plugin path returned a non-finite energy")
+    return dt, ctl.last_batcher.batches
 
 
 def main():
@@ -312,6 +485,12 @@ def main():
     torch.cuda.set_device(device)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda:%d" % device))
+    # measured FP32 FMA / shared-memory rates of this GPU (probe.cuh): the denominators of the MD kernel's roofline
+    import ctypes as C
+    pk = [C.c_double(0), C.c_double(0), C.c_double(0)]
+    _abi.check(_abi.load().igmk_peak_probe(device, C.byref(pk[0]), C.byref(pk[1]), C.byref(pk[2])), "igmk_peak_probe")
+    fp32_peak, fp32x2_peak, smem_peak = pk[0].value, pk[1].value, pk[2].value
+    log("probe: FFMA %.1f TFLOP/s, FFMA2 %.1f TFLOP/s, LDS.128 %.1f TB/s" % (fp32_peak, fp32x2_peak, smem_peak))
     wl = build_workload(args, rank, world, device, log)
     systems, prot = wl["systems"], wl["prot"]
     S = args.structures
@@ -372,13 +551,30 @@ def main():
     it = hic_iteration(crd, g, rad, wl["template"], wl["pairs"], wl["opts"], device=device, seeds=wl["seeds"])
     torch.cuda.synchronize(device)
     iter_s, t_astep, t_build = it["timings"]["total_s"], it["timings"]["astep_s"], it["timings"]["mstep_s"]
+    # ---- the north-star shape: ONE 1000-structure population over the N GPUs of the box (1000 / N per GPU) ----
+    ns_S = max(1, 1000 // world)
+    if world == 1 and S == 1000:
+        ns_s, ns_a, ns_m = iter_s, t_astep, t_build
+    else:
+        sub = np.ascontiguousarray(crd[:, :min(S, ns_S), :])
+        barrier()
+        it2 = hic_iteration(sub, g, rad, wl["template"], wl["pairs"], wl["opts"], device=device, seeds=wl["seeds"][:sub.shape[1]])
+        torch.cuda.synchronize(device)
+        ns_s, ns_a, ns_m = it2["timings"]["total_s"], it2["timings"]["astep_s"], it2["timings"]["mstep_s"]
+        ns_S = sub.shape[1]
+    # ---- the drop-in path itself: B200Controller.map(task) -> optimize(model, cfg) per structure ----
+    plug_n, plug_s, plug_batches = min(S, 256), None, None
+    if not args.no_plugin:
+        barrier()
+        plug_s, plug_batches = plugin_e2e(wl, plug_n, rank, S, device)
 
     tt = torch.tensor([ms_step, e2e_ms, wl["astep"]["actdist_kernel_ms"], wl["astep"]["actdist_e2e_ms"],
-                       wl["astep"]["assign_kernel_ms"], wl["astep"]["assign_e2e_ms"], iter_s, t_astep, t_build],
+                       wl["astep"]["assign_kernel_ms"], wl["astep"]["assign_e2e_ms"], iter_s, t_astep, t_build, ns_s, ns_a, ns_m,
+                       plug_s or 0.0],
                       dtype=torch.float64, device="cuda:%d" % device)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_step, e2e_ms, ad_k, ad_e, as_k, as_e, iter_s, t_astep, t_build = [float(v) for v in tt.tolist()]
+    ms_step, e2e_ms, ad_k, ad_e, as_k, as_e, iter_s, t_astep, t_build, ns_s, ns_a, ns_m, plug_s = [float(v) for v in tt.tolist()]
     if rank == 0:
         peaks = {}
         try:
@@ -386,10 +582,12 @@ def main():
         except Exception:
             pass
         traffic = {}
-        try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
-        except Exception:
-            pass
+        for name in ("r02_traffic.json", "r01_traffic.json"):
+            try:
+                traffic = json.load(open(os.path.join(ROOT, "profiles", name)))
+                break
+            except Exception:
+                pass
         hbm = peaks.get("hbm_gbs", 6650.0)
         which = "measured" if "hbm_gbs" in peaks else "fallback"
         feval, feval_exec, smem_eval = work_per_eval(systems, coords)
@@ -399,64 +597,86 @@ def main():
         a = wl["astep"]
         ad_gbs = a["actdist_bytes"] / (a["actdist_kernel_ms"] * 1e-3) / 1e9
         as_gbs = a["assign_bytes"] / (a["assign_kernel_ms"] * 1e-3) / 1e9
+        slab_mb = 12.0 * len(g) * wl["slab_structures"] / 1e6
+        l2_resident = slab_mb < 100.0                       # 126 MB L2: the slab is re-read from L2, not from HBM
+        if not (fp32_peak > 0):
+            fp32_peak, peak_src = FP32_PEAK_TFLOPS, "derived: 148 SM x 128 lanes x 2 x 1.965 GHz (probe failed)"
+        else:
+            peak_src = "measured in-run: dependent-chain FFMA micro-kernel, one 1024-thread CTA per SM (igmk_peak_probe)"
+        mdk = [k for k in traffic if k.startswith("k_md")]
         line = {
             "metric": "optimised structures/sec at 2Mb diploid", "value": S * world / (ms_step * 1e-3), "unit": "structures/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (MD) + f64 (CG)", "data": "synthetic",
-            "config": {"workload": "configs[1]: 2 Mb diploid Hi-C, %d structures per GPU, spherical envelope, full demo annealing "
-                                   "protocol + CG; Hi-C matrix = contact frequencies of the relaxed synthetic population, sigma=%.4g "
-                                   "keeps %d haploid pairs (the demo matrix keeps 614140 at its last sigma, 0.01)"
-                                   % (S, a["sigma"], a["pairs_total"]),
-                       "beads": 3008, "structures_per_gpu": S, "hic_bonds_per_structure": a["hic_bonds_per_structure"],
-                       "md_force_evals": evals, "cg_evals_mean": cg_evals, "md_scale": args.md_scale,
-                       "l2_policy": "working set per step (bond lists + neighbour tables, >400 MB) exceeds L2; A-step slab is "
-                                    "L2 resident at S=1000 (36 MB), noted in roofline_astep"},
+            "config": workload_config(args, evals),
+            "workload_stats": {"sigma": a["sigma"], "pairs_kept": a["pairs_total"], "hic_bonds_per_structure": a["hic_bonds_per_structure"],
+                               "cg_evals_mean": cg_evals, "fixture_check": wl["fixture_check"]},
             "e2e": {"value": S * world / (e2e_ms * 1e-3), "unit": "structures/s", "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h)},
+            "e2e_plugin": None if args.no_plugin else {
+                "value": plug_n * world / plug_s, "unit": "structures/s", "structures": plug_n, "seconds": plug_s, "launches": plug_batches,
+                "what": "B200Controller.map over one task per structure, each calling igm_b200.kernel.optimize(model, cfg) on a "
+                        "Model of Particle / Force objects (pack_model in Python, one launch for all parked calls, positions "
+                        "written back per particle); the Model objects are built outside the timed region, as ModelingStep.task "
+                        "(unchanged reference code) would"},
             "gpu_launches": 2 * args.steps,
             "am_iteration": {"seconds": iter_s, "structures_per_s": S * world / iter_s, "astep_seconds": t_astep,
                              "mstep_seconds": t_build,
                              "what": "host coordinates -> upload, all-gather, activation distances, row gather, assignment, "
                                      "bond build + submit, annealing MD + CG, coordinates back on the host"},
+            "am_iteration_north_star": {"seconds": ns_s, "structures": ns_S * world, "structures_per_gpu": ns_S, "astep_seconds": ns_a,
+                                        "mstep_seconds": ns_m,
+                                        "what": "the same iteration with 1000 / n_gpus structures per GPU: north_star's 'full 2 Mb "
+                                                "diploid 1000-structure A/M iteration' when n_gpus = 8"},
             "clocks": clocks,
-            "roofline": {"bound": "fp32", "kernel": "k_md", "achieved": md_tflops, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
-                         "frac": md_tflops / FP32_PEAK_TFLOPS,
-                         "traffic": (traffic["k_md2<3>"]["dram_bytes"] / traffic["k_md2<3>"]["structures"] / traffic["k_md2<3>"]["force_evals"]
-                                     * S * evals) if "k_md2<3>" in traffic else None,
-                         "traffic_note": "scaled from a short ncu --set full capture (profiles/r01_traffic.json): bytes per structure and "
+            "roofline": {"bound": "fp32", "kernel": "k_md2", "achieved": md_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": md_tflops / fp32_peak,
+                         "traffic": (traffic[mdk[0]]["dram_bytes"] / traffic[mdk[0]]["structures"] / traffic[mdk[0]]["force_evals"]
+                                     * S * evals) if mdk else None,
+                         "traffic_note": "scaled from a short ncu --set full capture (profiles/r0*_traffic.json): bytes per structure and "
                                          "force evaluation x this launch",
                          "flops_per_force_eval": feval,
-                         "flops_note": "algorithmic = SURVEY 8(d) formula, every pair and bond counted once; the kernel gathers "
-                                       "(no floating-point atomics, deterministic sums) and so executes each from both ends",
+                         "flops_note": "algorithmic = SURVEY 8(d) formula, every pair and bond counted once",
                          "executed": {"flops_per_force_eval": feval_exec,
                                       "tflops": feval_exec * evals * S / md_t / 1e12,
-                                      "frac": feval_exec * evals * S / md_t / 1e12 / FP32_PEAK_TFLOPS},
+                                      "frac": feval_exec * evals * S / md_t / 1e12 / fp32_peak},
                          "smem": {"bytes_per_force_eval": smem_eval, "achieved": smem_eval * evals * S / md_t / 1e12,
-                                  "peak": SMEM_PEAK_TBS, "unit": "TB/s", "frac": smem_eval * evals * S / md_t / 1e12 / SMEM_PEAK_TBS,
-                                  "note": "16-byte position reads the force loops issue, before bank-conflict replays "
-                                          "(ncu: 2.3x on the gathers, LSU data pipe 54 % busy)"},
+                                  "peak": smem_peak if smem_peak > 0 else SMEM_PEAK_TBS, "unit": "TB/s",
+                                  "frac": smem_eval * evals * S / md_t / 1e12 / (smem_peak if smem_peak > 0 else SMEM_PEAK_TBS),
+                                  "peak_source": "measured in-run: conflict-free LDS.128 micro-kernel" if smem_peak > 0 else "derived",
+                                  "note": "16-byte position reads the force loops issue, before bank-conflict replays"},
+                         "us_per_force_eval": md_t * 1e6 / evals / max(1.0, S / 148.0),
                          "kernel_ms": md_t * 1e3, "cg_kernel_ms": float(np.mean(cg_ms)),
-                         "peak_source": "derived: 148 SM x 128 lanes x 2 x 1.965 GHz (non-tensor FP32; not in MEASURED_PEAKS.json)"},
+                         "peak_source": peak_src, "fp32x2_peak": fp32x2_peak,
+                         "derived_peak": FP32_PEAK_TFLOPS},
             "astep": {"metric": "A-step haploid pairs/sec", "pairs": a["pairs_total"], "rows": a["rows"],
                       "structures": S * world,
                       "value": a["pairs_total"] / (ad_k * 1e-3), "e2e": a["pairs_total"] / (ad_e * 1e-3), "unit": "pairs/s",
                       "actdist_kernel_ms": ad_k, "actdist_e2e_ms": ad_e, "assign_kernel_ms": as_k, "assign_e2e_ms": as_e,
                       "assign_rows_x_structures_per_s": a["rows"] * float(S) / (as_k * 1e-3)},
             "roofline_astep": {"bound": "hbm", "kernel": "k_actdist", "achieved": ad_gbs, "peak": hbm, "unit": "GB/s",
-                               "frac": ad_gbs / hbm,
+                               "frac": ad_gbs / hbm, "l2_resident": l2_resident, "slab_mb": slab_mb,
+                               "note": ("the %.0f MB coordinate slab stays in the 126 MB L2 at this size: `achieved` is algorithmic bytes "
+                                        "per second served mostly from L2, not an HBM fraction; the HBM-streaming figure is the one at "
+                                        ">= 8000 structures (SCALE N = 8, tools/prof_astep.py)" % slab_mb) if l2_resident else
+                                       "the slab exceeds L2: coordinate rows stream from HBM",
                                "traffic": (traffic["k_actdist_reg<4>"]["dram_bytes"] / traffic["k_actdist_reg<4>"]["pairs"] * a["pairs_local"])
                                if ("k_actdist_reg<4>" in traffic and S * world == 1000) else None,
-                               "traffic_note": "ncu --set full capture at 1000 structures scaled by pairs; the slab is L2 resident",
+                               "traffic_note": "ncu --set full capture at 1000 structures scaled by pairs",
                                "peak_source": which + " copy bandwidth",
                                "assign_achieved": as_gbs, "assign_frac": as_gbs / hbm},
         }
         if not args.no_cpu_baseline and world == 1:
             cores = os.cpu_count() or 1
-            n_sample = args.cpu_sample or cores
+            n_sample = min(args.cpu_sample or cores, len(systems))
             v, dt, _ = cpu_mstep_baseline(systems, prot, n_sample, cores)
             line["cpu_baseline"] = {"value": v, "unit": "structures/s", "cores": cores, "kind": "port",
-                                    "sample": "%d of the %d structures (same restraints, full protocol), one per host "
-                                              "thread, %.1f s" % (n_sample, S, dt)}
+                                    "sample": "structures 0..%d of the %d (same restraints, full protocol), one per host "
+                                              "thread, %.1f s" % (n_sample - 1, S, dt)}
+            try:
+                line["astep"]["cpu_baseline"] = cpu_astep_baseline(wl)
+            except Exception as e:          # the A-step baseline must never cost the bench line
+                line["astep"]["cpu_baseline"] = {"error": repr(e)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -174,6 +174,7 @@ _SIGNATURES = {
     "igmk_last_error": (C.c_char_p, []),
     "igmk_version": (C.c_int, []),
     "igmk_device_count": (C.c_int, []),
+    "igmk_peak_probe": (C.c_int, [C.c_int, c_f64p, c_f64p, c_f64p]),
     "igmk_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
     "igmk_destroy": (C.c_int, [_vp]),
     "igmk_clear": (C.c_int, [_vp]),

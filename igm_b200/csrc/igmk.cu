@@ -19,6 +19,7 @@
 #include "md2.cuh"
 #include "md_big.cuh"
 #include "astep.cuh"
+#include "probe.cuh"
 
 using namespace igmk;
 
@@ -324,6 +325,50 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
     return 0;
 }
 
+// ---- measured rates for the MD kernel's roofline (probe.cuh) ----------------------------------
+extern "C" int igmk_peak_probe(int device, double* fp32_tflops, double* fp32x2_tflops, double* smem_tbs)
+{
+    int n = 0;
+    CU(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail("igmk_peak_probe: no such CUDA device");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    const int grid = prop.multiProcessorCount;          // one 1024-thread CTA per SM, like k_md2
+    float* d_out = nullptr;
+    CU(cudaMalloc((void**)&d_out, 16));
+    cudaStream_t st;
+    CU(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    const size_t lds_smem = 4 * PROBE_THREADS * sizeof(float4);
+    CU(cudaFuncSetAttribute(k_probe_lds, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lds_smem));
+    const int it_f = 1 << 17, it_l = 1 << 15;
+    double best[3] = {0, 0, 0};
+    for (int rep = 0; rep < 6; rep++)                    // rep 0 warms up; best of the rest
+        for (int which = 0; which < 3; which++) {
+            CU(cudaEventRecord(e0, st));
+            if (which == 0) k_probe_ffma<<<grid, PROBE_THREADS, 0, st>>>(it_f, 1.000001f, 1e-7f, d_out);
+            else if (which == 1) k_probe_ffma2<<<grid, PROBE_THREADS, 0, st>>>(it_f, 1.000001f, 1e-7f, d_out);
+            else k_probe_lds<<<grid, PROBE_THREADS, lds_smem, st>>>(it_l, d_out);
+            CU(cudaGetLastError());
+            CU(cudaEventRecord(e1, st));
+            CU(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, e0, e1));
+            if (rep == 0 || ms <= 0.f) continue;
+            const double per_s = 1e3 / ms;
+            const double v = which < 2 ? (double)grid * PROBE_THREADS * PROBE_CHAINS * 2.0 * it_f * per_s / 1e12
+                                       : (double)grid * PROBE_THREADS * 4.0 * 16.0 * it_l * per_s / 1e12;
+            best[which] = std::max(best[which], v);
+        }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st); cudaFree(d_out);
+    if (fp32_tflops) *fp32_tflops = best[0];
+    if (fp32x2_tflops) *fp32x2_tflops = best[1];
+    if (smem_tbs) *smem_tbs = best[2];
+    return 0;
+}
+
 // ---- whole population from a template + the assignment bit matrix ---------------------------
 // Append the staged structures of `parts` (in this order) to dst: the destination vectors grow once, then
 // every part copies its slice on its own thread, rebasing its offsets.
@@ -460,8 +505,10 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
                 sys.xyz = xyz.data();
                 sys.n_bonds = (int32_t)bi.size();
                 sys.bond_i = bi.data(); sys.bond_j = bj.data(); sys.bond_k = bk.data(); sys.bond_r0 = br.data(); sys.bond_style = bs.data();
-                sys.seed = seeds ? seeds[sl] : tmpl->seed;
                 sys.struct_id = tmpl->struct_id + sg;
+                // no seed list: the script's formula (lammps.py:159-165) with tmpl->seed standing for seed * step_no, so that
+                // every structure draws its own velocities (structure id 0 gets seed 1, as in the reference)
+                sys.seed = seeds ? seeds[sl] : (int64_t)(((__int128)std::max<int64_t>(tmpl->seed, 1) * sys.struct_id) % 9190037) + 1;
                 if (igmk_submit(part[t], &sys, nullptr)) { errs[t] = igmk_last_error(); return; }
             }
         });

@@ -119,6 +119,11 @@ typedef struct igmk_pop    igmk_pop_t;       /* device-resident population (A-st
 const char* igmk_last_error(void);
 int  igmk_version(void);
 int  igmk_device_count(void);
+/* Measurement aid (no counterpart in the reference): rates of three micro-kernels on `device`, one 1024-thread CTA
+ * per SM like the MD kernel -- dependent-chain FFMA (TFLOP/s, 2 flops per FMA), the same as packed fma.rn.f32x2,
+ * and conflict-free 16-byte shared-memory reads (TB/s).  bench.py states the MD kernel's FP32 / shared-memory
+ * fractions against these ("confirm by micro-benchmark").  Any pointer may be NULL. */
+int  igmk_peak_probe(int device, double* fp32_tflops, double* fp32x2_tflops, double* smem_tbs);
 
 /* ---- M-step: per-structure submit / run / fetch -------------------------------- */
 /* device: a CUDA ordinal, or IGMK_STAGING_ONLY for a handle that only stages on the host (submit, submit_population,
@@ -138,8 +143,10 @@ int igmk_submit(igmk_handle_t* h, const igmk_system_t* sys, int32_t* slot_out);
  * (host), the others keep tmpl->xyz.  On top, structure s gets HarmonicUpperBound((row[r], col[r]),
  * row_r0[r], row_k) for every actdist row r whose bit (s - s_begin) is set in bits[r]
  * (`bits_words` words per row: the matrix igmk_pop_assign returns for a population of those
- * structures; inter_hic.py:53-62, intra_hic.py:54-63).  seeds[k] (or tmpl->seed) and
- * tmpl->struct_id + s identify structure s.  Multi-threaded on the host.
+ * structures; inter_hic.py:53-62, intra_hic.py:54-63).  tmpl->struct_id + s identifies structure s; its velocity
+ * seed is seeds[s - s_begin], or with seeds == NULL ((max(tmpl->seed, 1) * (tmpl->struct_id + s)) mod 9190037) + 1
+ * -- the script's own formula (lammps.py:159-165) with tmpl->seed in the place of seed * step_no -- so that no two
+ * structures share a `velocity create` stream.  Multi-threaded on the host.
  */
 int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t n_bead,
                            int32_t n_struct_total, int32_t s_begin, int32_t n_struct, const float* crd,

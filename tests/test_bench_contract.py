@@ -14,6 +14,9 @@ def test_reference_arm_json_line():
     lines = [l for l in out.decode().splitlines() if l.strip()]
     assert len(lines) == 1
     j = json.loads(lines[0])
+    if not os.path.isfile(os.path.join(ROOT, "tests", "golden", "bench_c2_structures.npz")):
+        assert j["impl"] == "reference" and "unavailable" in j        # the fixture is made on a B200 (bench.py --write-fixture)
+        return
     for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
                 "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
         assert key in j, key
@@ -21,6 +24,13 @@ def test_reference_arm_json_line():
     assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1 and j["cpu_baseline"]["value"] == j["value"]
     assert j["e2e"] == {"value": j["value"], "unit": j["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert j["value"] > 0 and "workload" in j["config"]
+    # both arms print the same `config`: it is built from the arguments alone
+    sys.path.insert(0, ROOT)
+    import bench
+    import argparse
+    args = argparse.Namespace(structures=1000, pairs=614140, md_scale=0.002)
+    assert j["config"] == bench.workload_config(args, j["config"]["md_force_evals"])
+    assert j["workload_stats"]["structures_per_step"] == 2
 
 
 def test_reference_arm_other_ranks_do_nothing():

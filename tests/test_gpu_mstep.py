@@ -235,6 +235,35 @@ def test_submit_population_equals_per_structure_submits():
                 assert c.fetch(k)[1].final_energy == e_sp[20 + k]
 
 
+def test_population_without_seed_list_gives_every_structure_its_own_seed():
+    """seeds=None: structure s runs `velocity create` with ((max(tmpl.seed, 1) * (tmpl.struct_id + s)) mod 9190037) + 1
+    (lammps.py:159-165), not one shared stream -- identical start coordinates must end in different places, and exactly
+    where an explicit list of those seeds puts them"""
+    g = synth.Genome([14, 11, 8, 6], n_autosomes=3)
+    R = 1400.0
+    rad = synth.bead_radii(len(g), R, 0.3)
+    one = synth.territories(g, R, np.random.default_rng(3))
+    S = 4
+    crd = np.ascontiguousarray(np.repeat(one[:, None, :], S, axis=1))
+    none_i = np.zeros(0, dtype=np.int32)
+    bits = np.zeros((0, 1), dtype=np.uint32)
+    prot = short_protocol(md=120, relax=20)
+    out = []
+    for tmpl_seed, seeds in ((0, None), (0, np.array([((1 * (50 + s)) % 9190037) + 1 for s in range(S)], dtype=np.int64)),
+                             (977, None), (977, np.array([((977 * (50 + s)) % 9190037) + 1 for s in range(S)], dtype=np.int64))):
+        tmpl = synth.pack_structure(np.zeros((len(g), 3), dtype=np.float32), rad, g, nucleus_radius=R, seed=tmpl_seed, struct_id=50)
+        with MStepBatch(0) as b:
+            b.submit_population(tmpl, crd, len(g), none_i, none_i, np.zeros(0), 1.0, bits, seeds=seeds)
+            b.run(prot)
+            out.append([b.fetch(s)[0] for s in range(S)])
+    for k in (0, 2):
+        for s in range(S):
+            assert np.array_equal(out[k][s].view(np.uint32), out[k + 1][s].view(np.uint32))
+            for t in range(s):
+                assert not np.array_equal(out[k][s], out[k][t])
+    assert not np.array_equal(out[0][1], out[2][1])
+
+
 def test_run_population_pipeline_equals_one_batch():
     """kernel.run_population (chunks of 32 on their own streams, assembly overlapping the MD) returns
     bit-identical coordinates, energies and violation counts to one batch holding every structure"""
