@@ -65,6 +65,16 @@ class Result(C.Structure):
     ]
 
 
+class PopExtras(C.Structure):
+    """igmk_pop_extras_t: restraints that differ from structure to structure (see include/igmk.h)"""
+    _fields_ = [
+        ("bond_off", c_i64p), ("bond_i", c_i32p), ("bond_j", c_i32p), ("bond_k", c_f64p), ("bond_r0", c_f64p),
+        ("bond_style", c_u8p),
+        ("n_env", C.c_int32), ("env_abck", c_f64p), ("env_row_off", c_i64p), ("env_bead", c_i32p), ("env_bits", c_u32p),
+        ("env_bits_words", C.c_int32),
+    ]
+
+
 def _ptr(a, ct):
     return a.ctypes.data_as(ct)
 
@@ -181,12 +191,15 @@ _SIGNATURES = {
     "igmk_submit": (C.c_int, [_vp, C.POINTER(System), c_i32p]),
     "igmk_submit_population": (C.c_int, [_vp, C.POINTER(System), C.c_int32, C.c_int32, C.c_int32, C.c_int32, c_f32p, C.c_int64,
                                          c_i32p, c_i32p, c_f64p, C.c_double, c_u32p, C.c_int32, c_i64p, c_i32p]),
+    "igmk_submit_population_ex": (C.c_int, [_vp, C.POINTER(System), C.c_int32, C.c_int32, C.c_int32, C.c_int32, c_f32p, C.c_int64,
+                                            c_i32p, c_i32p, c_f64p, C.c_double, c_u32p, C.c_int32, c_i64p, C.POINTER(PopExtras), c_i32p]),
     "igmk_slot_sizes": (C.c_int, [_vp, C.c_int32, c_i32p, c_i64p, c_i64p]),
     "igmk_upload": (C.c_int, [_vp]),
     "igmk_reset_coordinates": (C.c_int, [_vp]),
     "igmk_run": (C.c_int, [_vp, C.POINTER(Protocol)]),
     "igmk_single_point": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double]),
     "igmk_single_point_f32": (C.c_int, [_vp, C.c_double, C.c_double, C.c_double]),
+    "igmk_md_forces": (C.c_int, [_vp, C.POINTER(Protocol), C.c_int32]),
     "igmk_fetch": (C.c_int, [_vp, C.c_int32, c_f32p, C.POINTER(Result)]),
     "igmk_fetch_forces": (C.c_int, [_vp, C.c_int32, c_f64p]),
     "igmk_layout_stats": (C.c_int, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),

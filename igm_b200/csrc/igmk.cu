@@ -81,13 +81,19 @@ struct igmk_handle {
     int nl_width = NL_WIDTH0;
     // thread-per-atom MD layout (md2.cuh), built at upload time
     int md2_K = 0, md2_nlw = MD2_NLW0;
-    float skin_factor = 0.7f;   // measured optimum on the 2 Mb workload (profiles/)
+    float skin_factor = 0.7f;   // k_md_big: single-level neighbour skin in bead radii
+    float skin_inner = 0.7f;    // k_md2: neighbour skin in bead radii (profiles/)
     std::vector<Md2Desc> md2_desc;
     std::vector<uint16_t> md2_perm;
     std::vector<int32_t>  md2_ell_off;
+    std::vector<int4>     md2_eblk;
     std::vector<uint32_t> md2_ell_items;
+    std::string md2_error;
+    int64_t md2_sym_bonds = 0, md2_bonds = 0;
     Md2Desc* d_md2_desc = nullptr; uint16_t* d_md2_perm = nullptr; int32_t* d_md2_ell_off = nullptr;
     uint32_t* d_md2_ell_items = nullptr; uint32_t* d_md2_ell_act = nullptr; uint16_t* d_md2_nl = nullptr;
+    int4* d_md2_eblk = nullptr; float4* d_md2_gf = nullptr;
+    double* d_md2_dbg = nullptr;
     bool md_big = false; float* d_big_state = nullptr; double* d_big = nullptr;
     bool dirty = true;
     // device
@@ -110,6 +116,8 @@ struct igmk_handle {
         cudaFree(d_xd); cudaFree(d_fd); cudaFree(d_work); cudaFree(d_res); cudaFree(d_flags);
         cudaFree(d_big_state); cudaFree(d_big); d_big_state = nullptr; d_big = nullptr;
         cudaFree(d_md2_desc); cudaFree(d_md2_perm); cudaFree(d_md2_ell_off); cudaFree(d_md2_ell_items); cudaFree(d_md2_ell_act); cudaFree(d_md2_nl); d_md2_ell_act = nullptr;
+        cudaFree(d_md2_eblk); cudaFree(d_md2_gf); cudaFree(d_md2_dbg);
+        d_md2_eblk = nullptr; d_md2_gf = nullptr; d_md2_dbg = nullptr;
         d_md2_desc = nullptr; d_md2_perm = nullptr; d_md2_ell_off = nullptr; d_md2_ell_items = nullptr; d_md2_nl = nullptr;
         d_desc = nullptr; d_xyzr = nullptr; d_xyzr0 = nullptr; d_kind = nullptr; d_envmask = nullptr; d_bond_ptr = nullptr;
         d_bond_items = nullptr; d_btype_f = nullptr; d_btype_d = nullptr; d_nl = nullptr; d_nl_cnt = nullptr;
@@ -151,7 +159,7 @@ extern "C" int igmk_create(int device, igmk_handle_t** out)
     }
     if (const char* e = getenv("IGMK_SKIN")) {              // neighbour skin in units of the bead radius (results do not depend on it)
         const float f = (float)atof(e);
-        if (f >= 0.05f && f <= 4.0f) h->skin_factor = f;
+        if (f >= 0.05f && f <= 4.0f) { h->skin_factor = f; h->skin_inner = f; }
     }
 
     CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -427,7 +435,27 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
                                       int64_t n_rows, const int32_t* row, const int32_t* col, const double* row_r0, double row_k,
                                       const uint32_t* bits, int32_t bits_words, const int64_t* seeds, int32_t* first_slot_out)
 {
+    return igmk_submit_population_ex(h, tmpl, n_bead, n_struct_total, s_begin, n_struct, crd, n_rows, row, col, row_r0, row_k,
+                                     bits, bits_words, seeds, nullptr, first_slot_out);
+}
+
+extern "C" int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t n_bead, int32_t n_struct_total,
+                                         int32_t s_begin, int32_t n_struct, const float* crd,
+                                         int64_t n_rows, const int32_t* row, const int32_t* col, const double* row_r0, double row_k,
+                                         const uint32_t* bits, int32_t bits_words, const int64_t* seeds,
+                                         const igmk_pop_extras_t* ex, int32_t* first_slot_out)
+{
     if (!h || !tmpl || !crd) return fail("igmk_submit_population: NULL argument");
+    if (ex) {
+        if (ex->n_env < 0 || tmpl->n_env + ex->n_env > IGMK_MAX_ENVELOPES) return fail("igmk_submit_population: too many envelopes");
+        if (ex->n_env > 0 && (!ex->env_abck || !ex->env_row_off || (ex->env_row_off[ex->n_env] > 0 && (!ex->env_bead || !ex->env_bits))))
+            return fail("igmk_submit_population: NULL envelope arguments in extras");
+        if (ex->n_env > 0 && ex->env_row_off[ex->n_env] > 0 && ex->env_bits_words * 32 < n_struct)
+            return fail("igmk_submit_population: envelope bit matrix narrower than the structure range");
+        if (ex->bond_off && ex->bond_off[n_struct] > ex->bond_off[0] &&
+            (!ex->bond_i || !ex->bond_j || !ex->bond_k || !ex->bond_r0 || !ex->bond_style))
+            return fail("igmk_submit_population: NULL bond arguments in extras");
+    }
     if (n_bead < 1 || n_bead > tmpl->n_atoms) return fail("igmk_submit_population: n_bead must be 1..tmpl->n_atoms");
     if (n_struct < 0 || s_begin < 0 || s_begin + n_struct > n_struct_total) return fail("igmk_submit_population: bad structure range");
     if (n_rows > 0 && (!row || !col || !row_r0 || !bits)) return fail("igmk_submit_population: NULL row arguments");
@@ -478,6 +506,7 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
             const int na = tmpl->n_atoms;
             std::vector<float> xyz((size_t)na * 3);
             std::vector<int32_t> bi, bj; std::vector<double> bk, br; std::vector<uint8_t> bs;
+            std::vector<double> eabck; std::vector<int32_t> eoff, emem;
             {                                             // this thread's share of the staging vectors, allocated once
                 size_t nb = 0;
                 for (int sl = lo; sl < hi; sl++) { nb += (size_t)tmpl->n_bonds; for (int q = 0; q < nscan; q++) nb += found[q][sl].size(); }
@@ -502,6 +531,24 @@ extern "C" int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmp
                         bi.push_back(row[r]); bj.push_back(col[r]); bk.push_back(row_k); br.push_back(row_r0[r]); bs.push_back(IGMK_BOND_UPPER);
                     }
                 igmk_system_t sys = *tmpl;
+                if (ex && ex->bond_off)                // this structure's own restraints (FISH, fish.py:93-274), after the Hi-C ones
+                    for (int64_t q = ex->bond_off[sl]; q < ex->bond_off[sl + 1]; q++) {
+                        bi.push_back(ex->bond_i[q]); bj.push_back(ex->bond_j[q]); bk.push_back(ex->bond_k[q]);
+                        br.push_back(ex->bond_r0[q]); bs.push_back(ex->bond_style[q]);
+                    }
+                if (ex && ex->n_env > 0) {             // envelope groups whose members differ by structure (DamID, damid.py:116-142)
+                    eabck.assign(tmpl->env_abck, tmpl->env_abck + 4 * (size_t)tmpl->n_env);
+                    eabck.insert(eabck.end(), ex->env_abck, ex->env_abck + 4 * (size_t)ex->n_env);
+                    eoff.assign(tmpl->env_off, tmpl->env_off + tmpl->n_env + 1);
+                    emem.assign(tmpl->env_members, tmpl->env_members + tmpl->env_off[tmpl->n_env]);
+                    for (int e = 0; e < ex->n_env; e++) {
+                        for (int64_t r = ex->env_row_off[e]; r < ex->env_row_off[e + 1]; r++)
+                            if ((ex->env_bits[(size_t)r * ex->env_bits_words + (sl >> 5)] >> (sl & 31)) & 1u) emem.push_back(ex->env_bead[r]);
+                        eoff.push_back((int32_t)emem.size());
+                    }
+                    sys.n_env = tmpl->n_env + ex->n_env;
+                    sys.env_abck = eabck.data(); sys.env_off = eoff.data(); sys.env_members = emem.data();
+                }
                 sys.xyz = xyz.data();
                 sys.n_bonds = (int32_t)bi.size();
                 sys.bond_i = bi.data(); sys.bond_j = bj.data(); sys.bond_k = bk.data(); sys.bond_r0 = br.data(); sys.bond_style = bs.data();
@@ -619,6 +666,130 @@ static void md2_build(igmk_handle* h)
     for (auto& th : pool) th.join();
 }
 
+// Layout for k_md2 (md2.cuh): every bond is ORIENTED -- one end owns it, the other receives it through an inbox slot --
+// and the owned items of an atom are split into block A (the most frequent bond type, when that is an upper bound) and
+// block B (everything else, and bonds whose two ends both have full inboxes: listed at both ends, SYM).  Atoms are
+// ordered by the number of items they own, 32 at a time into warp-slots laid out boustrophedon over the warps.
+static void md2_build_owner(igmk_handle* h)
+{
+    const int K = h->md2_K, np = K * MD2_T, NW = MD2_NW, G = K * NW;
+    const size_t ns = h->desc.size();
+    h->md2_desc.assign(ns, Md2Desc());
+    h->md2_perm.assign(ns * (size_t)np, MD2_NONE);
+    h->md2_eblk.assign(ns * (size_t)G, make_int4(0, 0, 0, 0));
+    h->md2_ell_off.clear();
+    h->md2_error.clear();
+    std::vector<std::vector<uint32_t>> items(ns);
+    std::vector<int64_t> nsym(ns, 0), nbond(ns, 0);
+    std::vector<std::string> errs(ns);
+    auto build_one = [&](size_t s) {
+        const StructDesc& d = h->desc[s];
+        const int n = d.n_atoms;
+        const int32_t* bp = h->bond_ptr.data() + d.bond_ptr_off;
+        const uint32_t* bi = h->bond_items.data() + d.bond_item_off;
+        const bool a_ok = h->btype_f[d.btype_off].y > 0.f;              // type 0 is an upper bound: block A may be used
+        // ---- orientation: the owner is the end that owns fewer items so far; the other end must have a free inbox slot ----
+        struct Own { int32_t other; uint32_t type; int8_t q; };         // q < 0: SYM
+        std::vector<std::vector<Own>> rows((size_t)n);
+        std::vector<int> own((size_t)n, 0), indeg((size_t)n, 0);
+        for (int a = 0; a < n; a++)
+            for (int c = bp[a]; c < bp[a + 1]; c++) {
+                const int b = (int)(bi[c] & 0xffffu);
+                const uint32_t t = bi[c] >> 16;
+                if (b <= a) continue;                                   // every bond once (b == a: a bond to oneself has no force)
+                if (t >= (uint32_t)MD2_MAX_TYPES) { errs[s] = "more than 16384 distinct bond types in one structure"; return; }
+                nbond[s]++;
+                const int da = bp[a + 1] - bp[a], db = bp[b + 1] - bp[b];
+                int o = (own[a] < own[b] || (own[a] == own[b] && da >= db)) ? a : b, r = o == a ? b : a;
+                if (indeg[r] >= MD2_INBOX - 1) std::swap(o, r);
+                if (indeg[r] >= MD2_INBOX - 1) {                        // both inboxes full: evaluate from both ends
+                    rows[a].push_back({b, t, -1}); rows[b].push_back({a, t, -1});
+                    own[a]++; own[b]++; nsym[s]++;
+                    continue;
+                }
+                rows[o].push_back({r, t, (int8_t)indeg[r]});
+                indeg[r]++; own[o]++;
+            }
+        // ---- atom order by owned items ----
+        std::vector<int> order((size_t)n), pos((size_t)n, -1);
+        for (int a = 0; a < n; a++) order[a] = a;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return own[a] > own[b]; });
+        uint16_t* perm = h->md2_perm.data() + s * (size_t)np;
+        auto slot_of_group = [&](int g) { const int k = g / NW, r = g % NW; return k * NW + ((k & 1) ? NW - 1 - r : r); };
+        for (int g = 0; g < G; g++) {
+            const int gi = slot_of_group(g), k = gi / NW, w = gi % NW;
+            for (int l = 0; l < 32; l++) {
+                const int q = g * 32 + l;
+                if (q >= n) break;
+                const int p = k * MD2_T + w * 32 + l;
+                perm[p] = (uint16_t)order[q]; pos[order[q]] = p;
+            }
+        }
+        Md2Desc& m = h->md2_desc[s];
+        m.perm_off = (int32_t)(s * (size_t)np);
+        m.ell_desc_off = (int32_t)(s * (size_t)G);
+        m.K = K;
+        int4* eb = h->md2_eblk.data() + m.ell_desc_off;
+        std::vector<uint32_t>& out = items[s];
+        for (int gi = 0; gi < G; gi++) {               // blocks in (slot, warp) order = the order the kernel indexes them
+            const int k = gi / NW, w = gi % NW;
+            int cols[2] = {0, 0};
+            for (int l = 0; l < 32; l++) {
+                const int a = perm[k * MD2_T + w * 32 + l];
+                if (a == MD2_NONE) continue;
+                int c[2] = {0, 0};
+                for (const Own& it : rows[a]) c[(a_ok && it.type == 0 && it.q >= 0) ? 0 : 1]++;
+                cols[0] = std::max(cols[0], c[0]); cols[1] = std::max(cols[1], c[1]);
+            }
+            int off[2];
+            for (int blk = 0; blk < 2; blk++) {
+                cols[blk] = (cols[blk] + 3) / 4 * 4;    // the kernel reads 4 columns at a time, unguarded
+                off[blk] = (int)out.size();
+                out.resize(out.size() + (size_t)cols[blk] * 32, 0u);
+                uint32_t* b = out.data() + off[blk];
+                // layout [batch of 4 columns][lane][4]: one 16-byte load per lane and batch; padding = an item to oneself
+                for (int l = 0; l < 32; l++) {
+                    const uint32_t self = ((uint32_t)(k * MD2_T + w * 32 + l) << 4) | (blk == 0 ? 15u : MD2_IT_SYM);
+                    for (int c = 0; c < cols[blk]; c++) b[((c >> 2) * 32 + l) * 4 + (c & 3)] = self;
+                }
+                for (int l = 0; l < 32; l++) {
+                    const int a = perm[k * MD2_T + w * 32 + l];
+                    if (a == MD2_NONE) continue;
+                    int c = 0;
+                    for (const Own& it : rows[a]) {
+                        if (((a_ok && it.type == 0 && it.q >= 0) ? 0 : 1) != blk) continue;
+                        const uint32_t v = ((uint32_t)pos[it.other] << 4) | (it.q >= 0 ? (uint32_t)it.q : MD2_IT_SYM) | (it.type << MD2_IT_TSHIFT);
+                        b[((c >> 2) * 32 + l) * 4 + (c & 3)] = v;
+                        c++;
+                    }
+                }
+            }
+            eb[gi] = make_int4(off[0], cols[0] / 4, off[1], cols[1] / 4);
+        }
+    };
+    const int nthr = (int)std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), ns));
+    std::vector<std::thread> pool;
+    for (int t = 0; t < nthr; t++)
+        pool.emplace_back([&, t]() { for (size_t s = (size_t)t; s < ns; s += (size_t)nthr) build_one(s); });
+    for (auto& th : pool) th.join();
+    size_t total = 0;
+    h->md2_sym_bonds = 0; h->md2_bonds = 0;
+    for (size_t s = 0; s < ns; s++) {
+        if (!errs[s].empty() && h->md2_error.empty()) h->md2_error = errs[s];
+        h->md2_desc[s].ell_item_off = (int64_t)total; total += items[s].size();
+        h->md2_sym_bonds += nsym[s]; h->md2_bonds += nbond[s];
+    }
+    h->md2_ell_items.resize(total);
+    pool.clear();
+    for (int t = 0; t < nthr; t++)
+        pool.emplace_back([&, t]() {
+            for (size_t s = (size_t)t; s < ns; s += (size_t)nthr)
+                if (!items[s].empty())
+                    memcpy(h->md2_ell_items.data() + h->md2_desc[s].ell_item_off, items[s].data(), items[s].size() * sizeof(uint32_t));
+        });
+    for (auto& th : pool) th.join();
+}
+
 static int upload(igmk_handle* h)
 {
     if (h->device < 0) return fail("igmk: this handle was created with IGMK_STAGING_ONLY and cannot touch a GPU");
@@ -654,19 +825,28 @@ static int upload(igmk_handle* h)
     if (ctx_is_big<double>(h->max_atoms, false) || ctx_is_big<float>(h->max_atoms, false))
         CU(cudaMalloc((void**)&h->d_big, (na + 32 * ns) * 10 * sizeof(double)));
     if (h->md2_K > 0) {
-        md2_build(h);
+        if (h->md_big) md2_build(h);
+        else {
+            md2_build_owner(h);
+            if (!h->md2_error.empty()) return fail("igmk: " + h->md2_error);
+        }
         CU(dev_alloc_copy(&h->d_md2_desc, h->md2_desc, h->stream));
         CU(dev_alloc_copy(&h->d_md2_perm, h->md2_perm, h->stream));
         CU(dev_alloc_copy(&h->d_md2_ell_off, h->md2_ell_off, h->stream));
         CU(dev_alloc_copy(&h->d_md2_ell_items, h->md2_ell_items, h->stream));
         CU(cudaMalloc((void**)&h->d_md2_ell_act, std::max<size_t>(h->md2_ell_items.size(), 1) * sizeof(uint32_t)));
         CU(cudaMalloc((void**)&h->d_md2_nl, h->md2_perm.size() * (size_t)h->md2_nlw * sizeof(uint16_t)));
+        if (!h->md_big) {
+            CU(dev_alloc_copy(&h->d_md2_eblk, h->md2_eblk, h->stream));
+            CU(cudaMalloc((void**)&h->d_md2_gf, h->md2_perm.size() * (size_t)MD2_INBOX * sizeof(float4)));
+        }
     }
     h->h2d_bytes = ns * sizeof(StructDesc) + 2 * na * sizeof(float4) + na * (sizeof(uint8_t) + sizeof(uint32_t)) +
                    h->bond_ptr.size() * sizeof(int32_t) + h->bond_items.size() * sizeof(uint32_t) +
                    h->btype_f.size() * (sizeof(float2) + sizeof(double2)) +
                    h->md2_desc.size() * sizeof(Md2Desc) + h->md2_perm.size() * sizeof(uint16_t) +
-                   h->md2_ell_off.size() * sizeof(int32_t) + h->md2_ell_items.size() * sizeof(uint32_t);
+                   h->md2_ell_off.size() * sizeof(int32_t) + h->md2_ell_items.size() * sizeof(uint32_t) +
+                   (h->md_big ? 0 : h->md2_eblk.size() * sizeof(int4));
     h->dirty = false;
     return 0;
 }
@@ -690,7 +870,7 @@ extern "C" int igmk_layout_stats(igmk_handle_t* h, int32_t* slots_per_thread, in
     const int keep_K = h->md2_K;
     h->md2_K = K;
     const auto t0 = std::chrono::steady_clock::now();
-    md2_build(h);
+    if (md2_pick_K(h->max_atoms) == 0) md2_build(h); else md2_build_owner(h);
     const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     h->md2_K = keep_K;
     h->dirty = true;                                              // the next upload rebuilds for its own K / path
@@ -814,23 +994,26 @@ template <int K>
 static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
 {
     const size_t sm = md2_smem_bytes(K);
-    CU(cudaFuncSetAttribute(k_md2<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    CU(cudaFuncSetAttribute(k_md2<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    CU(cudaFuncSetAttribute(k_md2<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     Md2View V;
     V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
     V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.ell_act = h->d_md2_ell_act;
+    V.eblk = h->d_md2_eblk; V.gf = h->d_md2_gf; V.dbg_forces = h->d_md2_dbg;
     V.prof = nullptr;
-    const bool prof = getenv("IGMK_PROF") != nullptr;
-    if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 8 * sizeof(long long))); CU(cudaMemsetAsync(V.prof, 0, (size_t)ns * 8 * sizeof(long long), h->stream)); }
-    k_md2<K><<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
+    const bool prof = getenv("IGMK_PROF") != nullptr && P.debug_stage < 0;
+    if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 16 * sizeof(long long))); CU(cudaMemsetAsync(V.prof, 0, (size_t)ns * 16 * sizeof(long long), h->stream)); }
+    if (prof) k_md2<K, true><<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
+    else k_md2<K, false><<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
     CU(cudaGetLastError());
     if (prof) {                  // diagnostics only: per-phase SM cycles of thread 0, averaged over the structures
-        std::vector<long long> t((size_t)ns * 8);
+        std::vector<long long> t((size_t)ns * 16);
         CU(copy_on(h->stream, t.data(), V.prof, t.size() * sizeof(long long), cudaMemcpyDeviceToHost));
         cudaFree(V.prof);
-        double a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        for (int s = 0; s < ns; s++) for (int k = 0; k < 8; k++) a[k] += (double)t[8 * (size_t)s + k] / ns;
-        fprintf(stderr, "[igmk prof] k_md2 mean cycles per structure: forces %.3g, rebuild-search %.3g, rebuilds %.3g, n_rebuilds %.1f; "
-                "stages %.3g %.3g %.3g %.3g\n", a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7]);
+        double a[16] = {0};
+        for (int s = 0; s < ns; s++) for (int k = 0; k < 16; k++) a[k] += (double)t[16 * (size_t)s + k] / ns;
+        fprintf(stderr, "[igmk prof] k_md2 mean cycles per structure (thread 0): force evaluations %.3g (pair loops %.3g, bond block A %.3g, "
+                "barrier + receive %.3g); rebuilds %.3g (of which search %.3g), %.1f rebuilds\n", a[0], a[5], a[6], a[4], a[2], a[1], a[3]);
     }
     return 0;
 }
@@ -838,9 +1021,11 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
 static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
 {
     if (h->md_big) {
+        if (P.debug_stage >= 0) return fail("igmk_md_forces: not available on the global-memory MD path");
         const size_t sm = md_big_smem_bytes(h->md2_K);
         CU(cudaFuncSetAttribute(k_md_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         Md2View V;
+        memset(&V, 0, sizeof V);
         V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
         V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.prof = nullptr; V.ell_act = h->d_md2_ell_act;
         k_md_big<<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P, h->d_big_state);
@@ -881,7 +1066,8 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
         cudaEvent_t e0, e1, e2;
         CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
         CU(cudaEventRecord(e0, h->stream));
-        MdParams P; P.prot = *prot; P.skin_factor = h->skin_factor;
+        MdParams P; P.prot = *prot; P.skin_factor = h->md_big ? h->skin_factor : h->skin_inner;
+        P.debug_stage = -1;
         if (int rc = launch_md2(h, B, P, ns)) return rc;
         CU(cudaEventRecord(e1, h->stream));
         CU(cudaStreamWaitEvent(h->stream_hi, e1, 0));
@@ -911,6 +1097,41 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
     h->viol_valid = false;
     for (auto& r : h->res) r.md_seconds = ms * 1e-3;
     h->forces.clear();                 // copied on demand by igmk_fetch_forces
+    h->have_forces = true;
+    return 0;
+}
+
+// Forces as the MD kernel itself computes them (float32, its own lists and approximations), for the parity test of
+// that routine: run setup of annealing stage `stage` (its pair and envelope scales), no time step taken.
+extern "C" int igmk_md_forces(igmk_handle_t* h, const igmk_protocol_t* prot, int32_t stage)
+{
+    if (!h || !prot) return fail("igmk_md_forces: NULL argument");
+    if (h->desc.empty()) return fail("igmk_md_forces: nothing submitted");
+    if (stage < 0 || stage >= prot->n_stage) return fail("igmk_md_forces: no such stage");
+    if (h->device < 0) return upload(h);
+    CU(cudaSetDevice(h->device));
+    const int ns = (int)h->desc.size();
+    for (;;) {
+        if (int rc = upload(h)) return rc;
+        if (!h->d_md2_dbg) CU(cudaMalloc((void**)&h->d_md2_dbg, h->xyzr.size() * 3 * sizeof(double)));
+        CU(cudaMemsetAsync(h->d_md2_dbg, 0, h->xyzr.size() * 3 * sizeof(double), h->stream));
+        Batch B = make_batch(h);
+        CU(cudaMemsetAsync(h->d_flags, 0, ns * sizeof(int32_t), h->stream));
+        MdParams P; P.prot = *prot; P.skin_factor = h->skin_inner; P.debug_stage = stage;
+        if (int rc = launch_md2(h, B, P, ns)) return rc;
+        CU(cudaStreamSynchronize(h->stream));
+        const int rc = collect(h, "igmk_md_forces");
+        if (rc == IGMK_NL_OVERFLOW) {
+            const int cap = (h->max_atoms + 7) / 8 * 8;
+            bool w = false;
+            if (h->md2_nlw < cap) { h->md2_nlw = std::min(h->md2_nlw * 2, cap); w = true; }
+            if (w) { h->dirty = true; continue; }
+        }
+        if (rc) return 1;
+        break;
+    }
+    h->forces.resize(h->xyzr.size() * 3);
+    CU(copy_on(h->stream, h->forces.data(), h->d_md2_dbg, h->forces.size() * sizeof(double), cudaMemcpyDeviceToHost));
     h->have_forces = true;
     return 0;
 }

@@ -1,21 +1,42 @@
 // md2.cuh -- the annealing-MD kernel of the M-step (lammps.py:285-351), one CTA per structure.
 //
 // Work decomposition: THREAD PER ATOM.  Thread t owns the atoms at positions t, t+1024, ...
-// (K slots per thread) of a host-chosen ordering in which the 32 atoms of a warp-slot have
-// similar bond counts.  Each thread gathers the complete force on its own atoms (no atomics, no
-// cross-lane reductions => bit-reproducible), and keeps their velocities and forces in registers.
-// Shared memory holds only what other threads read: the positions (float4 x,y,z,radius), a copy of
-// them in cell order for the neighbour search, the coordinates of the last neighbour build and the
-// cell grid.  Lists are laid out so that a warp reads them with full 32-lane coalescing:
-//   * neighbour table   nl[batch][position][4]   (uint16; 4 neighbours per 8-byte load; rebuilt in-kernel)
-//   * bond items        ell[warp-slot][batch][lane][4] (uint32 partner | type<<16; 4 items per 16-byte load)
-//   * bond candidates   same layout, rewritten by the first force evaluation after every rebuild
-// They live in global memory and are streamed through L1/L2.  Rows are padded with self-references
-// (r = 0, no force) so that the inner loops carry no bounds tests.
+// (K slots per thread) of a host-chosen ordering in which the 32 atoms of a warp-slot own similar
+// numbers of bonds.  Velocities and forces of a thread's atoms live in registers; shared memory holds
+// what other threads read: the positions (float4 x,y,z,radius), the coordinates of the last neighbour
+// build, the cell grid of that build and one 16-byte "inbox" of bond flags per atom.  Every
+// floating-point sum is taken in a fixed order (no floating-point atomics): runs are bit-reproducible.
+//
+// The kernel is bound by instruction issue, so the force loops are organised around the COMMON case:
+// in a population that is close to satisfying its restraints most pair candidates do not overlap and
+// most bonds are not violated.  Every loop therefore first does the cheap part for four candidates
+// (gather the partner position, squared distance, one comparison: ~11 instructions per candidate) and
+// enters the expensive part (rsqrt / sin, force, accumulation) only when one of the four is active.
+//
+// Pairs (pair_style soft, lammps.py:189,216-219): neighbour table nl[batch][position][4] (uint16; 4
+// neighbours per 8-byte load), all beads within cutoff + skin, rebuilt in-kernel through a cell grid in
+// shared memory when some bead has moved half the skin.  Rows are written 8 bytes at a time.
+//
+// Bonds (harmonic_upper_bound / harmonic_lower_bound) are evaluated ONCE per bond: the host orients every
+// bond -- one end OWNS it (walks it in its sliced-ELL row, ell[warp-slot][batch][lane][4], one 16-byte load
+// per 4 items), the other end RECEIVES it through slot q < 15 of its inbox.  When the owner finds the
+// restraint violated it adds the force to its own accumulator, writes (dx, dy, dz, f/r) to the mailbox
+// gf[position*16 + q] in global memory and sets flag byte q of the receiver's inbox.  After one barrier every
+// atom reads its 16 flag bytes with one LDS.128, collects the flagged mailboxes in slot order (a
+// deterministic sum) and clears the inbox.  The receiving side thus costs a few instructions per ATOM and
+// evaluation instead of a full evaluation per bond.  Bonds that do not fit an inbox (more than 15 received)
+// are listed at both ends as before (SYM items).  Items of the most frequent bond type (an upper bound: all
+// polymer and Hi-C restraints of a uniform-radius genome) sit in block A of a warp-slot and run a loop
+// specialised for that type; everything else is in block B.  A bound that is inactive with a margin of one
+// skin cannot switch on before the next rebuild, so the first evaluation after a rebuild walks the full
+// lists and writes the candidates to `eact`, which the following evaluations walk.
 #pragma once
+#include <type_traits>
 #include "mstep.cuh"
 
 namespace igmk {
+
+#define MOVES(k) ((meta[k] & 3u) == IGMK_KIND_BEAD || (meta[k] & 3u) == IGMK_KIND_CENTROID)
 
 #ifndef MD2_THREADS
 #define MD2_THREADS 1024
@@ -25,22 +46,30 @@ constexpr int MD2_NW = MD2_T / 32;    // warps per CTA
 constexpr int MD2_KMAX = 8;           // slots per thread supported (n_atoms <= 8192 on the 1-CTA path)
 constexpr int MD2_NLW0 = 256;         // initial neighbour-table width (columns)
 constexpr uint16_t MD2_NONE = 0xffffu;
+constexpr int MD2_INBOX = 16;         // flag bytes per atom; slot 15 is never used (padding items point at it)
+// bond item of k_md2: bits 0-3 inbox slot q, 4-16 partner position, 17 SYM (listed at both ends, no inbox), 18-31 type
+constexpr uint32_t MD2_IT_ADDR = 0x1ffffu, MD2_IT_POS = 0x1fff0u, MD2_IT_SYM = 0x20000u;
+constexpr int MD2_IT_TSHIFT = 18;
+constexpr int MD2_MAX_TYPES = 1 << 14;
 
 struct Md2View {
     const uint16_t* perm;      // [sum np] position -> original atom (0xffff: empty position)
-    const int32_t*  ell_off;   // per structure: 32*K+1 offsets (in items) of each warp-slot block
+    const int32_t*  ell_off;   // k_md_big: per structure 32*K+1 offsets (in items) of each warp-slot block
     const uint32_t* ell_items; // sliced-ELL bond items
-    uint32_t*       ell_act;   // same size: the items that can be active before the next rebuild (k_md2 scratch)
-    uint16_t*       nl;        // [sum np * nl_width] column-major per structure
+    uint32_t*       ell_act;   // same size: the items that can be active before the next rebuild (kernel scratch)
+    uint16_t*       nl;        // neighbour table [sum np * nl_width], column-major per structure
     int32_t         nl_width;
-    long long*      prof;      // optional [n_struct][8] SM cycles (IGMK_PROF=1): force loops, rebuild search, rebuilds,
-                               // number of rebuilds, then cycles of annealing stages 0..3
+    long long*      prof;      // optional [n_struct][16] SM cycles of thread 0 (IGMK_PROF=1)
+    // k_md2 only
+    const int4*     eblk;      // per structure K*32 entries {offset A, batches A, offset B, batches B} (offsets in items)
+    float4*         gf;        // bond mailboxes [sum np * 16]
+    double*         dbg_forces;// debug: [atoms*3] forces of the run-setup evaluation of stage MdParams.debug_stage
 };
 
 struct Md2Desc {               // per structure
     int64_t ell_item_off;
     int32_t perm_off;          // offset into perm (== sum of np of the structures before)
-    int32_t ell_desc_off;      // offset into ell_off
+    int32_t ell_desc_off;      // offset into ell_off (k_md_big) / eblk (k_md2)
     int32_t K;
     int32_t pad;
 };
@@ -50,7 +79,7 @@ struct Md2Desc {               // per structure
 __device__ __forceinline__ float fast_rsqrt(float v) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
 __device__ __forceinline__ float fast_rcp(float v) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
 __device__ __forceinline__ float fast_sin(float v) { float r; asm("sin.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
-// shared-memory load through an explicit 32-bit shared address (keeps the address arithmetic to one shift-add)
+// shared-memory load through an explicit 32-bit shared address (keeps the address arithmetic to one op)
 __device__ __forceinline__ float4 lds_f4(uint32_t addr)
 {
     float4 v;
@@ -61,18 +90,47 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr)
 __host__ __device__ inline size_t md2_smem_bytes(int K)
 {
     const size_t np = (size_t)K * MD2_T;
-    size_t b = np * 16;                       // x
-    b += np * 16;                             // positions in cell order (neighbour search)
+    size_t b = (np + 1) * 16;                 // x + one sentinel position far away (padding of the neighbour rows)
+    b += np * 16;                             // positions in cell order (neighbour search) / bond inboxes (between rebuilds)
     b += np * 12;                             // build coordinates
-    b += ((size_t)MAX_CELLS + 1) * 4;         // cell_start
-    b += np * 2 * 2;                          // cell_atoms, cell_of
+    b += ((size_t)MAX_CELLS + 4) * 4;         // cell_start (+1 entry, padded to 16 bytes)
+    b += np * 2 * 2;                          // cell_atoms, cell_of (= row lengths between rebuilds)
     b += 2 * 32 * 8 * 4;                      // reduction scratch
     b += IGMK_MAX_ENVELOPES * 4 * 4;          // envelope parameters
-    b += (size_t)K * MD2_NW * 4;              // active bond batches per warp-slot
+    b += (size_t)K * MD2_NW * 16;             // bond block descriptors
+    b += (size_t)K * MD2_NW * 8;              // candidate batches per warp-slot (A, B)
     return (b + 255) / 256 * 256;
 }
 
-template <int K>
+// Neighbour row of one atom, written 4 entries (one 8-byte store) at a time: the table is [batch][position][4] uint16, so
+// the 8-byte stores of neighbouring positions share sectors -- 2-byte stores, one sector each, saturate the L2 instead.
+struct Md2Row {
+    uint2* base; size_t stride; uint32_t lo, hi; int cnt, cap;
+    __device__ __forceinline__ Md2Row(uint16_t* table, int p, int np, int width)
+        : base((uint2*)table + p), stride((size_t)np), lo(0u), hi(0u), cnt(0), cap(width) {}
+    __device__ __forceinline__ void add(uint32_t v)
+    {
+        const int slot = cnt & 3;
+        const uint32_t sv = v << ((slot & 1) << 4);
+        if (slot < 2) lo |= sv; else hi |= sv;
+        if (slot == 3) {
+            if (cnt < cap) base[(size_t)(cnt >> 2) * stride] = make_uint2(lo, hi);
+            lo = 0u; hi = 0u;
+        }
+        cnt++;
+    }
+    // pad the last batch with `self` (an index that never interacts); -> entries kept, *ovf set when the row did not fit
+    __device__ __forceinline__ int finish(uint32_t self, int* ovf)
+    {
+        const int n = cnt;
+        while (cnt & 3) add(self);
+        if (n > cap) { *ovf = 1; return cap; }
+        return n;
+    }
+};
+
+// PROF: per-phase clock64 counters (IGMK_PROF=1); a separate instantiation, because the counters cost ~14 registers
+template <int K, bool PROF = false>
 __global__ void __launch_bounds__(MD2_T, 1)
 k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
 {
@@ -84,58 +142,56 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     const int n = d->n_atoms;
 
     float4* x = (float4*)smem;
-    float4* xsort = x + np;
+    float4* xsort = x + np + 1;               // rebuild only (x[np] is the far-away sentinel the neighbour rows are padded with)
+    uint4* inbox = (uint4*)xsort;             // [np] 16 flag bytes per atom, between rebuilds
     float* xbx = (float*)(xsort + np); float* xby = xbx + np; float* xbz = xby + np;
     uint32_t* cell_start = (uint32_t*)(xbz + np);
-    uint16_t* cell_atoms = (uint16_t*)(cell_start + MAX_CELLS + 1);
-    uint16_t* cell_of = cell_atoms + np;
+    uint16_t* cell_atoms = (uint16_t*)(cell_start + MAX_CELLS + 4);
+    uint16_t* cell_of = cell_atoms + np;      // during a rebuild: cell of a position; afterwards: its row length
     float* rbuf = (float*)(cell_of + np);
     float* envp = rbuf + 2 * 256;
-    int* bact = (int*)(envp + IGMK_MAX_ENVELOPES * 4);      // [K][32] batches of candidate bond items per warp-slot
+    int4* eblk = (int4*)(envp + IGMK_MAX_ENVELOPES * 4);    // [K*32]
+    int2* bact = (int2*)(eblk + K * MD2_NW);                 // [K*32] candidate batches (A, B)
+    unsigned char* flagb = (unsigned char*)inbox;
     int rb_par = 0;
 
     const igmk_protocol_t& pr = P.prot;
     const uint16_t* perm = V.perm + md.perm_off;
     uint32_t* eact = V.ell_act + md.ell_item_off;
-    const int32_t* eoff = V.ell_off + md.ell_desc_off;
     const uint32_t* eitems = V.ell_items + md.ell_item_off;
     uint16_t* nl = V.nl + (size_t)md.perm_off * V.nl_width;
     const int nlw = V.nl_width;
+    float4* gf = V.gf + (size_t)md.perm_off * MD2_INBOX;
     const float2* btype = B.btype_f + d->btype_off;
     float4* xg = B.xyzr + d->atom_off;
 
     // ---- per-slot state in registers ----
-    int   kind[K];            // IGMK_KIND_*, 3 = empty position
-    uint32_t emask[K];
-    int   ncnt[K];            // neighbours in my row
-    int   boff[K], bcols[K];  // my warp-slot's block of bond items
+    uint32_t meta[K];         // bits 0-1: IGMK_KIND_*, 3 = empty position; bits 8-15: envelope membership mask
     float vx[K], vy[K], vz[K], fx[K], fy[K], fz[K];
 #pragma unroll
     for (int k = 0; k < K; k++) {
         const int p = k * MD2_T + tid;
         const uint16_t a = perm[p];
         float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-        kind[k] = 3; emask[k] = 0;
+        meta[k] = 3u;
         if (a != MD2_NONE) {
             q = xg[a];
-            kind[k] = B.kind[d->atom_off + a];
-            emask[k] = B.envmask[d->atom_off + a];
+            meta[k] = (uint32_t)B.kind[d->atom_off + a] | (B.envmask[d->atom_off + a] << 8);
         }
         x[p] = q;
-        const int g = k * MD2_NW + warp;
-        boff[k] = eoff[g];
-        bcols[k] = (eoff[g + 1] - eoff[g]) >> 5;
-        vx[k] = vy[k] = vz[k] = 0.f; fx[k] = fy[k] = fz[k] = 0.f; ncnt[k] = 0;
+        vx[k] = vy[k] = vz[k] = 0.f; fx[k] = fy[k] = fz[k] = 0.f;
     }
-    // the two most frequent bond types stay in registers (the host orders the type table by use)
-    const float2 bt0 = btype[0], bt1 = btype[1];
+    if (tid < K * MD2_NW) { eblk[tid] = V.eblk[md.ell_desc_off + tid]; bact[tid] = make_int2(0, 0); }
+    if (tid == 0) x[np] = make_float4(1e18f, 1e18f, 1e18f, 0.f);
+    const float2 bt0 = btype[0];       // block A's type: the most frequent one (the host orders the table by use)
     const float skin = d->maxrad * P.skin_factor;
     const float lim = 0.25f * skin * skin;
     const float bond_pref2 = 2.f * (float)pr.bond_prefactor;
     float ev_c = -1.f;                 // evfactor * stage scale / pi  (force prefactor / rc), < 0: no sterics
     int n_rebuild = 0, overflow = 0;
     bool bond_build = true;
-    long long t_search = 0;
+    long long t_search = 0, t_recv = 0, t_bondA = 0, t_pair = 0, t_force = 0, t_build = 0;
+    auto tick = [&]() -> long long { return PROF ? clock64() : 0ll; };
     __syncthreads();
 
     // ------------------------------------------------------------------------------------
@@ -157,15 +213,16 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     };
 
     const uint32_t xs = (uint32_t)__cvta_generic_to_shared(x);
-    // ---- neighbour table: cell binning in shared memory, every thread fills its own rows ----
+
+    // ---- neighbour table: cell binning in shared memory, cutoff + skin; resets the bond inboxes ----
     auto rebuild = [&]() {
+        const long long tb0 = tick();
         float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
 #pragma unroll
         for (int k = 0; k < K; k++) {
             const int p = k * MD2_T + tid;
             const float4 q = x[p];
-            xbx[p] = q.x; xby[p] = q.y; xbz[p] = q.z;
-            if (kind[k] == IGMK_KIND_BEAD) {
+            if ((meta[k] & 3u) == IGMK_KIND_BEAD) {
                 lo[0] = fminf(lo[0], q.x); hi[0] = fmaxf(hi[0], q.x);
                 lo[1] = fminf(lo[1], q.y); hi[1] = fmaxf(hi[1], q.y);
                 lo[2] = fminf(lo[2], q.z); hi[2] = fmaxf(hi[2], q.z);
@@ -184,7 +241,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         for (int c = 0; c < 3; c++) {
             lo[c] = warp_min(lane < MD2_NW ? rb[lane * 6 + c] : 1e30f); hi[c] = warp_max(lane < MD2_NW ? rb[lane * 6 + 3 + c] : -1e30f);
         }
-        const float rlist = 2.f * d->maxrad + skin;
+        const float rlist = 2.f * d->maxrad + skin, rlist2 = rlist * rlist;
         int dim[3]; float inv[3];
 #pragma unroll
         for (int c = 0; c < 3; c++) {
@@ -202,7 +259,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         for (int k = 0; k < K; k++) {
             const int p = k * MD2_T + tid;
             int c = MD2_NONE;
-            if (kind[k] == IGMK_KIND_BEAD) {
+            if ((meta[k] & 3u) == IGMK_KIND_BEAD) {
                 const float4 q = x[p];
                 int cx = (int)((q.x - lo[0]) * inv[0]), cy = (int)((q.y - lo[1]) * inv[1]), cz = (int)((q.z - lo[2]) * inv[2]);
                 cx = min(max(cx, 0), dim[0] - 1); cy = min(max(cy, 0), dim[1] - 1); cz = min(max(cz, 0), dim[2] - 1);
@@ -230,10 +287,9 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             for (int c = c0; c < c1; c++) { const int cnt = cell_start[c + 1]; run += cnt; cell_start[c + 1] = run; }
         }
         __syncthreads();
-        // scatter with a per-cell cursor kept in cell_of's upper half?  no: reuse the counts trick --
         // drop atoms unordered behind the cell start, then sort each (tiny) cell by index so that the
         // row order, and with it the floating-point summation order, is independent of the race.
-        uint32_t* cursor = (uint32_t*)xbx;          // aliases the build x, which is re-written below
+        uint32_t* cursor = (uint32_t*)xbx;          // aliases the build coordinates, which are rewritten below
         for (int c = tid; c < ncell; c += MD2_T) cursor[c] = 0;
         __syncthreads();
 #pragma unroll
@@ -256,16 +312,19 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         }
         __syncthreads();
 #pragma unroll
-        for (int k = 0; k < K; k++) xbx[k * MD2_T + tid] = x[k * MD2_T + tid].x;
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2_T + tid;
+            const float4 q = x[p];
+            xbx[p] = q.x; xby[p] = q.y; xbz[p] = q.z;
+        }
         // positions in cell order: the search below walks them contiguously
-        const long long ts0 = clock64();
+        const long long ts0 = tick();
         const int nbead = cell_start[ncell];
         for (int s0 = tid; s0 < nbead; s0 += MD2_T) xsort[s0] = x[cell_atoms[s0]];
         __syncthreads();
-        // neighbour search.  Thread t takes the t-th bead IN CELL ORDER (not one of its own atoms), so the
-        // lanes of a warp sit in the same or adjacent cells, scan nearly the same ranges (little divergence,
-        // broadcast shared-memory reads) and need no index indirection until a candidate is accepted.
-        // Row layout: nl[batch][position][4] -- the force loop fetches 4 neighbours with one 8-byte load.
+        // Thread t takes the t-th bead IN CELL ORDER (not one of its own atoms), so the lanes of a warp sit in
+        // the same or adjacent cells, scan nearly the same ranges (little divergence, broadcast shared-memory
+        // reads) and need no index indirection until a candidate is accepted.
         int ovf = 0;
         for (int s0 = tid; s0 < nbead; s0 += MD2_T) {
             const int p = cell_atoms[s0];
@@ -273,8 +332,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             const int c = cell_of[p];
             const int cx = c % dim[0], cy = (c / dim[0]) % dim[1], cz = c / (dim[0] * dim[1]);
             const int ax0 = max(cx - 1, 0), ax1 = min(cx + 1, dim[0] - 1);
-            uint16_t* row = nl + ((size_t)p << 2);
-            int cnt = 0;
+            Md2Row row(nl, p, np, nlw);
             for (int dz = -1; dz <= 1; dz++) {
                 const int az = cz + dz;
                 if (az < 0 || az >= dim[2]) continue;
@@ -284,57 +342,150 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                     const int cb = (az * dim[1] + ay) * dim[0];
                     const int b = cell_start[cb + ax0], e = cell_start[cb + ax1 + 1];   // 3 cells, contiguous
                     for (int s1 = b; s1 < e; s1 += 4) {
-                        bool hit[4];
+                        uint32_t hits = 0u;
 #pragma unroll
                         for (int u = 0; u < 4; u++) {
-                            const int s2 = min(s1 + u, e - 1);
+                            const int s2 = s1 + u;                      // may run past e: still inside this CTA's shared memory, masked below
                             const float4 pj = xsort[s2];
                             const float ddx = q.x - pj.x, ddy = q.y - pj.y, ddz = q.z - pj.z;
-                            const float rl = q.w + pj.w + skin;
-                            hit[u] = (s1 + u < e) && (s2 != s0) && (ddx * ddx + ddy * ddy + ddz * ddz < rl * rl);
+                            // list radius of the largest beads: a superset of cutoff + skin of this pair when radii differ
+                            const bool hit = (s2 < e) && (s2 != s0) && (ddx * ddx + ddy * ddy + ddz * ddz < rlist2);
+                            hits |= hit ? (1u << u) : 0u;
                         }
-#pragma unroll
-                        for (int u = 0; u < 4; u++) {
-                            if (hit[u]) {
-                                if (cnt < nlw) row[(((size_t)(cnt >> 2) * np) << 2) + (cnt & 3)] = cell_atoms[s1 + u];
-                                cnt++;
-                            }
+                        while (hits) {                       // ~15 % of the tests hit
+                            const int u = __ffs(hits) - 1; hits &= hits - 1;
+                            row.add(cell_atoms[s1 + u]);
                         }
                     }
                 }
             }
-            if (cnt > nlw) { ovf = 1; cnt = nlw; }
-            for (int cc = cnt; cc & 3; cc++) row[(((size_t)(cc >> 2) * np) << 2) + (cc & 3)] = (uint16_t)p;   // self padding
-            cell_of[p] = (uint16_t)cnt;            // hand the row length to the atom's owner
+            cell_of[p] = (uint16_t)row.finish((uint32_t)np, &ovf);  // padded with the sentinel; the row length stays here until the next rebuild
         }
         __syncthreads();
+        // the cell-ordered copy is dead: its memory becomes the bond inboxes (all flags clear); dummies / empty positions: no row
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const uint16_t c = cell_of[k * MD2_T + tid];
-            ncnt[k] = c == MD2_NONE ? 0 : (int)c;
+            const int p = k * MD2_T + tid;
+            inbox[p] = make_uint4(0u, 0u, 0u, 0u);
+            if (cell_of[p] == MD2_NONE) cell_of[p] = 0;
         }
         overflow |= __syncthreads_or(ovf);
-        t_search += clock64() - ts0;
-        bond_build = true;        // the next force evaluation also refreshes the bond candidate list
+        if (PROF) { t_search += tick() - ts0; t_build += tick() - tb0; }
+        bond_build = true;        // the next force evaluation also refreshes the bond candidate lists
         n_rebuild++;
     };
 
-    // ---- forces on my atoms (gather) -------------------------------------------------------
-    // Rows of the neighbour table are padded with the atom's own index to a multiple of 4 and the bond
-    // blocks with self-bonds of type 0: a self pair has r2 = 0 and contributes nothing, so the inner
-    // loops need no bounds or validity tests and run branch-free.
-    auto forces = [&]() {
+    // ---- forces on my atoms ---------------------------------------------------------------
+    // Rows of the neighbour table are padded to a multiple of 4 with the index of a sentinel position far away and
+    // the bond blocks with items to oneself (r2 = 0, never beyond an upper bound): the loops need no bounds tests.
+    // BUILD: first evaluation after a rebuild -- walk the full bond lists and write the candidate lists.
+    auto forces = [&](auto build_tag) {
+        constexpr bool BUILD = decltype(build_tag)::value;
 #pragma unroll
         for (int k = 0; k < K; k++) {
             const int p = k * MD2_T + tid;
             const float4 pi = x[p];
             float ax = 0.f, ay = 0.f, az = 0.f;
-            // pair_style soft: F = A pi/rc sin(pi r/rc) r_hat, A = rc^2 ev/pi^2  =>  F/r = ev_c rc sin(pi r/rc) / r
+            const long long tp1 = tick();
+            // harmonic upper / lower bounds I own: F = -2 pref k (r - r0) r_hat when violated
+            const int g = k * MD2_NW + warp;
+            const int4 eb = eblk[g];
+            const int2 ba = bact[g];
+            {   // block A: every item is of type 0, an upper bound, and has an inbox slot at the other end
+                const uint4* it = (const uint4*)((BUILD ? eitems : eact) + eb.x) + lane;   // [batch][lane][4 items]
+                const int nb4 = BUILD ? eb.y : ba.x;
+                uint32_t* out = eact + eb.x + (lane << 2);
+                const float r0 = bt0.x, r02 = r0 * r0, kf = -bond_pref2 * bt0.y;
+                const float cl = fmaxf(r0 - skin, 0.f), cl2 = cl * cl;
+                int ccnt = 0;
+                uint4 nxt = nb4 > 0 ? it[0] : make_uint4(0, 0, 0, 0);
+                for (int c = 0; c < nb4; c++) {
+                    const uint4 cur = nxt;
+                    if (c + 1 < nb4) nxt = it[(c + 1) * 32];                  // next batch in flight while this one is used
+                    const uint32_t v[4] = {cur.x, cur.y, cur.z, cur.w};
+                    float4 pj[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) pj[u] = lds_f4(xs + (v[u] & MD2_IT_POS));
+                    float dx[4], dy[4], dz[4], r2[4];
+                    bool any = false;
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        dx[u] = pi.x - pj[u].x; dy[u] = pi.y - pj[u].y; dz[u] = pi.z - pj[u].z;
+                        r2[u] = dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u];
+                        any |= r2[u] > r02;                                  // a self item has r2 = 0
+                    }
+                    if (any) {                               // a restraint of the four is violated
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            if (r2[u] > r02) {
+                                const float fb = kf * (1.f - r0 * fast_rsqrt(r2[u]));
+                                ax += dx[u] * fb; ay += dy[u] * fb; az += dz[u] * fb;
+                                gf[v[u] & MD2_IT_ADDR] = make_float4(dx[u], dy[u], dz[u], fb);
+                                flagb[v[u] & MD2_IT_ADDR] = 1;
+                            }
+                        }
+                    }
+                    if (BUILD) {
+#pragma unroll
+                        for (int u = 0; u < 4; u++)
+                            if (r2[u] > cl2) { out[((ccnt >> 2) << 7) + (ccnt & 3)] = v[u]; ccnt++; }
+                    }
+                }
+                if (BUILD) {
+                    const int most = warp_max((ccnt + 3) >> 2);
+                    for (int cc = ccnt; cc < (most << 2); cc++) out[((cc >> 2) << 7) + (cc & 3)] = ((uint32_t)p << 4) | 15u;   // self item
+                    if (lane == 0) bact[g].x = most;
+                }
+            }
+            if (PROF) t_bondA += tick() - tp1;
+            if (eb.w > 0) {   // block B: any type, upper or lower bound; SYM items are evaluated at both ends
+                const uint4* it = (const uint4*)((BUILD ? eitems : eact) + eb.z) + lane;
+                const int nb4 = BUILD ? eb.w : ba.y;
+                uint32_t* out = eact + eb.z + (lane << 2);
+                int ccnt = 0;
+                for (int c = 0; c < nb4; c++) {
+                    const uint4 cur = it[c * 32];
+                    const uint32_t v[4] = {cur.x, cur.y, cur.z, cur.w};
+                    float4 pj[4];
+#pragma unroll
+                    for (int u = 0; u < 4; u++) pj[u] = lds_f4(xs + (v[u] & MD2_IT_POS));
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const float2 t = btype[v[u] >> MD2_IT_TSHIFT];     // (r0, k); k < 0: lower bound
+                        const float dx = pi.x - pj[u].x, dy = pi.y - pj[u].y, dz = pi.z - pj[u].z;
+                        const float r2 = dx * dx + dy * dy + dz * dz;
+                        const float r02 = t.x * t.x;
+                        if ((t.y > 0.f ? (r2 > r02) : (r2 < r02)) && r2 > 0.f) {
+                            const float fb = -bond_pref2 * fabsf(t.y) * (1.f - t.x * fast_rsqrt(r2));
+                            ax += dx * fb; ay += dy * fb; az += dz * fb;
+                            if (!(v[u] & MD2_IT_SYM)) {
+                                gf[v[u] & MD2_IT_ADDR] = make_float4(dx, dy, dz, fb);
+                                flagb[v[u] & MD2_IT_ADDR] = 1;
+                            }
+                        }
+                        if (BUILD) {
+                            const float lo = fmaxf(t.x - skin, 0.f), hi = t.x + skin;
+                            if (t.y > 0.f ? (r2 > lo * lo) : (r2 < hi * hi)) { out[((ccnt >> 2) << 7) + (ccnt & 3)] = v[u]; ccnt++; }
+                        }
+                    }
+                }
+                if (BUILD) {
+                    const int most = warp_max((ccnt + 3) >> 2);
+                    for (int cc = ccnt; cc < (most << 2); cc++) out[((cc >> 2) << 7) + (cc & 3)] = ((uint32_t)p << 4) | MD2_IT_SYM;   // self item
+                    if (lane == 0) bact[g].y = most;
+                }
+            }
+            const long long tp0 = tick();     // (the pair loop runs after the bond loops: the mailbox stores land meanwhile)
+            // pair_style soft: F = A pi/rc sin(pi r/rc) r_hat, A = rc^2 ev/pi^2  =>  F/r = ev_c rc sin(pi r/rc) / r.  Branch-free:
+            // at MD temperatures nearly every batch of four has an overlapping bead in some lane of the warp, so an early-out
+            // only adds divergence here (measured, profiles/r02g: +8 % instructions).
             if (ev_c >= 0.f) {
                 const uint2* col = (const uint2*)nl + p;
-                const int nb4 = (ncnt[k] + 3) >> 2;
+                const int nb4 = ((int)cell_of[p] + 3) >> 2;
+                uint2 wn = nb4 > 0 ? col[0] : make_uint2(0u, 0u);
                 for (int q = 0; q < nb4; q++) {
-                    const uint2 w = col[(size_t)q * np];
+                    const uint2 w = wn;
+                    if (q + 1 < nb4) wn = col[(size_t)(q + 1) * np];            // next batch in flight while this one is used
                     const uint32_t j[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
@@ -343,57 +494,16 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                         const float rc = pi.w + pj.w;
                         const float r2 = dx * dx + dy * dy + dz * dz;
                         const float rinv = fast_rsqrt(r2);
-                        const float s = fast_sin(3.14159265358979323846f * (r2 * rinv) * fast_rcp(rc));
-                        float fp = ev_c * rc * s * rinv;
-                        fp = (r2 < rc * rc && r2 > 0.f) ? fp : 0.f;
+                        const float sn = fast_sin(3.14159265358979323846f * (r2 * rinv) * fast_rcp(rc));
+                        float fp = ev_c * rc * sn * rinv;
+                        fp = (r2 < rc * rc && r2 > 0.f) ? fp : 0.f;               // (the padding sentinel is far away)
                         ax += dx * fp; ay += dy * fp; az += dz * fp;
                     }
                 }
             }
-            // harmonic upper / lower bounds: F = -2 pref k (r - r0) r_hat when violated
-            {
-                // Bond candidates.  No atom moves more than skin/2 before the next rebuild, so no pair distance
-                // changes by more than skin: an upper bound with r < r0 - skin (a lower bound with r > r0 + skin)
-                // stays inactive until then.  The first evaluation after a rebuild walks the full list and
-                // writes the candidates (original order kept) to `eact`; the others walk only those.  In a
-                // converged population most restraints are satisfied with room to spare.
-                const bool build = bond_build;
-                const uint4* it = (const uint4*)((build ? eitems : eact) + boff[k]) + lane;   // [batch][lane][4 items]
-                const int nb4 = build ? (bcols[k] >> 2) : bact[k * MD2_NW + warp];
-                uint32_t* out = eact + boff[k] + (lane << 2);
-                int ccnt = 0;
-                uint4 nxt = nb4 > 0 ? it[0] : make_uint4(0, 0, 0, 0);
-                for (int c = 0; c < nb4; c++) {
-                    const uint4 cur = nxt;
-                    if (c + 1 < nb4) nxt = it[(c + 1) * 32];                  // next batch in flight while this one is used
-                    const uint32_t v[4] = {cur.x, cur.y, cur.z, cur.w};
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const uint32_t ti = v[u] >> 16;
-                        float2 t = ti == 0 ? bt0 : bt1;                    // (r0, k); k < 0: lower bound
-                        if (ti > 1) t = btype[ti];
-                        const float4 pj = lds_f4(xs + ((v[u] & 0xffffu) << 4));
-                        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
-                        const float r2 = dx * dx + dy * dy + dz * dz;
-                        const float r02 = t.x * t.x;
-                        const bool act = (t.y > 0.f ? (r2 > r02) : (r2 < r02)) && r2 > 0.f;
-                        float fb = -bond_pref2 * fabsf(t.y) * (1.f - t.x * fast_rsqrt(r2));
-                        fb = act ? fb : 0.f;
-                        ax += dx * fb; ay += dy * fb; az += dz * fb;
-                        if (build) {
-                            const float lo = fmaxf(t.x - skin, 0.f), hi = t.x + skin;
-                            if (t.y > 0.f ? (r2 > lo * lo) : (r2 < hi * hi)) { out[((ccnt >> 2) << 7) + (ccnt & 3)] = v[u]; ccnt++; }
-                        }
-                    }
-                }
-                if (build) {
-                    const int most = warp_max((ccnt + 3) >> 2);
-                    for (int cc = ccnt; cc < (most << 2); cc++) out[((cc >> 2) << 7) + (cc & 3)] = (uint32_t)p;   // self-bond padding
-                    if (lane == 0) bact[k * MD2_NW + warp] = most;
-                }
-            }
+            if (PROF) t_pair += tick() - tp0;
             // fix ellipsoidalenvelope
-            uint32_t m = emask[k];
+            uint32_t m = meta[k] >> 8;
             while (m) {
                 const int e = __ffs(m) - 1; m &= m - 1;
                 const float ia = fast_rcp(envp[4 * e] - pi.w), ib = fast_rcp(envp[4 * e + 1] - pi.w),
@@ -401,27 +511,51 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 const float ux = pi.x * ia, uy = pi.y * ib, uz = pi.z * ic;
                 const float k2 = ux * ux + uy * uy + uz * uz;
                 const bool act = (kk > 0.f ? (k2 > 1.f) : (kk < 0.f && k2 < 1.f)) && k2 > 0.f;
-                const float g = act ? fabsf(kk) * (1.f - fast_rsqrt(k2)) : 0.f;
-                ax -= g * pi.x; ay -= g * pi.y; az -= g * pi.z;
+                if (act) {
+                    const float g2 = fabsf(kk) * (1.f - fast_rsqrt(k2));
+                    ax -= g2 * pi.x; ay -= g2 * pi.y; az -= g2 * pi.z;
+                }
             }
-            if (kind[k] != IGMK_KIND_BEAD && kind[k] != IGMK_KIND_CENTROID) { ax = 0.f; ay = 0.f; az = 0.f; }   // frozen / empty
             fx[k] = ax; fy[k] = ay; fz[k] = az;
         }
         bond_build = false;
+        const long long tr0 = tick();
+        __syncthreads();            // every inbox flag and mailbox of this evaluation is written
+        // bonds I receive: the owner's (dx, dy, dz, f/r) with the opposite sign, in inbox order; then clear the inbox
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2_T + tid;
+            const uint4 fl = inbox[p];
+            if (fl.x | fl.y | fl.z | fl.w) {
+                const uint32_t w[4] = {fl.x, fl.y, fl.z, fl.w};
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (w[u]) {                          // the (up to) four mailboxes of this word are fetched together: one L2 latency
+                        float4 f[4];
+#pragma unroll
+                        for (int b = 0; b < 4; b++) {
+                            f[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if ((w[u] >> (b << 3)) & 0xffu) f[b] = __ldcg(gf + ((size_t)p << 4) + (u << 2) + b);
+                        }
+#pragma unroll
+                        for (int b = 0; b < 4; b++) { fx[k] -= f[b].x * f[b].w; fy[k] -= f[b].y * f[b].w; fz[k] -= f[b].z * f[b].w; }
+                    }
+                }
+                inbox[p] = make_uint4(0u, 0u, 0u, 0u);
+            }
+            if (!MOVES(k)) { fx[k] = 0.f; fy[k] = 0.f; fz[k] = 0.f; }   // frozen / empty
+        }
+        if (PROF) t_recv += tick() - tr0;
     };
 
     // ------------------------------------------------------------------------------------
-    long long t_force = 0, t_integ = 0, t_build = 0;
-    const long long t_begin = clock64();
     rebuild();
-    t_build += clock64() - t_begin;
     const float dt = (float)pr.timestep, dtf = 0.5f * dt;
     const float dof = 3.f * (float)d->n_nonfixed - 3.f;
     float last_temp = 0.f;
+    int dbg_pass = 0;
 
-    long long t_stage[4] = {0, 0, 0, 0};
-    for (int st = 0; st < pr.n_stage; st++) {
-        const long long ts_stage = clock64();
+    for (int st = (P.debug_stage >= 0 ? P.debug_stage : 0); st < pr.n_stage; st++) {
         set_stage(pr.evfactor[st], pr.envfactor[st]);
         for (int sub = (pr.relax_mdsteps > 0 ? 0 : 1); sub < 2; sub++) {
             const int nsteps = sub == 0 ? pr.relax_mdsteps : pr.mdsteps[st];
@@ -437,7 +571,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
 #pragma unroll
                 for (int k = 0; k < K; k++) {
                     float a = 0.f, b = 0.f, c = 0.f;
-                    if (kind[k] == IGMK_KIND_BEAD || kind[k] == IGMK_KIND_CENTROID) {
+                    if (MOVES(k)) {
                         uint32_t r = ranpark_jump(seed, 3u * (uint32_t)perm[k * MD2_T + tid] + 1u);
                         const double AM = 1.0 / 2147483647.0;
                         a = (float)(AM * r - 0.5);
@@ -452,7 +586,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 float ke = 0.f;
 #pragma unroll
                 for (int k = 0; k < K; k++) {
-                    if (kind[k] == IGMK_KIND_BEAD || kind[k] == IGMK_KIND_CENTROID) {
+                    if (MOVES(k)) {
                         vx[k] -= s0 * inv; vy[k] -= s1 * inv; vz[k] -= s2 * inv;
                         ke += vx[k] * vx[k] + vy[k] * vy[k] + vz[k] * vz[k];
                     }
@@ -463,14 +597,26 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
 #pragma unroll
                 for (int k = 0; k < K; k++) { vx[k] *= fac; vy[k] *= fac; vz[k] *= fac; }
             }
-            // ---- run nsteps: velocity Verlet with the nve/limit speed cap + temp/rescale ----
-            forces();                                   // run setup
+            // ---- run nsteps: velocity Verlet with the nve/limit speed cap + temp/rescale; step 0 = run setup ----
             float scale = 1.f;
             for (int step = 0; step <= nsteps; step++) {
-                const long long tc0 = clock64();
+                const long long tc0 = tick();
+                if (bond_build) forces(std::true_type{}); else forces(std::false_type{});
+                if (PROF) t_force += tick() - tc0;
+                if (P.debug_stage >= 0) {       // forces of one run-setup evaluation, for the parity test of THIS force routine:
+                    if (dbg_pass++ == 0) { step = -1; __syncthreads(); continue; }   // once through the full bond lists, once through the candidates
+#pragma unroll
+                    for (int k = 0; k < K; k++) {
+                        const uint16_t a = perm[k * MD2_T + tid];
+                        if (a != MD2_NONE && V.dbg_forces) {
+                            double* o = V.dbg_forces + 3 * (size_t)(d->atom_off + a);
+                            o[0] = fx[k]; o[1] = fy[k]; o[2] = fz[k];
+                        }
+                    }
+                    if (tid == 0) B.flags[blockIdx.x] = overflow ? 1 : 0;
+                    return;
+                }
                 if (step > 0) {
-                    forces();
-                    t_force += clock64() - tc0;
                     float ke = 0.f;
 #pragma unroll
                     for (int k = 0; k < K; k++) {       // second half kick (frozen/empty: f = v = 0)
@@ -480,14 +626,12 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                         vx[k] = a; vy[k] = b; vz[k] = c;
                         ke += a * a + b * b + c * c;
                     }
-                    ke = block_sum1(ke);                // its barrier also ends every read of x for this step
+                    ke = block_sum1(ke);
                     const float tcur = dof > 0.f ? ke / dof : 0.f;
                     const float ttar = t0 + ((float)step / (float)nsteps) * (t1 - t0);
                     scale = 1.f;
                     if (tcur > 0.f && fabsf(tcur - ttar) > 0.1f) scale = sqrtf(ttar / tcur);
                     last_temp = tcur * scale * scale;
-                } else {
-                    __syncthreads();
                 }
                 if (step == nsteps) {
 #pragma unroll
@@ -497,7 +641,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 int need = 0;
 #pragma unroll
                 for (int k = 0; k < K; k++) {           // rescale + first half kick + drift
-                    if (kind[k] == IGMK_KIND_BEAD || kind[k] == IGMK_KIND_CENTROID) {
+                    if (MOVES(k)) {
                         const int p = k * MD2_T + tid;
                         float a = vx[k] * scale + dtf * fx[k], b = vy[k] * scale + dtf * fy[k], c = vz[k] * scale + dtf * fz[k];
                         const float vsq = a * a + b * b + c * c;
@@ -510,13 +654,9 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                         need |= (ddx * ddx + ddy * ddy + ddz * ddz > lim);
                     }
                 }
-                const bool stale = __syncthreads_or(need);
-                const long long tc1 = clock64();
-                if (stale) { rebuild(); t_build += clock64() - tc1; }
-                t_integ += tc1 - tc0;
+                if (__syncthreads_or(need)) rebuild();
             }
         }
-        if (st < 4) t_stage[st] = clock64() - ts_stage;
     }
     // results: coordinates back in the original atom order (float32 like Particle.pos)
     int bad = 0;
@@ -536,12 +676,14 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         r->temperature = dof_all > 0 ? (double)last_temp * (double)dof / dof_all : 0.0;
         r->n_rebuilds = n_rebuild;
         B.flags[blockIdx.x] = (overflow ? 1 : 0) | (bad ? 2 : 0);
-        if (V.prof) {
-            long long* o = V.prof + 8 * (size_t)blockIdx.x;
+        if (PROF && V.prof) {
+            long long* o = V.prof + 16 * (size_t)blockIdx.x;
             o[0] = t_force; o[1] = t_search; o[2] = t_build; o[3] = n_rebuild;
-            for (int k = 0; k < 4; k++) o[4 + k] = t_stage[k];
+            o[4] = t_recv; o[5] = t_pair; o[6] = t_bondA;
         }
     }
 }
+
+#undef MOVES
 
 }  // namespace igmk

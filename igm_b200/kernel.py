@@ -86,13 +86,15 @@ class MStepBatch(object):
         return slot.value
 
     def submit_population(self, template, crd, n_bead, row, col, row_r0, row_k, bits, s_begin=0, n_struct=None, seeds=None,
-                          bits_word0=0):
+                          bits_word0=0, extras=None):
         """Submit structures ``s_begin .. s_begin+n_struct-1`` of the .hss-layout slab ``crd``
         ([n_bead][S][3] float32): every structure = ``template`` (a PackedSystem: shared particles and
         restraints) with the slab's coordinates and a HarmonicUpperBound per actdist row whose bit is set
         in ``bits`` (the matrix Population.assign returned for exactly these structures; ``bits_word0`` =
         word of every row that holds the bit of structure ``s_begin``, for a matrix that covers more
-        structures than this call submits).  -> first slot."""
+        structures than this call submits).  ``extras``: a PopulationExtras with the restraints that differ by
+        structure beyond the Hi-C rows (FISH bonds, DamID envelope members); it covers the same structures as
+        ``crd`` (global indices).  -> first slot."""
         crd = np.ascontiguousarray(crd, dtype=np.float32)
         S = crd.shape[1]
         if n_struct is None:
@@ -105,11 +107,13 @@ class MStepBatch(object):
             raise ValueError("bit matrix does not cover structures %d..%d from word %d" % (s_begin, s_begin + n_struct, bits_word0))
         sd = None if seeds is None else np.ascontiguousarray(seeds, dtype=np.int64)
         first = C.c_int32(-1)
-        _abi.check(self._lib.igmk_submit_population(
+        ex = None if extras is None else extras.c_view(s_begin, n_struct)
+        _abi.check(self._lib.igmk_submit_population_ex(
             self._h, C.byref(template.c), int(n_bead), int(S), int(s_begin), int(n_struct), crd.ctypes.data_as(_abi.c_f32p),
             r.size, r.ctypes.data_as(_abi.c_i32p), c.ctypes.data_as(_abi.c_i32p), r0.ctypes.data_as(_abi.c_f64p), float(row_k),
             C.cast(b.ctypes.data + 4 * int(bits_word0), _abi.c_u32p), int(b.shape[1]),
             None if sd is None else sd.ctypes.data_as(_abi.c_i64p),
+            None if ex is None else C.byref(ex[0]),
             C.byref(first)), "igmk_submit_population")
         self._packed.extend([template] * n_struct)        # sizes for fetch(); bond arrays differ per structure
         return first.value
@@ -126,6 +130,11 @@ class MStepBatch(object):
     def single_point(self, ev_scale=1.0, env_scale=1.0, bond_prefactor=1.0, f32=False):
         fn = self._lib.igmk_single_point_f32 if f32 else self._lib.igmk_single_point
         _abi.check(fn(self._h, float(ev_scale), float(env_scale), float(bond_prefactor)), "igmk_single_point")
+
+    def md_forces(self, protocol, stage=0):
+        """forces of the MD kernel's own (float32) force routine at the submitted coordinates, run setup of `stage`;
+        read them with fetch_forces"""
+        _abi.check(self._lib.igmk_md_forces(self._h, C.byref(protocol), int(stage)), "igmk_md_forces")
 
     def layout_stats(self):
         """-> (slots per thread K, bond items, items after sliced-ELL padding, host seconds of the layout build)"""
@@ -179,6 +188,67 @@ class MStepBatch(object):
         return f
 
 
+class PopulationExtras(object):
+    """Restraints of a population that differ from structure to structure beyond the assigned Hi-C rows
+    (igmk_pop_extras_t): per-structure bonds in CSR form and envelope groups whose members are given by a bit
+    matrix over the structures.
+
+    bonds: (off i8 [S+1], i i4, j i4, k f8, r0 f8, style u1) or None -- structure s owns entries off[s]..off[s+1];
+    envelopes: list of (abck (a, b, c, k), bead ids i4 [n_rows], bits u4 [n_rows][ceil(S/32)]) -- bit s of row r set
+    means bead ids[r] belongs to the group in structure s (the matrix Population.damid_assign returns)."""
+
+    def __init__(self, n_struct, bonds=None, envelopes=()):
+        self.n_struct = int(n_struct)
+        if bonds is not None:
+            off, bi, bj, bk, br0, bs = bonds
+            self.bond_off = np.ascontiguousarray(off, dtype=np.int64)
+            self.bond_i = np.ascontiguousarray(bi, dtype=np.int32)
+            self.bond_j = np.ascontiguousarray(bj, dtype=np.int32)
+            self.bond_k = np.ascontiguousarray(bk, dtype=np.float64)
+            self.bond_r0 = np.ascontiguousarray(br0, dtype=np.float64)
+            self.bond_style = np.ascontiguousarray(bs, dtype=np.uint8)
+            if self.bond_off.size != self.n_struct + 1 or not (self.bond_i.size == self.bond_j.size == self.bond_k.size ==
+                                                                 self.bond_r0.size == self.bond_style.size == int(self.bond_off[-1])):
+                raise ValueError("per-structure bond arrays are inconsistent")
+        else:
+            self.bond_off = None
+        nw = (self.n_struct + 31) // 32
+        self.env_abck = np.ascontiguousarray([e[0] for e in envelopes], dtype=np.float64).reshape(-1, 4)
+        beads = [np.ascontiguousarray(e[1], dtype=np.int32).ravel() for e in envelopes]
+        bits = [np.ascontiguousarray(e[2], dtype=np.uint32).reshape(b.size, nw) for e, b in zip(envelopes, beads)]
+        self.env_row_off = np.concatenate([[0], np.cumsum([b.size for b in beads])]).astype(np.int64)
+        self.env_bead = np.concatenate(beads) if beads else np.zeros(0, dtype=np.int32)
+        self.env_bits = np.concatenate(bits) if bits else np.zeros((0, nw), dtype=np.uint32)
+        self._nw = nw
+
+    def c_view(self, s_begin, n_struct):
+        """-> (PopExtras, keep-alive list) for structures s_begin .. s_begin+n_struct-1 (s_begin a multiple of 32
+        when there are envelope bits)"""
+        if s_begin < 0 or s_begin + n_struct > self.n_struct:
+            raise ValueError("structure range outside the extras")
+        ex = _abi.PopExtras()
+        keep = []
+        if self.bond_off is not None:
+            off = np.ascontiguousarray(self.bond_off[s_begin:s_begin + n_struct + 1])       # absolute offsets into the full arrays
+            keep.append(off)
+            ex.bond_off = off.ctypes.data_as(_abi.c_i64p)
+            ex.bond_i = self.bond_i.ctypes.data_as(_abi.c_i32p)
+            ex.bond_j = self.bond_j.ctypes.data_as(_abi.c_i32p)
+            ex.bond_k = self.bond_k.ctypes.data_as(_abi.c_f64p)
+            ex.bond_r0 = self.bond_r0.ctypes.data_as(_abi.c_f64p)
+            ex.bond_style = self.bond_style.ctypes.data_as(_abi.c_u8p)
+        ex.n_env = int(self.env_abck.shape[0])
+        if ex.n_env:
+            if s_begin % 32:
+                raise ValueError("with per-structure envelopes a chunk must start at a multiple of 32 structures")
+            ex.env_abck = self.env_abck.ctypes.data_as(_abi.c_f64p)
+            ex.env_row_off = self.env_row_off.ctypes.data_as(_abi.c_i64p)
+            ex.env_bead = self.env_bead.ctypes.data_as(_abi.c_i32p)
+            ex.env_bits = C.cast(self.env_bits.ctypes.data + 4 * (s_begin // 32), _abi.c_u32p)
+            ex.env_bits_words = self._nw
+        return ex, keep
+
+
 def info_from_result(res):
     """igmk_result_t -> the dict get_info_from_log builds (lammps_io.py:6-37)."""
     thermo = {"Temp": res.temperature, "E_pair": res.pair_energy, "E_bond": res.bond_energy}
@@ -214,7 +284,7 @@ PIPELINE_CHUNK = 128     # structures per launch sequence of run_population: a m
 
 
 def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protocol, device=0, seeds=None,
-                   chunk=PIPELINE_CHUNK, violations_tol=None):
+                   chunk=PIPELINE_CHUNK, violations_tol=None, extras=None):
     """M-step of a whole assigned population, host buffers in, host buffers out: the population-wide
     form of ``ModelingStep.task`` (igm/steps/ModelingStep.py:184-264 build, :266 optimize, :341-382 results).
 
@@ -256,7 +326,7 @@ def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protoco
             hi = min(S, lo + chunk)
             batches.append((MStepBatch(device), lo, hi))
             batches[-1][0].submit_population(template, crd, n_bead, row, col, row_r0, row_k, bits, s_begin=lo, n_struct=hi - lo,
-                                             seeds=None if seeds is None else seeds[lo:hi], bits_word0=lo // 32)
+                                             seeds=None if seeds is None else seeds[lo:hi], bits_word0=lo // 32, extras=extras)
             w = threading.Thread(target=finish, args=batches[-1])
             w.start()
             workers.append(w)

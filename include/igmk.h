@@ -153,6 +153,37 @@ int igmk_submit_population(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t 
                            int64_t n_rows, const int32_t* row, const int32_t* col, const double* row_r0,
                            double row_k, const uint32_t* bits, int32_t bits_words, const int64_t* seeds,
                            int32_t* first_slot_out);
+/*
+ * The same with restraints that differ from structure to structure beyond the Hi-C rows -- what ModelingStep.task adds
+ * after inter/intraHiC (igm/steps/ModelingStep.py:268-330).  All pointers are host pointers; index k of the
+ * per-structure arrays is structure s_begin + k.
+ *   bonds: structure k gets bond_i/j/k/r0/style[bond_off[k] .. bond_off[k+1]) appended after its Hi-C bonds, atom
+ *     indices in the template's numbering (FISH: lower / upper bounds to the restraint's static centre particle or
+ *     between the selected copies, with that structure's own target distances, igm/restraints/fish.py:93-274);
+ *   envelopes: n_env groups appended after the template's; group e has the parameters env_abck[e] and, in structure
+ *     k, the members env_bead[r] of its rows r = env_row_off[e] .. env_row_off[e+1] whose bit k is set in
+ *     env_bits[r][env_bits_words] (the matrix igmk_pop_damid_assign returns; DamID: EllipticEnvelope(affected
+ *     particles of THIS structure, semiaxes * (1 - contact_range), -k), igm/restraints/damid.py:116-142).
+ */
+typedef struct igmk_pop_extras {
+    const int64_t*  bond_off;       /* [n_struct + 1] or NULL: no extra bonds */
+    const int32_t*  bond_i;
+    const int32_t*  bond_j;
+    const double*   bond_k;
+    const double*   bond_r0;
+    const uint8_t*  bond_style;     /* IGMK_BOND_* */
+    int32_t         n_env;
+    const double*   env_abck;       /* [n_env][4] */
+    const int64_t*  env_row_off;    /* [n_env + 1] */
+    const int32_t*  env_bead;
+    const uint32_t* env_bits;
+    int32_t         env_bits_words;
+} igmk_pop_extras_t;
+int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t n_bead,
+                              int32_t n_struct_total, int32_t s_begin, int32_t n_struct, const float* crd,
+                              int64_t n_rows, const int32_t* row, const int32_t* col, const double* row_r0,
+                              double row_k, const uint32_t* bits, int32_t bits_words, const int64_t* seeds,
+                              const igmk_pop_extras_t* extras /* or NULL */, int32_t* first_slot_out);
 /* builds the MD kernel's host-side layout (atom order + sliced-ELL bond blocks) for what is submitted and reports
  * it: slots per thread, bond items (both ends), items after padding, seconds the build took (any pointer may be NULL) */
 int igmk_layout_stats(igmk_handle_t* h, int32_t* slots_per_thread, int64_t* bond_items, int64_t* ell_items,
@@ -172,9 +203,16 @@ int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot);
  * semi-axes by env_scale. */
 int igmk_single_point(igmk_handle_t* h, double ev_scale, double env_scale,
                       double bond_prefactor);
-/* same single point through the float32 force routine the MD loop uses */
+/* same single point in float32 through the team-per-atom routine of mstep.cuh (the arithmetic of the double-precision
+ * path at MD precision; NOT the force loop of the MD kernel -- that one is igmk_md_forces) */
 int igmk_single_point_f32(igmk_handle_t* h, double ev_scale, double env_scale,
                           double bond_prefactor);
+/* Forces exactly as the annealing-MD kernel computes them (its float32 arithmetic, neighbour tables, oriented bond
+ * lists and hardware approximations): the run-setup evaluation of annealing stage `stage` of `prot` (pair prefactor
+ * and envelope scaled as lammps.py:287-303 does for that stage), no time step taken; read them with
+ * igmk_fetch_forces.  What a `run 0` with the dump's fx fy fz columns is in the reference (lammps.py:253-256).
+ * Structures of at most 8192 atoms (the shared-memory MD path). */
+int igmk_md_forces(igmk_handle_t* h, const igmk_protocol_t* prot, int32_t stage);
 int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out /* [n_atoms][3] */,
                igmk_result_t* res);
 /* every structure of the batch at once, back into the .hss-layout slab crd [n_bead][n_struct_total][3] at

@@ -62,8 +62,63 @@ def test_single_point_stage_scales_and_prefactor(ff_golden):
         _check(b, slot, ps, f_ref, e_ref, 1e-10)
 
 
+MD_FORCE_RTOL = 2e-4   # float32 sums of ~30 terms + MUFU rsqrt / sin / rcp approximations (~1e-6 each), relative to max |F|
+
+
+@pytest.mark.parametrize("stage", [0, 3])
+def test_md_kernel_force_routine_matches_oracle(ff_golden, stage):
+    """The force loop k_md2 itself runs (oriented bond lists, inboxes, two-level neighbour tables, float32, hardware
+    approximations) against the double-precision oracle: 3008 beads, every term on, the stage's pair / envelope
+    scales.  Evaluated through the full bond lists and again through the candidate lists."""
+    from helpers import short_protocol
+    prot = short_protocol()
+    systems = [demo_structure(ff_golden, k) for k in (0, 3, 6, 8)]
+    ev, env = prot.evfactor[stage], prot.envfactor[stage]
+    with MStepBatch(0) as b:
+        slots = [b.submit(ps) for ps in systems]
+        b.md_forces(prot, stage)
+        for ps, slot in zip(systems, slots):
+            f_ref, _ = ff.single_point(ps, ev, env, 1.0)
+            f = b.fetch_forces(slot)
+            scale = np.abs(f_ref).max()
+            assert np.abs(f - f_ref).max() <= MD_FORCE_RTOL * scale, np.abs(f - f_ref).max() / scale
+            # per atom: relative to that atom's own force where it is not tiny
+            big = np.linalg.norm(f_ref, axis=1) > 1e-3 * scale
+            rel = np.linalg.norm(f - f_ref, axis=1)[big] / np.linalg.norm(f_ref, axis=1)[big]
+            assert rel.max() <= 2e-3, rel.max()
+
+
+def test_md_kernel_force_routine_small_and_hub_systems():
+    """more bonds on one atom than an inbox holds (SYM items at both ends), lower bounds as the most frequent type,
+    a structure without bonds"""
+    from helpers import short_protocol
+    prot = short_protocol()
+    g, rad, sys_ = small_system(seed=4, n_struct=2, n_hic=300)
+    n = len(g)
+    rng = np.random.default_rng(9)
+    ps0 = sys_[0]
+    # hub: atom 3 bonded to everyone, twice; mostly lower bounds of one type
+    hi = np.concatenate([np.full(2 * (n - 1), 3), rng.integers(0, n, 200)]).astype(np.int32)
+    hj = np.concatenate([np.delete(np.arange(n), 3)] * 2 + [rng.integers(0, n, 200)]).astype(np.int32)
+    keep = hi != hj
+    hi, hj = hi[keep], hj[keep]
+    from igm_b200._abi import PackedSystem, BOND_LOWER
+    hub = PackedSystem(ps0.xyz, ps0.radius, ps0.kind, hi, hj, np.full(hi.size, 0.7), np.full(hi.size, 3.0 * float(rad[0])),
+                       np.full(hi.size, BOND_LOWER, dtype=np.uint8), ps0.env_abck, ps0.env_off, ps0.env_members, 1.0, seed=3)
+    bare = synth.pack_structure(sys_[1].xyz[:n], rad, g, nucleus_radius=1400.0)       # polymer bonds only
+    systems = [sys_[0], sys_[1], hub, bare]
+    with MStepBatch(0) as b:
+        slots = [b.submit(ps) for ps in systems]
+        b.md_forces(prot, 1)
+        for ps, slot in zip(systems, slots):
+            f_ref, _ = ff.single_point(ps, prot.evfactor[1], prot.envfactor[1], 1.0)
+            f = b.fetch_forces(slot)
+            scale = np.abs(f_ref).max()
+            assert np.abs(f - f_ref).max() <= MD_FORCE_RTOL * scale, np.abs(f - f_ref).max() / scale
+
+
 def test_single_point_f32_md_force_routine(ff_golden):
-    """the float32 routine the MD loop uses: same terms, float32 round-off only"""
+    """the team-per-atom routine of mstep.cuh in float32: same terms, float32 round-off only"""
     systems = [demo_structure(ff_golden, k) for k in (0, 3, 6)]
     with MStepBatch(0) as b:
         slots = [b.submit(ps) for ps in systems]
