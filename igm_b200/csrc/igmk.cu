@@ -257,6 +257,10 @@ extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* sl
         if (i < 0 || i >= n || j < 0 || j >= n) return fail("igmk_submit: bond index out of range");
         if (s->bond_style[b] > 1) return fail("igmk_submit: unknown bond style");
         if (!(s->bond_k[b] >= 0.0)) return fail("igmk_submit: bond spring constants must be >= 0");
+        if (!(s->bond_r0[b] >= 0.0)) {      // the kernels compare squared distances; a negative bound (FISH target < tolerance, fish.py:193) has no meaning for them
+            snprintf(msg, sizeof msg, "igmk_submit: bond %d of structure %lld has a negative bound distance %g", b, (long long)s->struct_id, s->bond_r0[b]);
+            return fail(msg);
+        }
         cnt[i + 1]++; cnt[j + 1]++;
     }
     for (int i = 0; i < n; i++) cnt[i + 1] += cnt[i];

@@ -17,7 +17,7 @@ import time
 
 import numpy as np
 
-from . import _abi, parallel
+from . import _abi, parallel, restraints_pop
 from .astep import Population
 from .kernel import info_from_result, run_population
 
@@ -63,6 +63,122 @@ def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, 
     out["timings"].update({"mstep_s": time.perf_counter() - t0 - t_astep, "md_kernel_ms": md_ms, "cg_kernel_ms": cg_ms,
                            "h2d_bytes": h2d, "total_s": time.perf_counter() - t0})
     return out
+
+
+def assemble_restraints(crd_local, genome, radii, hic=None, damid=None, fish=None, device=0):
+    """The A-steps of one iteration for this rank's structures: everything ``ModelingStep.task`` later reads from the
+    actdist / assignment files, as arrays.
+
+    hic:   dict(pairs=(pair_i, pair_j, pwish, plast), contact_range=2.0)                     ActivationDistanceStep
+    damid: dict(loci, pwish, plast, contact_range=0.05, shape="sphere"|"ellipsoid", nucleus_param=R | (a, b, c))
+                                                                                             DamidActivationDistanceStep
+    fish:  dict(rtype, tol, center, probes=, radial_min=, radial_max=, pairs=, pair_min=, pair_max=) with the SORTED
+           experimental distributions [n_items][S_total] of the input file (FishAssignmentStep.py:220-252); `center` =
+           atom index of the restraint's static centre particle in the template                FishAssignmentStep
+    -> dict(hic_rows (row, col, dist, prob), hic_bits, damid_rows (bead, dist, prob), damid_bits, damid_semiaxes,
+            fish_targets {name: f8 [n][S_local]}, fish_bonds (CSR of this rank's structures), seconds)"""
+    import torch
+    rank, ws = parallel.world()
+    t0 = time.perf_counter()
+    crd_local = np.ascontiguousarray(crd_local, dtype=np.float32)
+    S = crd_local.shape[1]
+    dev = "cuda:%d" % device
+    local_t = torch.from_numpy(crd_local).to(dev)
+    slab_t = parallel.all_gather_slab(local_t)
+    s0 = rank * S                                  # this rank's block in the gathered slab (equal blocks)
+    out = {}
+    with Population(slab_t.shape[1], radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popg:
+        popg.attach(slab_t)
+        if hic is not None:
+            pi, pj, pw, pl = hic["pairs"]
+            cr = hic.get("contact_range", 2.0)
+            out["hic_rows"] = parallel.distributed_actdist(lambda a, b, c, d: popg.actdist(a, b, c, d, cr), pi, pj, pw, pl,
+                                                           genome.chrom, genome.copy_off, device=dev)
+        if damid is not None:                      # a few thousand loci at most: every rank computes all of them
+            out["damid_rows"] = popg.damid_actdist(damid["loci"], damid["pwish"], damid["plast"], damid.get("contact_range", 0.05),
+                                                   damid.get("shape", "sphere"), damid["nucleus_param"])
+        if fish is not None:
+            tg = {}
+            if fish.get("probes") is not None and len(fish["probes"]):
+                _, _, rmin, rmax = popg.fish_ranks(fish["probes"])
+                if "radial_min" in fish:
+                    tg["radial_min"] = restraints_pop.fish_targets(rmin, fish["radial_min"])[:, s0:s0 + S]
+                if "radial_max" in fish:
+                    tg["radial_max"] = restraints_pop.fish_targets(rmax, fish["radial_max"])[:, s0:s0 + S]
+            if fish.get("pairs") is not None and len(fish["pairs"]):
+                pr = np.asarray(fish["pairs"])
+                _, _, pmin, pmax = popg.fish_ranks(pr[:, 0], pr[:, 1])
+                if "pair_min" in fish:
+                    tg["pair_min"] = restraints_pop.fish_targets(pmin, fish["pair_min"])[:, s0:s0 + S]
+                if "pair_max" in fish:
+                    tg["pair_max"] = restraints_pop.fish_targets(pmax, fish["pair_max"])[:, s0:s0 + S]
+            out["fish_targets"] = tg
+    with Population(S, radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popl:
+        popl.attach(local_t)
+        if hic is not None:
+            row, col, dist, _ = out["hic_rows"]
+            out["hic_bits"] = popl.assign(row, col, dist)
+        if damid is not None:
+            bead, dist, _ = out["damid_rows"]
+            param = np.atleast_1d(np.asarray(damid["nucleus_param"], dtype=np.float64))
+            semi = np.repeat(param, 3) if param.size == 1 else param          # Damid.__init__: a = b = c = R for a sphere (damid.py:96-99)
+            out["damid_semiaxes"] = semi
+            out["damid_bits"] = popl.damid_assign(bead, dist, damid.get("contact_range", 0.05), semi)
+    if fish is not None:
+        tg = out["fish_targets"]
+        out["fish_bonds"] = restraints_pop.fish_bonds(
+            crd_local, genome.copy_off, genome.copy_beads, int(fish["center"]), fish["rtype"], float(fish["tol"]), float(fish.get("k", 1.0)),
+            probes=fish.get("probes"), radial_min=tg.get("radial_min"), radial_max=tg.get("radial_max"),
+            pairs=fish.get("pairs"), pair_min=tg.get("pair_min"), pair_max=tg.get("pair_max"))
+    out["seconds"] = time.perf_counter() - t0
+    return out
+
+
+def population_inputs(asm, radii, n_struct, hic=None, damid=None):
+    """assemble_restraints output -> the arguments of ``kernel.run_population`` / ``MStepBatch.submit_population``:
+    (row, col, row_r0, row_k, bits, extras)."""
+    if hic is not None:
+        row, col, _, _ = asm["hic_rows"]
+        cr = hic.get("contact_range", 2.0)
+        r0 = (cr * (radii[row] + radii[col])).astype(np.float64)             # float32 product like inter_hic.py:55
+        bits, k_hic = asm["hic_bits"], float(hic.get("k", 1.0))
+    else:
+        row = col = np.zeros(0, dtype=np.int32)
+        r0, bits, k_hic = np.zeros(0), np.zeros((0, 1), dtype=np.uint32), 1.0
+    envs = []
+    if damid is not None:
+        envs.append(restraints_pop.damid_envelope(asm["damid_rows"][0], asm["damid_bits"], asm["damid_semiaxes"],
+                                                  damid.get("contact_range", 0.05), damid.get("k", 1.0)))
+    extras = None
+    if envs or "fish_bonds" in asm:
+        extras = restraints_pop.extras(n_struct, bonds=asm.get("fish_bonds"), envelopes=envs)
+    return row, col, r0, k_hic, bits, extras
+
+
+def am_iteration(crd_local, genome, radii, template, optimizer_options, hic=None, damid=None, fish=None, device=0, seeds=None,
+                 bond_prefactor=1.0, violations=False, tol=0.05):
+    """One A/M iteration with any of the Hi-C, DamID and FISH restraints (bin/igm-run:99-131 for the restraint set of
+    igm-config_all.json): the A-steps of ``assemble_restraints``, then the M-step of the whole block of structures with
+    the per-structure restraints ModelingStep.task would add (ModelingStep.py:249-330).  `template`: PackedSystem of the
+    shared particles (beads, the Envelope / Damid / Fish centre dummies) and restraints (Steric, Envelope, Polymer).
+    -> dict(coordinates, infos, restraints (the assemble_restraints dict), timings, violations)."""
+    rank, _ = parallel.world()
+    t0 = time.perf_counter()
+    crd_local = np.ascontiguousarray(crd_local, dtype=np.float32)
+    n_bead, S = crd_local.shape[0], crd_local.shape[1]
+    asm = assemble_restraints(crd_local, genome, radii, hic=hic, damid=damid, fish=fish, device=device)
+    row, col, r0, k_hic, bits, extras = population_inputs(asm, radii, S, hic=hic, damid=damid)
+    protocol = _abi.make_protocol(optimizer_options, bond_prefactor=bond_prefactor)
+    new, results, viol, tim = run_population(template, crd_local, n_bead, row, col, r0, k_hic, bits, protocol, device=device,
+                                             seeds=seeds, violations_tol=tol if violations else None, extras=extras)
+    infos = []
+    for k, res in enumerate(results):
+        if res.status != 0 or not np.isfinite(res.final_energy):
+            raise RuntimeError("b200 kernel produced non-finite coordinates or energy (structure %d of rank %d)" % (k, rank))
+        infos.append(info_from_result(res))
+    total = time.perf_counter() - t0
+    return {"coordinates": new, "infos": infos, "restraints": asm, "violations": viol,
+            "timings": dict(tim, astep_s=asm["seconds"], mstep_s=total - asm["seconds"], total_s=total)}
 
 
 def relax_init(crd_local, template, optimizer_options, device=0, seeds=None, bond_prefactor=1.0):

@@ -144,14 +144,16 @@ def hic_pairs(genome, sigma, seed=7, intra_scale=0.9, intra_exp=1.08, inter_frac
 
 def pack_structure(xyz, radii, genome, hic_i=None, hic_j=None, hic_r0=None, nucleus_radius=5500.0,
                    semiaxes=None, contact_range=2.0, evfactor=1.0, k_poly=1.0, k_hic=1.0, k_env=1.0,
-                   seed=1, struct_id=0, extra_envelopes=()):
+                   seed=1, struct_id=0, extra_envelopes=(), n_extra_dummies=0):
     """One structure the way ModelingStep.task assembles it (igm/steps/ModelingStep.py:184-264):
     beads, Steric, Envelope (adds its DUMMY_STATIC centre particle, envelope.py:39), Polymer and
-    the assigned Hi-C HarmonicUpperBounds."""
+    the assigned Hi-C HarmonicUpperBounds.  n_extra_dummies: further DUMMY_STATIC particles at the origin,
+    the centres the Damid and Fish restraints add (damid.py:120, fish.py:119), atoms n+1, n+2, ..."""
     n = len(genome)
-    xyz_all = np.vstack([xyz.astype(np.float32), np.zeros((1, 3), dtype=np.float32)])
-    rad_all = np.concatenate([radii.astype(np.float32), np.zeros(1, dtype=np.float32)])
-    kind = np.concatenate([np.full(n, KIND_BEAD, dtype=np.uint8), np.array([KIND_STATIC], dtype=np.uint8)])
+    nd = 1 + int(n_extra_dummies)
+    xyz_all = np.vstack([xyz.astype(np.float32), np.zeros((nd, 3), dtype=np.float32)])
+    rad_all = np.concatenate([radii.astype(np.float32), np.zeros(nd, dtype=np.float32)])
+    kind = np.concatenate([np.full(n, KIND_BEAD, dtype=np.uint8), np.full(nd, KIND_STATIC, dtype=np.uint8)])
     bi, bj, r0 = polymer_bonds(genome, radii, contact_range)
     bk = np.full(bi.size, k_poly, dtype=np.float64)
     if hic_i is not None and len(hic_i):

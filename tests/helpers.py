@@ -76,3 +76,39 @@ def short_protocol(md=200, relax=50, **kw):
         p.mdsteps[k] = md
     p.relax_mdsteps = relax
     return p
+
+
+def population_stats(systems, coords, tol=0.05):
+    """Per-structure statistics of a population, evaluated by the SAME code (numpy + the C oracle) whichever arm produced
+    the coordinates: log10(1 + E_total), log10(1 + E_bond), E_pair per bead, number of violated bonds (ratio > tol,
+    forces.py:128-136, :176-184), radius of gyration.  -> dict name -> float64 [S]"""
+    from oracle import ff
+    out = {k: [] for k in ("log_e_total", "log_e_bond", "e_pair_per_bead", "n_violated", "rg")}
+    for ps, xyz in zip(systems, coords):
+        q = PackedSystem(xyz, ps.radius, ps.kind, ps.bond_i, ps.bond_j, ps.bond_k, ps.bond_r0, ps.bond_style,
+                         ps.env_abck, ps.env_off, ps.env_members, ps.evfactor, seed=ps.seed, struct_id=ps.struct_id)
+        _, e = ff.single_point(q)
+        nb = int((ps.kind == KIND_BEAD).sum())
+        d = np.linalg.norm(xyz[ps.bond_i].astype(np.float64) - xyz[ps.bond_j].astype(np.float64), axis=1)
+        viol = np.where(ps.bond_style == BOND_UPPER, d - ps.bond_r0, ps.bond_r0 - d)
+        ratio = np.where(ps.bond_r0 > 0, np.maximum(0.0, viol) / np.where(ps.bond_r0 > 0, ps.bond_r0, 1.0), 0.0)
+        x = xyz[:nb].astype(np.float64)
+        out["log_e_total"].append(np.log10(1.0 + e["total"]))
+        out["log_e_bond"].append(np.log10(1.0 + e["bond"]))
+        out["e_pair_per_bead"].append(e["pair"] / nb)
+        out["n_violated"].append(float(np.count_nonzero(ratio > tol)))
+        out["rg"].append(float(np.sqrt(((x - x.mean(axis=0)) ** 2).sum(axis=1).mean())))
+    return {k: np.array(v, dtype=np.float64) for k, v in out.items()}
+
+
+def assert_population_stats_match(a, b, nsig=4.5, floors=None):
+    """Criterion 3 of north_star as a test: two populations (dicts of population_stats) agree when every statistic's
+    means differ by less than nsig standard errors of the difference, sqrt(var_a / S_a + var_b / S_b) -- plus an
+    absolute floor per statistic for quantities whose spread is ~0 (all structures satisfied)."""
+    floors = floors or {}
+    for k in a:
+        ma, mb = a[k].mean(), b[k].mean()
+        se = np.sqrt(a[k].var(ddof=1) / a[k].size + b[k].var(ddof=1) / b[k].size)
+        lim = nsig * se + floors.get(k, 0.0)
+        assert abs(ma - mb) <= lim, "%s: means %.5g vs %.5g differ by %.3g > %.3g (%.1f standard errors)" % (
+            k, ma, mb, abs(ma - mb), lim, abs(ma - mb) / max(se, 1e-300))
