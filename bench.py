@@ -235,6 +235,19 @@ def build_workload(args, rank, world, device, log):
         astep["actdist_bytes"] = float(12.0 * S_tot * (n_copies[pi[sl]] + n_copies[pj[sl]]).sum() + 32.0 * pi[sl].size)
     rows = parallel.all_gather_rows(rows, device="cuda:%d" % device)      # rank order == global pair order
     row, col, dst, prb = rows
+    # the structure-sharded variant (configs[4]: nobody holds the whole slab; per-pair counts and radix histograms are
+    # all-reduced over NCCL): timed on the same pairs, and its rows must equal the gathered ones bit for bit
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop:
+        pop.attach(local)
+        torch.cuda.synchronize(device)
+        t1 = time.perf_counter()
+        rows_sh = parallel.sharded_actdist(pop, S_tot, pi, pj, pw, pl, 2.0)
+        astep["sharded_e2e_ms"] = (time.perf_counter() - t1) * 1e3
+        astep["sharded_kernel_ms"] = parallel.sharded_actdist.last_kernel_ms
+        astep["sharded_identical"] = bool(all(np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a,
+                                                             b.view(np.uint32) if b.dtype == np.float32 else b)
+                                              for a, b in zip(rows_sh, rows)))
+    del rows_sh
     with Population(S, rad, g.chrom, g.copy_off, g.copy_beads, device=device) as pop:
         pop.attach(local)
         kt, et = [], []
@@ -653,7 +666,11 @@ def main():
                       "structures": S * world,
                       "value": a["pairs_total"] / (ad_k * 1e-3), "e2e": a["pairs_total"] / (ad_e * 1e-3), "unit": "pairs/s",
                       "actdist_kernel_ms": ad_k, "actdist_e2e_ms": ad_e, "assign_kernel_ms": as_k, "assign_e2e_ms": as_e,
-                      "assign_rows_x_structures_per_s": a["rows"] * float(S) / (as_k * 1e-3)},
+                      "assign_rows_x_structures_per_s": a["rows"] * float(S) / (as_k * 1e-3),
+                      "structure_sharded": {"what": "configs[4] variant: the population stays sharded by structure, per-pair contact "
+                                                    "counts and four radix-256 histograms are all-reduced (NCCL) instead of gathering the slab",
+                                            "e2e_ms": a["sharded_e2e_ms"], "kernel_ms_this_rank": a["sharded_kernel_ms"],
+                                            "rows_bit_identical_to_gathered": a["sharded_identical"]}},
             "roofline_astep": {"bound": "hbm", "kernel": "k_actdist", "achieved": ad_gbs, "peak": hbm, "unit": "GB/s",
                                "frac": ad_gbs / hbm, "l2_resident": l2_resident, "slab_mb": slab_mb,
                                "note": ("the %.0f MB coordinate slab stays in the 126 MB L2 at this size: `achieved` is algorithmic bytes "

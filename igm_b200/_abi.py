@@ -222,6 +222,10 @@ _SIGNATURES = {
     "igmk_pop_set_pairs": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f64p, c_f64p]),
     "igmk_pop_actdist_launch": (C.c_int, [_vp, C.c_double]),
     "igmk_pop_actdist_collect": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p, c_f32p, c_i64p]),
+    "igmk_pop_shard_count": (C.c_int, [_vp, C.c_double, _vp]),
+    "igmk_pop_shard_rank": (C.c_int, [_vp, C.c_int32, _vp, _vp, _vp]),
+    "igmk_pop_shard_hist": (C.c_int, [_vp, C.c_int32, _vp, _vp]),
+    "igmk_pop_shard_pick": (C.c_int, [_vp, C.c_int32, _vp, _vp, _vp]),
     "igmk_pop_contact_freq": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, C.c_double, c_f32p]),
     "igmk_pop_damid_actdist": (C.c_int, [_vp, C.c_int64, c_i32p, c_f64p, c_f64p, C.c_double, C.c_int32, c_f64p,
                                          C.c_int64, c_i32p, c_f32p, c_f32p, c_i64p]),

@@ -38,6 +38,7 @@ class Population(object):
         self.copy_beads = np.ascontiguousarray(copy_beads, dtype=np.int32)
         self.n_bead = int(self.radii.size)
         self.n_struct = int(n_struct)
+        self.device = int(device)
         self.n_hap = int(self.copy_off.size - 1)
         self.max_copies = int(np.diff(self.copy_off).max())
         self._keep = None
@@ -135,6 +136,23 @@ class Population(object):
                                                    pj.ctypes.data_as(_abi.c_i32p), float(contact_range),
                                                    out.ctypes.data_as(_abi.c_f32p)), "igmk_pop_contact_freq")
         return out
+
+    # ---- activation distances with the population sharded by structure ------------------------
+    def shard_count(self, contact_range, d_counts):
+        """local contact count of every staged pair -> device buffer u32 [n_pairs] (its address: ``d_counts``)"""
+        _abi.check(self._lib.igmk_pop_shard_count(self._p, float(contact_range), C.c_void_p(int(d_counts))), "igmk_pop_shard_count")
+
+    def shard_rank(self, n_struct_total, d_counts_total, d_want, d_prefix):
+        _abi.check(self._lib.igmk_pop_shard_rank(self._p, int(n_struct_total), C.c_void_p(int(d_counts_total)),
+                                                 C.c_void_p(int(d_want)), C.c_void_p(int(d_prefix))), "igmk_pop_shard_rank")
+
+    def shard_hist(self, radix_pass, d_prefix, d_hist):
+        _abi.check(self._lib.igmk_pop_shard_hist(self._p, int(radix_pass), C.c_void_p(int(d_prefix)), C.c_void_p(int(d_hist))),
+                   "igmk_pop_shard_hist")
+
+    def shard_pick(self, radix_pass, d_hist_total, d_want, d_prefix):
+        _abi.check(self._lib.igmk_pop_shard_pick(self._p, int(radix_pass), C.c_void_p(int(d_hist_total)), C.c_void_p(int(d_want)),
+                                                 C.c_void_p(int(d_prefix))), "igmk_pop_shard_pick")
 
     # ---- contact assignment ---------------------------------------------------------------
     def set_rows(self, row, col, dist):

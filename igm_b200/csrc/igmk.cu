@@ -19,6 +19,7 @@
 #include "md2.cuh"
 #include "md_big.cuh"
 #include "astep.cuh"
+#include "astep_shard.cuh"
 #include "probe.cuh"
 
 using namespace igmk;
@@ -1507,6 +1508,82 @@ extern "C" int igmk_pop_actdist(igmk_pop_t* p, int64_t n_pairs, const int32_t* p
     if (int rc = igmk_pop_set_pairs(p, n_pairs, pair_i, pair_j, pwish, plast)) return rc;
     if (int rc = igmk_pop_actdist_launch(p, contact_range)) return rc;
     return igmk_pop_actdist_collect(p, max_rows, row, col, dist, prob, n_rows_out);
+}
+
+// ---- activation distances with the population sharded by structure (astep_shard.cuh) -----------------
+// The pairs are staged with igmk_pop_set_pairs on this rank's LOCAL population; the caller owns the device buffers
+// and all-reduces (sum) d_counts after _count and d_hist after every _hist over the ranks (NCCL).  Every call has
+// finished on the device when it returns.
+static int shard_ready(igmk_pop_t* p, const char* who, const void* a, const void* b)
+{
+    if (!p) return fail(std::string(who) + ": NULL handle");
+    if (p->n_pairs > 0 && (!a || !b)) return fail(std::string(who) + ": NULL device buffer");
+    return 0;
+}
+
+extern "C" int igmk_pop_shard_count(igmk_pop_t* p, double contact_range, void* d_counts)
+{
+    if (int rc = shard_ready(p, "igmk_pop_shard_count", d_counts, d_counts)) return rc;
+    p->actdist_done = false;
+    if (p->n_pairs == 0) return 0;
+    CU(cudaSetDevice(p->device));
+    const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * 8);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_shard_count<<<(int)grid, AD_THREADS, 0, p->stream>>>(p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, (float)contact_range, (uint32_t*)d_counts);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(p->ev1, p->stream));
+    CU(cudaEventSynchronize(p->ev1));
+    CU(cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1));
+    return 0;
+}
+
+extern "C" int igmk_pop_shard_rank(igmk_pop_t* p, int32_t n_struct_total, const void* d_counts_total, void* d_want, void* d_prefix)
+{
+    if (int rc = shard_ready(p, "igmk_pop_shard_rank", d_counts_total, d_want)) return rc;
+    if (n_struct_total < p->n_struct) return fail("igmk_pop_shard_rank: the whole population cannot be smaller than this rank's share");
+    if (p->n_pairs == 0) return 0;
+    if (!d_prefix) return fail("igmk_pop_shard_rank: NULL device buffer");
+    CU(cudaSetDevice(p->device));
+    k_shard_rank<<<(int)std::min<int64_t>((p->n_pairs + 255) / 256, (int64_t)p->sm_count * 8), 256, 0, p->stream>>>(
+        p->view(), p->n_pairs, n_struct_total, p->d_pi.p, p->d_pj.p, p->d_pw.p, p->d_pl.p, (const uint32_t*)d_counts_total,
+        (uint32_t*)d_want, (uint32_t*)d_prefix, p->d_prob.p, p->d_valid.p);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
+extern "C" int igmk_pop_shard_hist(igmk_pop_t* p, int32_t pass, const void* d_prefix, void* d_hist)
+{
+    if (int rc = shard_ready(p, "igmk_pop_shard_hist", d_prefix, d_hist)) return rc;
+    if (pass < 0 || pass > 3) return fail("igmk_pop_shard_hist: pass must be 0..3");
+    if (p->n_pairs == 0) return 0;
+    CU(cudaSetDevice(p->device));
+    const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * 8);
+    CU(cudaEventRecord(p->ev0, p->stream));
+    k_shard_hist<<<(int)grid, AD_THREADS, 0, p->stream>>>(p->view(), p->n_pairs, p->d_pi.p, p->d_pj.p, p->d_valid.p,
+                                                          (const uint32_t*)d_prefix, pass, (uint32_t*)d_hist);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(p->ev1, p->stream));
+    CU(cudaEventSynchronize(p->ev1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, p->ev0, p->ev1));
+    p->last_ms = pass == 0 ? ms : p->last_ms + ms;        // the four histogram passes add up
+    return 0;
+}
+
+extern "C" int igmk_pop_shard_pick(igmk_pop_t* p, int32_t pass, const void* d_hist_total, void* d_want, void* d_prefix)
+{
+    if (int rc = shard_ready(p, "igmk_pop_shard_pick", d_hist_total, d_want)) return rc;
+    if (pass < 0 || pass > 3) return fail("igmk_pop_shard_pick: pass must be 0..3");
+    if (p->n_pairs == 0) { p->actdist_done = pass == 3; return 0; }
+    if (!d_prefix) return fail("igmk_pop_shard_pick: NULL device buffer");
+    CU(cudaSetDevice(p->device));
+    k_shard_pick<<<(int)std::min<int64_t>((p->n_pairs + 7) / 8, (int64_t)p->sm_count * 8), 256, 0, p->stream>>>(
+        p->n_pairs, p->d_valid.p, (const uint32_t*)d_hist_total, pass, (uint32_t*)d_want, (uint32_t*)d_prefix, p->d_dist.p);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(p->stream));
+    if (pass == 3) p->actdist_done = true;                // igmk_pop_actdist_collect expands the pairs to rows
+    return 0;
 }
 
 extern "C" int igmk_pop_contact_freq(igmk_pop_t* p, int64_t n_pairs, const int32_t* pair_i, const int32_t* pair_j,

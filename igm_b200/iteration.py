@@ -23,10 +23,13 @@ from .kernel import info_from_result, run_population
 
 
 def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, device=0, contact_range=2.0,
-                  k_hic=1.0, seeds=None, bond_prefactor=1.0, violations=False, tol=0.05):
+                  k_hic=1.0, seeds=None, bond_prefactor=1.0, violations=False, tol=0.05, astep="gather"):
     """crd_local: float32 [n_bead][S_local][3] (host).  genome: object with chrom, copy_off, copy_beads.
     template: PackedSystem of the shared particles and restraints (Steric, Envelope, Polymer).
     pairs: (pair_i, pair_j, pwish, plast) haploid pairs kept at this sigma -- identical on every rank.
+    astep: "gather" = all-gather the coordinate slab, shard the pair list (every rank sees the whole population);
+           "reduce" = the population stays sharded by structure, per-pair counts and radix histograms are all-reduced
+           (``parallel.sharded_actdist``; BASELINE configs[4]).  Both give the same rows, bit for bit.
     -> dict(coordinates [n_bead][S_local][3], infos [S_local], rows (row, col, dist, prob), timings,
             violations = per-structure (n_imposed, n_violated) of the harmonic restraints if asked)."""
     import torch
@@ -35,15 +38,21 @@ def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, 
     t0 = time.perf_counter()
     dev = "cuda:%d" % device
     local_t = torch.from_numpy(np.ascontiguousarray(crd_local, dtype=np.float32)).to(dev)
-    slab_t = parallel.all_gather_slab(local_t)
     pi, pj, pw, pl = pairs
-    with Population(slab_t.shape[1], radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popg:
-        popg.attach(slab_t)
-        rows = parallel.distributed_actdist(lambda a, b, c, d: popg.actdist(a, b, c, d, contact_range), pi, pj, pw, pl,
-                                            genome.chrom, genome.copy_off, device=dev)
-    row, col, dist, prob = rows
+    if astep == "gather":
+        slab_t = parallel.all_gather_slab(local_t)
+        with Population(slab_t.shape[1], radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popg:
+            popg.attach(slab_t)
+            rows = parallel.distributed_actdist(lambda a, b, c, d: popg.actdist(a, b, c, d, contact_range), pi, pj, pw, pl,
+                                                genome.chrom, genome.copy_off, device=dev)
+        del slab_t
+    elif astep != "reduce":
+        raise ValueError("astep must be 'gather' or 'reduce'")
     with Population(S, radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popl:
         popl.attach(local_t)
+        if astep == "reduce":
+            rows = parallel.sharded_actdist(popl, parallel.total_structures(S, device=dev), pi, pj, pw, pl, contact_range)
+        row, col, dist, prob = rows
         bits = popl.assign(row, col, dist)
     t_astep = time.perf_counter() - t0
     r0 = (contact_range * (radii[row] + radii[col])).astype(np.float64)      # float32 product like inter_hic.py:55
@@ -84,8 +93,8 @@ def assemble_restraints(crd_local, genome, radii, hic=None, damid=None, fish=Non
     S = crd_local.shape[1]
     dev = "cuda:%d" % device
     local_t = torch.from_numpy(crd_local).to(dev)
-    slab_t = parallel.all_gather_slab(local_t)
-    s0 = rank * S                                  # this rank's block in the gathered slab (equal blocks)
+    slab_t, offs = parallel.all_gather_slab(local_t, return_offsets=True)
+    s0 = offs[rank]                                # this rank's block in the gathered slab
     out = {}
     with Population(slab_t.shape[1], radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as popg:
         popg.attach(slab_t)

@@ -320,6 +320,26 @@ int igmk_pop_actdist_collect(igmk_pop_t* p, int64_t max_rows, int32_t* row, int3
                              float* dist, float* prob, int64_t* n_rows_out);
 
 /*
+ * The same activation distances with the population SHARDED by structure over several GPUs (north_star: "NCCL ...
+ * reduces the per-pair distance histograms"; BASELINE configs[4]): every rank holds its own structures only.  The
+ * two population-wide numbers get_actdist needs per pair -- the contact count (:419) and the o-th smallest squared
+ * distance (:425, :446) -- are sums over structures:
+ *     igmk_pop_set_pairs (same pair list on every rank)
+ *     igmk_pop_shard_count -> d_counts [n_pairs] u32            | caller: all-reduce(sum) over the ranks
+ *     igmk_pop_shard_rank  (total counts -> probability, wanted rank o; clears d_prefix)
+ *     for pass = 0..3:  igmk_pop_shard_hist -> d_hist [n_pairs][256] u32   | caller: all-reduce(sum)
+ *                       igmk_pop_shard_pick (the radix digit holding rank o; pass 3 also stores the distance)
+ *     igmk_pop_actdist_collect (rows, identical on every rank and bit-identical to igmk_pop_actdist over the
+ *     whole population)
+ * d_* are DEVICE buffers owned by the caller (e.g. torch tensors handed to NCCL); each call has completed on the
+ * device when it returns.
+ */
+int igmk_pop_shard_count(igmk_pop_t* p, double contact_range, void* d_counts);
+int igmk_pop_shard_rank(igmk_pop_t* p, int32_t n_struct_total, const void* d_counts_total, void* d_want, void* d_prefix);
+int igmk_pop_shard_hist(igmk_pop_t* p, int32_t pass, const void* d_prefix, void* d_hist);
+int igmk_pop_shard_pick(igmk_pop_t* p, int32_t pass, const void* d_hist_total, void* d_want, void* d_prefix);
+
+/*
  * Contact frequency of haploid pairs in the resident population: the `pnow` of get_actdist
  * (ActivationDistanceStep.py:373,:419-422), count(d_sq <= (contact_range*(ri+rj))^2) over all copy
  * pairs and structures divided by their number, as float32.  freq: host, [n_pairs].

@@ -179,3 +179,60 @@ def test_c5_size_population_vs_oracle():
         assert _bits_equal(a, pop.actdist(pi, pj, pw, pl, 2.0)) and a[0].size > 300
     want = ao.actdist_rows(pi, pj, pw, pl, crd, rad, g.chrom, g.copy_index, 2.0)
     assert _bits_equal(a, want)
+
+
+@pytest.mark.parametrize("shards", [1, 2, 5])
+def test_structure_sharded_actdist_is_bit_identical(astep_golden, shards):
+    """BASELINE configs[4]: the population sharded by structure, per-pair counts and radix histograms summed over the
+    shards (NCCL all-reduce between ranks; here the shards sit on one GPU and their buffers are added) -- the rows must
+    equal the reference's own get_actdist output and the single-population kernel, whatever the split"""
+    from igm_b200 import parallel
+    g = astep_golden
+    crd = np.ascontiguousarray(g["coordinates"])
+    S = crd.shape[1]
+    cuts = np.linspace(0, S, shards + 1).astype(int)
+    if shards == 5:
+        cuts = np.array([0, 1, 34, 35, 80, S])           # uneven, incl. single-structure shards
+    pops = []
+    for k in range(shards):
+        pop = Population(int(cuts[k + 1] - cuts[k]), g["radii"], g["chrom"], g["copy_off"], g["copy_beads"])
+        pop.upload(np.ascontiguousarray(crd[:, cuts[k]:cuts[k + 1], :]))
+        pops.append(pop)
+    try:
+        for chunk in (1 << 17, 97):
+            rows = parallel.sharded_actdist(pops, S, g["pair_i"], g["pair_j"], g["pwish"], g["plast"], 2.0, pair_chunk=chunk)
+            assert np.array_equal(rows[0], g["row"]) and np.array_equal(rows[1], g["col"])
+            assert np.array_equal(rows[2].view(np.uint32), g["dist"].view(np.uint32))
+            assert np.array_equal(rows[3].view(np.uint32), g["prob"].view(np.uint32))
+    finally:
+        for pop in pops:
+            pop.close()
+
+
+def test_structure_sharded_actdist_large_population_vs_full_kernel():
+    from igm_b200 import parallel
+    g = synth.Genome([9, 7, 6], n_autosomes=2)
+    rad = synth.bead_radii(len(g), 1500.0, 0.3)
+    S = 2300
+    crd = synth.population_territories(g, S, R=1500.0, seed=4)
+    iu, ju = np.triu_indices(g.n_hap, 1)
+    rng = np.random.default_rng(2)
+    pw = rng.uniform(0, 1, iu.size) ** 3
+    pl = np.where(rng.random(iu.size) < 0.5, 0.0, rng.uniform(0, 1, iu.size) ** 2)
+    with Population(S, rad, g.chrom, g.copy_off, g.copy_beads) as full:
+        full.upload(crd)
+        want = full.actdist(iu, ju, pw, pl, 2.0)
+    cuts = [0, 700, 701, 1500, S]
+    pops = []
+    for k in range(4):
+        pop = Population(cuts[k + 1] - cuts[k], rad, g.chrom, g.copy_off, g.copy_beads)
+        pop.upload(np.ascontiguousarray(crd[:, cuts[k]:cuts[k + 1], :]))
+        pops.append(pop)
+    try:
+        got = parallel.sharded_actdist(pops, S, iu, ju, pw, pl, 2.0)
+        assert got[0].size > 50
+        for a, b in zip(got, want):
+            assert np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a, b.view(np.uint32) if b.dtype == np.float32 else b)
+    finally:
+        for pop in pops:
+            pop.close()

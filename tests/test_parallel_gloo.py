@@ -41,12 +41,13 @@ def _worker(rank, ws, port, out_dir):
     dist.init_process_group("gloo", rank=rank, world_size=ws)
     g = synth.Genome([9, 7, 6, 4, 3], n_autosomes=3)
     rad = synth.bead_radii(len(g), 1500.0, 0.3)
-    S_local = 12
-    lo, hi = parallel.structure_shard(S_local * ws, rank, ws)
-    full = synth.population_territories(g, S_local * ws, R=1500.0, seed=3)
+    S_total = 25                                   # does not divide by the world size: blocks of 13 and 12 structures
+    lo, hi = parallel.structure_shard(S_total, rank, ws)
+    full = synth.population_territories(g, S_total, R=1500.0, seed=3)
     local = torch.from_numpy(np.ascontiguousarray(full[:, lo:hi, :]))
-    slab = parallel.all_gather_slab(local).numpy()
-    assert np.array_equal(slab, full)
+    slab, offs = parallel.all_gather_slab(local, return_offsets=True)
+    slab = slab.numpy()
+    assert np.array_equal(slab, full) and offs == [0, 13, 25]
     pi, pj, pw = synth.hic_pairs(g, 0.004, seed=1)
     pl = np.zeros(pi.size)
 
@@ -55,6 +56,11 @@ def _worker(rank, ws, port, out_dir):
 
     rows = parallel.distributed_actdist(fn, pi, pj, pw, pl, g.chrom, g.copy_off)
     np.savez(os.path.join(out_dir, "rank%d.npz" % rank), row=rows[0], col=rows[1], dist=rows[2], prob=rows[3])
+    # the structure-sharded variant: nobody holds the whole population, counts and radix histograms are all-reduced
+    from oracle.astep_shard_oracle import NumpyShard
+    shard = NumpyShard(np.ascontiguousarray(full[:, lo:hi, :]), rad, g.chrom, g.copy_index)
+    rows2 = parallel.sharded_actdist(shard, S_total, pi, pj, pw, pl, 2.0, pair_chunk=37)
+    np.savez(os.path.join(out_dir, "shard%d.npz" % rank), row=rows2[0], col=rows2[1], dist=rows2[2], prob=rows2[3])
     dist.destroy_process_group()
 
 
@@ -68,11 +74,12 @@ def test_two_rank_astep_equals_single_process(tmp_path):
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     g = synth.Genome([9, 7, 6, 4, 3], n_autosomes=3)
     rad = synth.bead_radii(len(g), 1500.0, 0.3)
-    full = synth.population_territories(g, 24, R=1500.0, seed=3)
+    full = synth.population_territories(g, 25, R=1500.0, seed=3)
     pi, pj, pw = synth.hic_pairs(g, 0.004, seed=1)
     want = ao.actdist_rows(pi, pj, pw, np.zeros(pi.size), full, rad, g.chrom, g.copy_index, 2.0)
     assert want[0].size > 50
     for r in range(2):
-        got = np.load(os.path.join(str(tmp_path), "rank%d.npz" % r))
-        for k, name in enumerate(("row", "col", "dist", "prob")):
-            assert np.array_equal(got[name].view(np.uint32), want[k].view(np.uint32)), (r, name)
+        for variant in ("rank", "shard"):          # slab all-gather + pair sharding; structure sharding + all-reduced histograms
+            got = np.load(os.path.join(str(tmp_path), "%s%d.npz" % (variant, r)))
+            for k, name in enumerate(("row", "col", "dist", "prob")):
+                assert np.array_equal(got[name].view(np.uint32), want[k].view(np.uint32)), (r, variant, name)
