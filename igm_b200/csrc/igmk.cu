@@ -18,6 +18,7 @@
 #include "mstep.cuh"
 #include "md2.cuh"
 #include "md_big.cuh"
+#include "md_cluster.cuh"
 #include "astep.cuh"
 #include "astep_shard.cuh"
 #include "probe.cuh"
@@ -60,6 +61,7 @@ static cudaError_t dev_alloc_copy(T** dptr, const std::vector<T>& h, cudaStream_
 struct igmk_handle {
     int device = 0;
     int smem_optin = 0;
+    int sm_count = 148;
     cudaStream_t stream = nullptr;      // non-blocking: batches of different handles overlap on one device
     cudaStream_t stream_hi = nullptr;   // same, highest priority: the short CG launch that ends a batch overtakes the queued MD
                                         // CTAs of other batches, so a finished chunk leaves the device while the others still run
@@ -94,6 +96,10 @@ struct igmk_handle {
     Md2Desc* d_md2_desc = nullptr; uint16_t* d_md2_perm = nullptr; int32_t* d_md2_ell_off = nullptr;
     uint32_t* d_md2_ell_items = nullptr; uint32_t* d_md2_ell_act = nullptr; uint16_t* d_md2_nl = nullptr;
     int4* d_md2_eblk = nullptr; float4* d_md2_gf = nullptr;
+    // cluster path (md_cluster.cuh): CTAs per structure (0: not used) and its rebuild workspace
+    int mdc_CL = 0;
+    float4* d_mdc_xall = nullptr; float4* d_mdc_xsorted = nullptr; uint32_t* d_mdc_sorted = nullptr; uint32_t* d_mdc_cells = nullptr;
+    uint16_t* d_mdc_rowlen = nullptr; float* d_mdc_bbox = nullptr;
     double* d_md2_dbg = nullptr;
     bool md_big = false; float* d_big_state = nullptr; double* d_big = nullptr;
     bool dirty = true;
@@ -119,6 +125,8 @@ struct igmk_handle {
         cudaFree(d_md2_desc); cudaFree(d_md2_perm); cudaFree(d_md2_ell_off); cudaFree(d_md2_ell_items); cudaFree(d_md2_ell_act); cudaFree(d_md2_nl); d_md2_ell_act = nullptr;
         cudaFree(d_md2_eblk); cudaFree(d_md2_gf); cudaFree(d_md2_dbg);
         d_md2_eblk = nullptr; d_md2_gf = nullptr; d_md2_dbg = nullptr;
+        cudaFree(d_mdc_xall); cudaFree(d_mdc_xsorted); cudaFree(d_mdc_sorted); cudaFree(d_mdc_cells); cudaFree(d_mdc_rowlen); cudaFree(d_mdc_bbox);
+        d_mdc_xall = nullptr; d_mdc_xsorted = nullptr; d_mdc_sorted = nullptr; d_mdc_cells = nullptr; d_mdc_rowlen = nullptr; d_mdc_bbox = nullptr;
         d_md2_desc = nullptr; d_md2_perm = nullptr; d_md2_ell_off = nullptr; d_md2_ell_items = nullptr; d_md2_nl = nullptr;
         d_desc = nullptr; d_xyzr = nullptr; d_xyzr0 = nullptr; d_kind = nullptr; d_envmask = nullptr; d_bond_ptr = nullptr;
         d_bond_items = nullptr; d_btype_f = nullptr; d_btype_d = nullptr; d_nl = nullptr; d_nl_cnt = nullptr;
@@ -154,6 +162,7 @@ extern "C" int igmk_create(int device, igmk_handle_t** out)
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, device));
     h->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    h->sm_count = prop.multiProcessorCount;
     if (const char* e = getenv("IGMK_NL_WIDTH")) {          // initial neighbour-table width (tuning / profiling aid)
         const int w = atoi(e);
         if (w >= 8 && w <= 65536) { h->md2_nlw = (w + 7) / 8 * 8; h->nl_width = h->md2_nlw; }
@@ -675,9 +684,15 @@ static void md2_build(igmk_handle* h)
 // and the owned items of an atom are split into block A (the most frequent bond type, when that is an upper bound) and
 // block B (everything else, and bonds whose two ends both have full inboxes: listed at both ends, SYM).  Atoms are
 // ordered by the number of items they own, 32 at a time into warp-slots laid out boustrophedon over the warps.
-static void md2_build_owner(igmk_handle* h)
+// CL > 1: the layout of k_md2c (md_cluster.cuh) -- the atoms are cut into CL contiguous blocks in index order (genome
+// order: a chromosome territory is compact in space), block r goes to CTA r of the cluster, a position is r * np + offset
+// and the item fields are wider.
+static void md2_build_owner(igmk_handle* h, int CL = 1)
 {
-    const int K = h->md2_K, np = K * MD2_T, NW = MD2_NW, G = K * NW;
+    const int K = h->md2_K, npc = K * MD2_T, np = npc * CL, NW = MD2_NW, G = K * NW * CL;
+    const uint32_t SYM = CL > 1 ? MDC_IT_SYM : MD2_IT_SYM;
+    const int TSHIFT = CL > 1 ? MDC_IT_TSHIFT : MD2_IT_TSHIFT;
+    const uint32_t MAXT = CL > 1 ? (uint32_t)MDC_MAX_TYPES : (uint32_t)MD2_MAX_TYPES;
     const size_t ns = h->desc.size();
     h->md2_desc.assign(ns, Md2Desc());
     h->md2_perm.assign(ns * (size_t)np, MD2_NONE);
@@ -702,7 +717,7 @@ static void md2_build_owner(igmk_handle* h)
                 const int b = (int)(bi[c] & 0xffffu);
                 const uint32_t t = bi[c] >> 16;
                 if (b <= a) continue;                                   // every bond once (b == a: a bond to oneself has no force)
-                if (t >= (uint32_t)MD2_MAX_TYPES) { errs[s] = "more than 16384 distinct bond types in one structure"; return; }
+                if (t >= MAXT) { errs[s] = "too many distinct bond types in one structure for the MD kernel's item format"; return; }
                 nbond[s]++;
                 const int da = bp[a + 1] - bp[a], db = bp[b + 1] - bp[b];
                 int o = (own[a] < own[b] || (own[a] == own[b] && da >= db)) ? a : b, r = o == a ? b : a;
@@ -715,19 +730,23 @@ static void md2_build_owner(igmk_handle* h)
                 rows[o].push_back({r, t, (int8_t)indeg[r]});
                 indeg[r]++; own[o]++;
             }
-        // ---- atom order by owned items ----
+        // ---- atom order: per CTA by owned items ----
         std::vector<int> order((size_t)n), pos((size_t)n, -1);
-        for (int a = 0; a < n; a++) order[a] = a;
-        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return own[a] > own[b]; });
         uint16_t* perm = h->md2_perm.data() + s * (size_t)np;
         auto slot_of_group = [&](int g) { const int k = g / NW, r = g % NW; return k * NW + ((k & 1) ? NW - 1 - r : r); };
-        for (int g = 0; g < G; g++) {
-            const int gi = slot_of_group(g), k = gi / NW, w = gi % NW;
-            for (int l = 0; l < 32; l++) {
-                const int q = g * 32 + l;
-                if (q >= n) break;
-                const int p = k * MD2_T + w * 32 + l;
-                perm[p] = (uint16_t)order[q]; pos[order[q]] = p;
+        const int per_cta = (n + CL - 1) / CL;
+        for (int r = 0; r < CL; r++) {
+            const int a0 = std::min(n, r * per_cta), a1 = std::min(n, a0 + per_cta), nr = a1 - a0;
+            for (int a = a0; a < a1; a++) order[a] = a;
+            std::stable_sort(order.begin() + a0, order.begin() + a1, [&](int a, int b) { return own[a] > own[b]; });
+            for (int g = 0; g < K * NW; g++) {
+                const int gi = slot_of_group(g), k = gi / NW, w = gi % NW;
+                for (int l = 0; l < 32; l++) {
+                    const int q = g * 32 + l;
+                    if (q >= nr) break;
+                    const int p = r * npc + k * MD2_T + w * 32 + l;
+                    perm[p] = (uint16_t)order[a0 + q]; pos[order[a0 + q]] = p;
+                }
             }
         }
         Md2Desc& m = h->md2_desc[s];
@@ -736,11 +755,11 @@ static void md2_build_owner(igmk_handle* h)
         m.K = K;
         int4* eb = h->md2_eblk.data() + m.ell_desc_off;
         std::vector<uint32_t>& out = items[s];
-        for (int gi = 0; gi < G; gi++) {               // blocks in (slot, warp) order = the order the kernel indexes them
-            const int k = gi / NW, w = gi % NW;
+        for (int gi = 0; gi < G; gi++) {               // blocks in (CTA, slot, warp) order = the order the kernel indexes them
+            const int w = gi % NW, p0 = (gi / NW) * MD2_T + w * 32;       // first position of the warp-slot ((CTA * K + slot) * 1024 + warp * 32)
             int cols[2] = {0, 0};
             for (int l = 0; l < 32; l++) {
-                const int a = perm[k * MD2_T + w * 32 + l];
+                const int a = perm[p0 + l];
                 if (a == MD2_NONE) continue;
                 int c[2] = {0, 0};
                 for (const Own& it : rows[a]) c[(a_ok && it.type == 0 && it.q >= 0) ? 0 : 1]++;
@@ -754,16 +773,16 @@ static void md2_build_owner(igmk_handle* h)
                 uint32_t* b = out.data() + off[blk];
                 // layout [batch of 4 columns][lane][4]: one 16-byte load per lane and batch; padding = an item to oneself
                 for (int l = 0; l < 32; l++) {
-                    const uint32_t self = ((uint32_t)(k * MD2_T + w * 32 + l) << 4) | (blk == 0 ? 15u : MD2_IT_SYM);
+                    const uint32_t self = ((uint32_t)(p0 + l) << 4) | (blk == 0 ? 15u : SYM);
                     for (int c = 0; c < cols[blk]; c++) b[((c >> 2) * 32 + l) * 4 + (c & 3)] = self;
                 }
                 for (int l = 0; l < 32; l++) {
-                    const int a = perm[k * MD2_T + w * 32 + l];
+                    const int a = perm[p0 + l];
                     if (a == MD2_NONE) continue;
                     int c = 0;
                     for (const Own& it : rows[a]) {
                         if (((a_ok && it.type == 0 && it.q >= 0) ? 0 : 1) != blk) continue;
-                        const uint32_t v = ((uint32_t)pos[it.other] << 4) | (it.q >= 0 ? (uint32_t)it.q : MD2_IT_SYM) | (it.type << MD2_IT_TSHIFT);
+                        const uint32_t v = ((uint32_t)pos[it.other] << 4) | (it.q >= 0 ? (uint32_t)it.q : SYM) | (it.type << TSHIFT);
                         b[((c >> 2) * 32 + l) * 4 + (c & 3)] = v;
                         c++;
                     }
@@ -821,6 +840,26 @@ static int upload(igmk_handle* h)
     CU(cudaMemsetAsync(h->d_flags, 0, std::max<size_t>(ns, 1) * sizeof(int32_t), h->stream));
     h->md2_K = md2_pick_K(h->max_atoms);
     h->md_big = h->md2_K == 0 || getenv("IGMK_FORCE_BIG") != nullptr;   // the variable routes small batches through md_big.cuh (tests)
+    h->mdc_CL = 0;
+    {   // more than 8192 atoms: a thread-block cluster per structure (md_cluster.cuh); IGMK_FORCE_CLUSTER=<CTAs> sends smaller
+        // structures there too (tests, latency of small populations), IGMK_FORCE_BIG keeps the one-CTA global-memory kernel
+        // The cluster kernel gives the lowest time per structure (measured at 29 838 beads: 78 us per force evaluation on 16
+        // CTAs, 123 us on 8, against 860-1250 us for the one-CTA global-memory kernel), the one-CTA kernel the highest
+        // throughput once there are more structures than clusters fit the GPU (148 structures at once: 8.5 us per structure
+        // and evaluation against 13.6 us for 18 clusters of 8).  So: clusters while all of them are resident at once.
+        int want = 0;
+        if (const char* e = getenv("IGMK_FORCE_CLUSTER")) want = atoi(e);
+        if (want == 0 && h->md2_K == 0 && !getenv("IGMK_FORCE_BIG") && h->max_atoms <= 65535) {
+            const long long nsl = (long long)ns;
+            if (nsl * 16 <= h->sm_count) want = 16;
+            else if (nsl * 8 <= h->sm_count && h->max_atoms <= 32768) want = 8;
+        }
+        if (want == 2 || want == 4 || want == 8 || want == 16) {
+            int k = 1;
+            while (k < 4 && k * MD2_T * want < h->max_atoms) k *= 2;
+            if (k * MD2_T * want >= h->max_atoms && !getenv("IGMK_FORCE_BIG")) { h->mdc_CL = want; h->md2_K = k; h->md_big = false; }
+        }
+    }
     if (h->md_big) {                                   // > 8192 atoms: state in global memory (md_big.cuh)
         h->md2_K = (h->max_atoms + MD2_T - 1) / MD2_T;
         if ((long long)md_big_smem_bytes(h->md2_K) > (long long)h->smem_optin)
@@ -832,7 +871,7 @@ static int upload(igmk_handle* h)
     if (h->md2_K > 0) {
         if (h->md_big) md2_build(h);
         else {
-            md2_build_owner(h);
+            md2_build_owner(h, std::max(h->mdc_CL, 1));
             if (!h->md2_error.empty()) return fail("igmk: " + h->md2_error);
         }
         CU(dev_alloc_copy(&h->d_md2_desc, h->md2_desc, h->stream));
@@ -844,6 +883,15 @@ static int upload(igmk_handle* h)
         if (!h->md_big) {
             CU(dev_alloc_copy(&h->d_md2_eblk, h->md2_eblk, h->stream));
             CU(cudaMalloc((void**)&h->d_md2_gf, h->md2_perm.size() * (size_t)MD2_INBOX * sizeof(float4)));
+            if (h->mdc_CL > 0) {
+                const size_t npos = h->md2_perm.size();
+                CU(cudaMalloc((void**)&h->d_mdc_xall, npos * sizeof(float4)));
+                CU(cudaMalloc((void**)&h->d_mdc_xsorted, npos * sizeof(float4)));
+                CU(cudaMalloc((void**)&h->d_mdc_sorted, npos * sizeof(uint32_t)));
+                CU(cudaMalloc((void**)&h->d_mdc_rowlen, npos * sizeof(uint16_t)));
+                CU(cudaMalloc((void**)&h->d_mdc_cells, ns * 2 * (size_t)(MDC_MAXC + 1) * sizeof(uint32_t)));
+                CU(cudaMalloc((void**)&h->d_mdc_bbox, ns * (size_t)MDC_MAX_CL * 8 * sizeof(float)));
+            }
         }
     }
     h->h2d_bytes = ns * sizeof(StructDesc) + 2 * na * sizeof(float4) + na * (sizeof(uint8_t) + sizeof(uint32_t)) +
@@ -1023,8 +1071,44 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
     return 0;
 }
 
+template <int K, int CL>
+static int launch_mdc_k(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
+{
+    const size_t sm = mdc_smem_bytes(K);
+    auto kern = k_md2c<K, CL, false>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    if (CL > 8) CU(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    MdcView V;
+    memset(&V, 0, sizeof V);
+    V.perm = h->d_md2_perm; V.ell_items = h->d_md2_ell_items; V.ell_act = h->d_md2_ell_act; V.eblk = h->d_md2_eblk;
+    V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.gf = h->d_md2_gf;
+    V.xall = h->d_mdc_xall; V.xsorted = h->d_mdc_xsorted; V.sorted = h->d_mdc_sorted; V.cells = h->d_mdc_cells;
+    V.rowlen = h->d_mdc_rowlen; V.bbox = h->d_mdc_bbox; V.dbg_forces = h->d_md2_dbg;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3((unsigned)(ns * CL)); cfg.blockDim = dim3(MD2_T); cfg.dynamicSmemBytes = sm; cfg.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    const Md2Desc* md = h->d_md2_desc;
+    CU(cudaLaunchKernelEx(&cfg, kern, B, V, md, P));
+    return 0;
+}
+
+static int launch_mdc(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
+{
+    const int K = h->md2_K, CL = h->mdc_CL;
+#define MDC_CASE(k, c) if (K == k && CL == c) return launch_mdc_k<k, c>(h, B, P, ns)
+    MDC_CASE(1, 2); MDC_CASE(2, 2); MDC_CASE(4, 2); MDC_CASE(1, 4); MDC_CASE(2, 4); MDC_CASE(4, 4);
+    MDC_CASE(1, 8); MDC_CASE(2, 8); MDC_CASE(4, 8); MDC_CASE(2, 16); MDC_CASE(4, 16);
+#undef MDC_CASE
+    return fail("igmk_run: no cluster MD kernel for this structure size / cluster size");
+}
+
 static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
 {
+    if (h->mdc_CL > 0) return launch_mdc(h, B, P, ns);
     if (h->md_big) {
         if (P.debug_stage >= 0) return fail("igmk_md_forces: not available on the global-memory MD path");
         const size_t sm = md_big_smem_bytes(h->md2_K);

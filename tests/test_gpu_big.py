@@ -1,5 +1,7 @@
-"""Structures beyond one SM's shared memory (BASELINE config 4 territory: 200 kb genomes): the
-global-memory MD kernel (md_big.cuh) and the global-state mode of the float64 single point / CG."""
+"""Structures beyond one SM's shared memory (BASELINE config 4 territory: 200 kb genomes): the cluster-per-structure
+MD kernel (md_cluster.cuh: atoms split over the CTAs of a thread-block cluster, partner positions through distributed
+shared memory), the one-CTA global-memory kernel it replaced (md_big.cuh, kept behind IGMK_FORCE_BIG) and the
+global-state mode of the float64 single point / CG."""
 import numpy as np
 import pytest
 
@@ -41,6 +43,48 @@ def test_big_md_kernel_follows_the_small_one(monkeypatch):
     for (a, ra), (c, rc), (e, _) in zip(*out):
         assert np.abs(a - c).max() <= 1e-3 and ra.n_rebuilds == rc.n_rebuilds
         assert np.array_equal(c.view(np.uint32), e.view(np.uint32))
+
+
+@pytest.mark.parametrize("cl", [2, 4, 8])
+def test_cluster_md_kernel_follows_the_single_cta_one(monkeypatch, cl):
+    """the same structures through k_md2 (one CTA) and, forced, through k_md2c on clusters of 2 / 4 / 8 CTAs: the same
+    trajectory up to float32 round-off (sums over bonds and CTAs are taken in another order), the same rebuild count,
+    and the cluster kernel reproduces itself bit for bit"""
+    g, rad, systems = small_system(seed=41, n_struct=3)
+    from helpers import demo_structure
+    ffg = np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "ff_golden.npz"))
+    systems = systems + [demo_structure(ffg, 2)]              # 3010 atoms with every kind of term
+    prot = short_protocol(md=6, relax=2)
+    prot.n_stage = 2
+    prot.skip_minimize = 1
+    out = []
+    for force in (False, True, True):
+        if force:
+            monkeypatch.setenv("IGMK_FORCE_CLUSTER", str(cl))
+        with MStepBatch(0) as b:
+            slots = [b.submit(ps) for ps in systems]
+            b.run(prot)
+            out.append([b.fetch(s) for s in slots])
+    for (a, ra), (c, rc), (e, _) in zip(*out):
+        assert np.abs(a - c).max() <= 2e-3 and ra.n_rebuilds == rc.n_rebuilds
+        assert np.array_equal(c.view(np.uint32), e.view(np.uint32))
+
+
+@pytest.mark.parametrize("cl", [2, 8])
+def test_cluster_md_kernel_force_loop_matches_oracle(monkeypatch, cl):
+    """the forces the cluster kernel itself computes (remote gathers, remote inbox flags, mailboxes) against the oracle"""
+    monkeypatch.setenv("IGMK_FORCE_CLUSTER", str(cl))
+    from helpers import demo_structure
+    ffg = np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "ff_golden.npz"))
+    systems = [demo_structure(ffg, k) for k in (1, 4)]
+    prot = short_protocol()
+    with MStepBatch(0) as b:
+        slots = [b.submit(ps) for ps in systems]
+        b.md_forces(prot, 2)
+        for ps, slot in zip(systems, slots):
+            f_ref, _ = ff.single_point(ps, prot.evfactor[2], prot.envfactor[2], 1.0)
+            f = b.fetch_forces(slot)
+            assert np.abs(f - f_ref).max() <= 2e-4 * np.abs(f_ref).max(), np.abs(f - f_ref).max() / np.abs(f_ref).max()
 
 
 def test_single_point_and_cg_beyond_shared_memory():
@@ -108,6 +152,10 @@ def test_config4_size_200kb_genome():
         f = b.fetch_forces(slot)
         assert res.final_energy == pytest.approx(e_ref["total"], rel=1e-10)
         assert np.abs(f - f_ref).max() <= 1e-10 * np.abs(f_ref).max()
+        b.md_forces(prot, 0)                       # the cluster kernel's own force loop at full size (8 CTAs x 4096 positions)
+        f32 = b.fetch_forces(slot)
+        f0, _ = ff.single_point(ps, prot.evfactor[0], prot.envfactor[0], 1.0)
+        assert np.abs(f32 - f0).max() <= 2e-4 * np.abs(f0).max()
         b.run(prot)
         xyz2, res = b.fetch(slot)
         md_ms, cg_ms, _ = b.last_timings()
