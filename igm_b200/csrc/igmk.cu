@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <chrono>
 #include <thread>
+#include <mutex>
 #include <cuda_runtime.h>
 
 #include "../../include/igmk.h"
@@ -1101,7 +1102,7 @@ static int launch_mdc(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
     const int K = h->md2_K, CL = h->mdc_CL;
 #define MDC_CASE(k, c) if (K == k && CL == c) return launch_mdc_k<k, c>(h, B, P, ns)
     MDC_CASE(1, 2); MDC_CASE(2, 2); MDC_CASE(4, 2); MDC_CASE(1, 4); MDC_CASE(2, 4); MDC_CASE(4, 4);
-    MDC_CASE(1, 8); MDC_CASE(2, 8); MDC_CASE(4, 8); MDC_CASE(2, 16); MDC_CASE(4, 16);
+    MDC_CASE(1, 8); MDC_CASE(2, 8); MDC_CASE(4, 8); MDC_CASE(1, 16); MDC_CASE(2, 16); MDC_CASE(4, 16);
 #undef MDC_CASE
     return fail("igmk_run: no cluster MD kernel for this structure size / cluster size");
 }
@@ -1403,8 +1404,7 @@ extern "C" int igmk_pop_create(int device, int32_t n_bead, int32_t n_struct, int
     p->radii.assign(radii, radii + n_bead);
     CU(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&p->ev0)); CU(cudaEventCreate(&p->ev1));
-    CU(cudaMalloc((void**)&p->d_crd, (size_t)n_bead * n_struct * 3 * sizeof(float)));
-    p->own_crd = true;
+    p->d_crd = nullptr; p->own_crd = false;      // the slab is allocated by the first igmk_pop_upload, or attached by the caller
     CU(cudaMalloc((void**)&p->d_radii, (size_t)n_bead * sizeof(float)));
     CU(cudaMalloc((void**)&p->d_chrom, (size_t)n_bead * sizeof(int32_t)));
     CU(cudaMalloc((void**)&p->d_copy_off, (size_t)(n_hap + 1) * sizeof(int32_t)));
@@ -1430,6 +1430,11 @@ extern "C" int igmk_pop_upload(igmk_pop_t* p, const float* crd)
 {
     if (!p || !crd) return fail("igmk_pop_upload: NULL argument");
     CU(cudaSetDevice(p->device));
+    if (!p->d_crd || !p->own_crd) {
+        p->d_crd = nullptr; p->own_crd = false;
+        CU(cudaMalloc((void**)&p->d_crd, (size_t)p->n_bead * p->n_struct * 3 * sizeof(float)));
+        p->own_crd = true;
+    }
     CU(cudaMemcpyAsync(p->d_crd, crd, (size_t)p->n_bead * p->n_struct * 3 * sizeof(float), cudaMemcpyHostToDevice, p->stream));
     CU(cudaStreamSynchronize(p->stream));
     return 0;
@@ -1438,6 +1443,7 @@ extern "C" int igmk_pop_upload(igmk_pop_t* p, const float* crd)
 extern "C" int igmk_pop_download(igmk_pop_t* p, float* crd)
 {
     if (!p || !crd) return fail("igmk_pop_download: NULL argument");
+    if (!p->d_crd) return fail("igmk_pop_download: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     CU(cudaMemcpyAsync(crd, p->d_crd, (size_t)p->n_bead * p->n_struct * 3 * sizeof(float), cudaMemcpyDeviceToHost, p->stream));
     CU(cudaStreamSynchronize(p->stream));
@@ -1459,6 +1465,9 @@ extern "C" int igmk_pop_attach_coords(igmk_pop_t* p, void* dptr)
     CU(cudaPointerGetAttributes(&a, dptr));
     if (a.type != cudaMemoryTypeDevice || a.device != p->device)
         return fail("igmk_pop_attach_coords: not a device pointer of this population's GPU");
+    // the slab was produced on a stream of the caller (a torch tensor after an NCCL all-gather, a copy): the kernels of
+    // this population run on its own non-blocking stream, which is not ordered after that work
+    CU(cudaDeviceSynchronize());
     if (p->own_crd) cudaFree(p->d_crd);
     p->d_crd = (float*)dptr; p->own_crd = false;
     return 0;
@@ -1495,6 +1504,7 @@ extern "C" int igmk_pop_actdist_launch(igmk_pop_t* p, double contact_range)
     if (!p) return fail("igmk_pop_actdist_launch: NULL handle");
     p->last_ms = 0.f;
     if (p->n_pairs == 0) { p->actdist_done = true; return 0; }
+    if (!p->d_crd) return fail("igmk_pop_actdist_launch: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const int spt = (p->n_struct + AD_THREADS - 1) / AD_THREADS;       // structures per thread
     if (spt <= 8 && p->max_copies * p->max_copies <= 4 && !getenv("IGMK_ACTDIST_SMEM")) {   // the kernel holds 4 combinations
@@ -1610,6 +1620,7 @@ extern "C" int igmk_pop_shard_count(igmk_pop_t* p, double contact_range, void* d
     if (int rc = shard_ready(p, "igmk_pop_shard_count", d_counts, d_counts)) return rc;
     p->actdist_done = false;
     if (p->n_pairs == 0) return 0;
+    if (!p->d_crd) return fail("igmk_pop_shard_count: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * 8);
     CU(cudaEventRecord(p->ev0, p->stream));
@@ -1641,6 +1652,7 @@ extern "C" int igmk_pop_shard_hist(igmk_pop_t* p, int32_t pass, const void* d_pr
     if (int rc = shard_ready(p, "igmk_pop_shard_hist", d_prefix, d_hist)) return rc;
     if (pass < 0 || pass > 3) return fail("igmk_pop_shard_hist: pass must be 0..3");
     if (p->n_pairs == 0) return 0;
+    if (!p->d_crd) return fail("igmk_pop_shard_hist: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const int64_t grid = std::min<int64_t>(p->n_pairs, (int64_t)p->sm_count * 8);
     CU(cudaEventRecord(p->ev0, p->stream));
@@ -1680,6 +1692,7 @@ extern "C" int igmk_pop_contact_freq(igmk_pop_t* p, int64_t n_pairs, const int32
     (void)zero;
     std::vector<double> dummy((size_t)n_pairs, 0.0);
     if (int rc = igmk_pop_set_pairs(p, n_pairs, pair_i, pair_j, dummy.data(), dummy.data())) return rc;
+    if (!p->d_crd) return fail("igmk_pop_contact_freq: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const int64_t grid = std::min<int64_t>((n_pairs + 7) / 8, (int64_t)p->sm_count * 32);
     CU(cudaEventRecord(p->ev0, p->stream));
@@ -1718,6 +1731,7 @@ extern "C" int igmk_pop_damid_actdist(igmk_pop_t* p, int64_t n_loci, const int32
     if (!loc || !pwish || !plast || !nucleus_param || !row_bead || !dist || !prob) return fail("igmk_pop_damid_actdist: NULL argument");
     for (int64_t q = 0; q < n_loci; q++)
         if (loc[q] < 0 || loc[q] >= p->n_hap) return fail("igmk_pop_damid_actdist: locus index out of range");
+    if (!p->d_crd) return fail("igmk_pop_damid_actdist: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const size_t smem = (size_t)p->max_copies * p->n_struct * sizeof(double);
     if ((long long)smem + 1024 > (long long)p->smem_optin) return fail("igmk_pop_damid_actdist: population too large for one CTA's shared memory");
@@ -1763,6 +1777,7 @@ extern "C" int igmk_pop_damid_assign(igmk_pop_t* p, int64_t n_rows, const int32_
     if (!bead || !dist || !semiaxes || !bits) return fail("igmk_pop_damid_assign: NULL argument");
     for (int64_t r = 0; r < n_rows; r++)
         if (bead[r] < 0 || bead[r] >= p->n_bead) return fail("igmk_pop_damid_assign: bead index out of range");
+    if (!p->d_crd) return fail("igmk_pop_damid_assign: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     std::vector<double> den;
     damid_denominators(p, n_rows, bead, contact_range, 1, semiaxes, p->radii, den);
@@ -1798,6 +1813,7 @@ extern "C" int igmk_pop_fish_ranks(igmk_pop_t* p, int64_t n_items, const int32_t
             (hap_j[q] >= 0 && p->copy_off[hap_j[q] + 1] - p->copy_off[hap_j[q]] < 2))
             return fail("igmk_pop_fish_ranks: locus has fewer than two copies (IndexError in the reference)");
     }
+    if (!p->d_crd) return fail("igmk_pop_fish_ranks: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const size_t S = (size_t)p->n_struct;
     const size_t smem = 2 * S * sizeof(float);
@@ -1848,6 +1864,7 @@ extern "C" int igmk_pop_sprite_rg2(igmk_pop_t* p, int32_t n_clusters, const int3
     const int32_t n_beads = rg_off[n_regions];
     for (int i = 0; i < n_beads; i++)
         if (beads[i] < 0 || beads[i] >= p->n_bead) return fail("igmk_pop_sprite_rg2: bead index out of range");
+    if (!p->d_crd) return fail("igmk_pop_sprite_rg2: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const size_t S = (size_t)p->n_struct;
     DevBuf<int32_t> d_cl, d_rg, d_b, d_ms; DevBuf<float> d_v; DevBuf<int8_t> d_ci;
@@ -1904,6 +1921,7 @@ extern "C" int igmk_pop_assign_launch(igmk_pop_t* p)
     if (!p) return fail("igmk_pop_assign_launch: NULL handle");
     p->last_ms = 0.f;
     if (p->n_rows == 0) { p->assign_done = true; return 0; }
+    if (!p->d_crd) return fail("igmk_pop_assign_launch: no coordinates uploaded or attached");
     CU(cudaSetDevice(p->device));
     const int64_t grid = std::min<int64_t>((p->n_rows + 31) / 32, (int64_t)p->sm_count * 2);
     CU(cudaEventRecord(p->ev0, p->stream));
@@ -1958,6 +1976,19 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH
 
 constexpr int NOALLOC_MAX_DEVICES = 64;
 unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};   // per device: device address of the array above
+std::mutex g_noalloc_mutex;                                      // the first calls of several host threads set up once
+
+// the entry point works on `device` and leaves the caller's current device as it found it
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t enter(int device)
+    {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) { prev = -1; return e; }
+        return prev == device ? cudaSuccess : cudaSetDevice(device);
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
 
 struct NoallocArgs {
     StructDesc desc;
@@ -2028,15 +2059,19 @@ extern "C" int igmk_single_point_noalloc(int device, void* stream, int32_t n_ato
     }
     if (n_env < 0 || n_env > IGMK_MAX_ENVELOPES || (n_env > 0 && !env_abck)) return fail("igmk_single_point_noalloc: bad envelope arguments");
     if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail("igmk_single_point_noalloc: bad device ordinal");
-    CU(cudaSetDevice(device));
+    DeviceGuard guard;
+    CU(guard.enter(device));
     const size_t sm = ctx_smem_bytes<double>(n_atoms, false);
-    if (!g_noalloc_ptr[device]) {
-        // one-time set-up on this device (with it current): resolve the array's device address
-        void* p = nullptr;
-        CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
-        CU(cudaFuncSetAttribute(k_single_point_noalloc, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)ctx_smem_bytes<double>(IGMK_NOALLOC_MAX_ATOMS, false)));
-        g_noalloc_ptr[device] = (unsigned char*)p;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_ptr[device]) {
+            // one-time set-up on this device (with it current): resolve the array's device address
+            void* p = nullptr;
+            CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            CU(cudaFuncSetAttribute(k_single_point_noalloc, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)ctx_smem_bytes<double>(IGMK_NOALLOC_MAX_ATOMS, false)));
+            g_noalloc_ptr[device] = (unsigned char*)p;
+        }
     }
     NoallocArgs a;
     memset(&a, 0, sizeof a);

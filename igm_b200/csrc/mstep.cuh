@@ -268,15 +268,18 @@ struct Ctx {
         // cursors: reuse nl_cnt-independent scratch -> use bx as int storage is unsafe; use cell_atoms
         // two-step: every atom finds its rank inside its cell by counting lower-indexed atoms of the
         // same cell among the cell's final members, so first drop atoms unordered via atomics ...
-        for (int c = tid; c < ncell; c += nt) cell_atoms[n + c] = 0;      // cursors live behind the atom list
+        // cursors live behind the atom list, from an EVEN offset: with an odd n the 32-bit word of cursor 0 would also hold
+        // atom slot n-1, which other threads write with plain 16-bit stores in this very phase
+        const int cur0 = (n + 1) & ~1;
+        for (int c = tid; c < ncell; c += nt) cell_atoms[cur0 + c] = 0;
         __syncthreads();
         for (int i = tid; i < n; i += nt) {
             int c = cell_of[i];
             if (c == 0xffff) continue;
             // 16-bit cursor increments through a 32-bit CAS-free atomicAdd on the containing word
-            unsigned int* w = (unsigned int*)(cell_atoms + ((n + c) & ~1));
-            unsigned int old = atomicAdd(w, ((n + c) & 1) ? 0x10000u : 1u);
-            int pos = ((n + c) & 1) ? (old >> 16) : (old & 0xffffu);
+            unsigned int* w = (unsigned int*)(cell_atoms + ((cur0 + c) & ~1));
+            unsigned int old = atomicAdd(w, ((cur0 + c) & 1) ? 0x10000u : 1u);
+            int pos = ((cur0 + c) & 1) ? (old >> 16) : (old & 0xffffu);
             cell_atoms[cell_start[c] + pos] = (uint16_t)i;
         }
         __syncthreads();

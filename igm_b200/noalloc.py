@@ -30,6 +30,10 @@ def host_layout(ps):
     types, tidx = np.unique(np.stack([ps.bond_r0, ks], axis=1), axis=0, return_inverse=True) if ps.bond_i.size \
         else (np.zeros((1, 2)), np.zeros(0, dtype=np.int64))
     tidx = np.asarray(tidx).reshape(-1)
+    if types.shape[0] > 65536:
+        raise ValueError("more than 65536 distinct bond types: the item format (partner | type << 16) cannot hold them")
+    if n > 65535:
+        raise ValueError("more than 65535 atoms: the item format (partner | type << 16) cannot hold them")
     owner = np.concatenate([ps.bond_i, ps.bond_j]).astype(np.int64)
     partner = np.concatenate([ps.bond_j, ps.bond_i]).astype(np.uint32)
     tt = np.concatenate([tidx, tidx]).astype(np.uint32)

@@ -261,6 +261,9 @@ int igmk_last_timings(igmk_handle_t* h, double* md_ms, double* cg_ms, int64_t* h
  * capture.  All calls on a device share the one scratch array: nothing in it has to start at zero
  * (each call rewrites every entry it reads), but two calls running on the GPU at the same time
  * would overwrite each other's neighbour table -- keep them on one stream or order them yourself.
+ * The call selects `device` for its own work and restores the caller's current device before it returns.  The
+ * scratch address found on the first call belongs to the device's primary context: after a cudaDeviceReset the
+ * library has to be reloaded.
  */
 #define IGMK_NOALLOC_MAX_ATOMS 3328
 int igmk_single_point_noalloc(int device, void* stream, int32_t n_atoms,

@@ -158,6 +158,20 @@ def test_ragged_batch_of_small_systems():
             assert np.abs(f - f_ref).max() <= 1e-10 * max(np.abs(f_ref).max(), 1e-30)
 
 
+def test_odd_atom_count():
+    """an odd number of atoms puts the 16-bit cell cursors of the float64 kernels next to the last atom slot"""
+    for sizes in ((13, 11, 8, 6), (14, 11, 8, 6)):
+        g = synth.Genome(list(sizes), n_autosomes=3)
+        rad = synth.bead_radii(len(g), 1400.0, 0.3)
+        rng = np.random.default_rng(7)
+        ps = synth.pack_structure(synth.territories(g, 1400.0, rng), rad, g, nucleus_radius=1400.0)
+        f_ref, e_ref = ff.single_point(ps)
+        with MStepBatch(0) as b:
+            slot = b.submit(ps)
+            b.single_point()
+            _check(b, slot, ps, f_ref, e_ref, 1e-10)
+
+
 def test_dense_start_widens_the_neighbour_table():
     """territory starts pack > 96 beads inside the list cutoff: the run must widen, not fail"""
     g = synth.Genome([400], n_autosomes=0)

@@ -10,8 +10,9 @@ scratch array and it keeps whatever the previous call left in it.  (Collected la
 import numpy as np
 import pytest
 
-from igm_b200 import noalloc
+from igm_b200 import noalloc, synth
 from igm_b200.kernel import MStepBatch
+from oracle import ff as ff_oracle
 from helpers import demo_structure, small_system
 
 pytestmark = pytest.mark.gpu
@@ -46,6 +47,8 @@ def _check(torch, ps):
     f_ref, res = _reference(ps)
     f, e, status = _call(torch, ps)
     assert status == 0
+    f_orc, e_orc = ff_oracle.single_point(ps)               # and directly against the CPU oracle
+    assert e[0] == pytest.approx(e_orc["total"], rel=RTOL) and np.abs(f - f_orc).max() <= RTOL * np.abs(f_orc).max()
     assert e[0] == pytest.approx(res.final_energy, rel=RTOL)
     assert e[1] == pytest.approx(res.pair_energy, rel=RTOL, abs=RTOL * abs(res.final_energy))
     assert e[2] == pytest.approx(res.bond_energy, rel=RTOL, abs=RTOL * abs(res.final_energy))
@@ -69,3 +72,21 @@ def test_noalloc_rejects_sizes_beyond_its_scratch():
     with pytest.raises(RuntimeError, match="at most %d" % noalloc.MAX_ATOMS):
         noalloc.single_point_noalloc(0, 0, noalloc.MAX_ATOMS + 1, *([z.data_ptr()] * 6), np.zeros((0, 4)), 1.0, 1.0,
                                      z.data_ptr(), z.data_ptr(), z.data_ptr())
+
+
+def test_noalloc_reports_a_full_neighbour_table_and_keeps_the_callers_device():
+    """more than 96 beads inside the list cutoff of one bead: the fixed scratch cannot hold the rows -> status 1 (the
+    regular entry point widens its table instead); and the call must not leave another device current"""
+    torch = pytest.importorskip("torch")
+    g = synth.Genome([400], n_autosomes=0)
+    rad = synth.bead_radii(len(g), 1500.0, 0.4)
+    xyz = (np.random.default_rng(1).normal(size=(400, 3)) * 120.0).astype(np.float32)
+    ps = synth.pack_structure(xyz, rad, g, nucleus_radius=1500.0)
+    before = torch.cuda.current_device()
+    _, _, status = _call(torch, ps)
+    assert status == 1
+    assert torch.cuda.current_device() == before
+    f_ref, res = _reference(ps)                              # the allocating entry point handles the same input
+    assert np.isfinite(res.final_energy)
+    _, _, small = small_system(seed=22)                      # and the next call on the dirty scratch is right again
+    _check(torch, small[0])
