@@ -72,6 +72,7 @@ class PopExtras(C.Structure):
         ("bond_style", c_u8p),
         ("n_env", C.c_int32), ("env_abck", c_f64p), ("env_row_off", c_i64p), ("env_bead", c_i32p), ("env_bits", c_u32p),
         ("env_bits_words", C.c_int32),
+        ("atom_off", c_i64p), ("atom_xyz", c_f32p), ("atom_radius", c_f32p), ("atom_kind", c_u8p),
     ]
 
 
@@ -232,6 +233,7 @@ _SIGNATURES = {
     "igmk_pop_damid_assign": (C.c_int, [_vp, C.c_int64, c_i32p, c_f32p, C.c_double, c_f64p, c_u32p]),
     "igmk_pop_fish_ranks": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p, c_f32p, c_i32p, c_i32p]),
     "igmk_pop_sprite_rg2": (C.c_int, [_vp, C.c_int32, c_i32p, c_i32p, c_i32p, c_f32p, C.POINTER(C.c_int8), c_i32p]),
+    "igmk_pop_sprite_select": (C.c_int, [_vp, C.c_int32, c_i32p, c_i32p, c_i32p, c_i32p, c_i32p, C.c_int32, c_f32p, c_i32p, c_i32p]),
     "igmk_pop_set_rows": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p]),
     "igmk_pop_assign_launch": (C.c_int, [_vp]),
     "igmk_pop_assign_collect": (C.c_int, [_vp, c_u32p]),

@@ -745,4 +745,142 @@ k_sprite_rg2(PopView P, int32_t n_clusters, const int32_t* __restrict__ cl_off /
     }
 }
 
+// SPRITE A-step, the whole of compute_gyration_radius (igm/cython_compiled/sprite.pyx:104-283) and the keep-best
+// selection of SpriteAssignmentStep.task (igm/steps/SpriteAssignmentStep.py:148-160) for one cluster per CTA.
+// A cluster is a list of segments (haploid ids, ascending = grouped by chromosome); segment i has the copies
+// beads[seg_off[i] .. seg_off[i+1]) and belongs to group seg_group[i] (its chromosome, numbered 0.. inside the cluster).
+//   * one group (sprite.pyx:198-212): every copy k of the chromosome is tried for ALL segments, the copy with the
+//     smallest Rg^2 wins (first minimum);
+//   * several groups (:215-283): the copy of every chromosome is chosen on ONE representative segment per group
+//     (rep[g], chosen by the caller: the reference draws it with np.random.choice) by enumerating the combinations
+//     like get_rg2s_cpp (region 0 = fastest digit, strict <), then Rg^2 is taken over all segments with those copies.
+// float32 arithmetic in the reference's order (gyration_radius_sq, cpp_sprite_assignment.cpp:49-61).
+// Then the `keep` structures with the smallest Rg^2 in ascending order (ties by structure index), their Rg^2 and,
+// per segment, the bead chosen in each of them.
+constexpr int SPRITE_MAX_GROUPS = 8;
+constexpr int SPRITE_SORT_MAX = 4096;      // structures the shared-memory sort holds
+
+__device__ __forceinline__ float sprite_rg2_of(const PopView& P, int s, int seg0, int nseg, const int32_t* __restrict__ seg_off,
+                                               const int32_t* __restrict__ beads, const int32_t* __restrict__ seg_group, uint32_t choice)
+{
+    const int S = P.n_struct;
+    float mx = 0.f, my = 0.f, mz = 0.f;
+    for (int i = 0; i < nseg; i++) {
+        const int c = (choice >> (4 * seg_group[seg0 + i])) & 15;
+        const float* x = P.crd + ((size_t)beads[seg_off[seg0 + i] + c] * S + s) * 3;
+        mx = __fadd_rn(mx, x[0]); my = __fadd_rn(my, x[1]); mz = __fadd_rn(mz, x[2]);
+    }
+    const float fn = (float)nseg;
+    mx = __fdiv_rn(mx, fn); my = __fdiv_rn(my, fn); mz = __fdiv_rn(mz, fn);
+    float rg = 0.f;
+    for (int i = 0; i < nseg; i++) {
+        const int c = (choice >> (4 * seg_group[seg0 + i])) & 15;
+        const float* x = P.crd + ((size_t)beads[seg_off[seg0 + i] + c] * S + s) * 3;
+        const float dx = __fsub_rn(x[0], mx), dy = __fsub_rn(x[1], my), dz = __fsub_rn(x[2], mz);
+        rg = __fadd_rn(rg, __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+    }
+    return __fdiv_rn(rg, fn);
+}
+
+__global__ void __launch_bounds__(256)
+k_sprite_select(PopView P, int32_t n_clusters, const int32_t* __restrict__ cl_off, const int32_t* __restrict__ seg_off,
+                const int32_t* __restrict__ beads, const int32_t* __restrict__ seg_group, const int32_t* __restrict__ n_groups,
+                const int32_t* __restrict__ rep /* [n_clusters][SPRITE_MAX_GROUPS] segment (within the cluster) of each group */,
+                int32_t keep, float* __restrict__ best_rg2 /* [n_clusters][keep] */, int32_t* __restrict__ best_struct,
+                int32_t* __restrict__ best_beads /* [n_segments][keep] */)
+{
+    extern __shared__ __align__(16) unsigned char sp_smem[];
+    const int S = P.n_struct;
+    int npow = 1;
+    while (npow < S) npow <<= 1;
+    float* val = (float*)sp_smem;                     // [npow]
+    int32_t* idx = (int32_t*)(val + npow);            // [npow]
+    uint32_t* cho = (uint32_t*)(idx + npow);          // [S] 4 bits per group
+    for (int c = blockIdx.x; c < n_clusters; c += gridDim.x) {
+        const int seg0 = cl_off[c], nseg = cl_off[c + 1] - seg0, ng = n_groups[c];
+        for (int s = threadIdx.x; s < npow; s += blockDim.x) {
+            float v = 3.0e38f;
+            uint32_t choice = 0;
+            if (s < S) {
+                if (ng == 1) {
+                    const int nc = seg_off[seg0 + 1] - seg_off[seg0];      // copies of the chromosome (those of the first segment, :199)
+                    for (int k = 0; k < nc; k++) {
+                        const float r = sprite_rg2_of(P, s, seg0, nseg, seg_off, beads, seg_group, (uint32_t)k);
+                        if (r < v) { v = r; choice = (uint32_t)k; }
+                    }
+                } else {
+                    // copy selection on the representatives (get_rg2s_cpp over ng regions)
+                    int rs[SPRITE_MAX_GROUPS], ncopy[SPRITE_MAX_GROUPS], ncomb = 1;
+#pragma unroll
+                    for (int g = 0; g < SPRITE_MAX_GROUPS; g++) {
+                        rs[g] = 0; ncopy[g] = 1;
+                        if (g < ng) { rs[g] = seg0 + rep[c * SPRITE_MAX_GROUPS + g]; ncopy[g] = seg_off[rs[g] + 1] - seg_off[rs[g]]; ncomb *= ncopy[g]; }
+                    }
+                    const float fg = (float)ng;
+                    float best = 100000000.0f;
+                    int best_k = 0;
+                    for (int k = 0; k < ncomb; k++) {
+                        float px[SPRITE_MAX_GROUPS], py[SPRITE_MAX_GROUPS], pz[SPRITE_MAX_GROUPS];
+                        float mx = 0.f, my = 0.f, mz = 0.f;
+                        int kk = k;
+#pragma unroll
+                        for (int g = 0; g < SPRITE_MAX_GROUPS; g++) {
+                            if (g < ng) {
+                                const int si = kk % ncopy[g]; kk /= ncopy[g];
+                                const float* x = P.crd + ((size_t)beads[seg_off[rs[g]] + si] * S + s) * 3;
+                                px[g] = x[0]; py[g] = x[1]; pz[g] = x[2];
+                                mx = __fadd_rn(mx, px[g]); my = __fadd_rn(my, py[g]); mz = __fadd_rn(mz, pz[g]);
+                            }
+                        }
+                        mx = __fdiv_rn(mx, fg); my = __fdiv_rn(my, fg); mz = __fdiv_rn(mz, fg);
+                        float rg = 0.f;
+#pragma unroll
+                        for (int g = 0; g < SPRITE_MAX_GROUPS; g++) {
+                            if (g < ng) {
+                                const float dx = __fsub_rn(px[g], mx), dy = __fsub_rn(py[g], my), dz = __fsub_rn(pz[g], mz);
+                                rg = __fadd_rn(rg, __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+                            }
+                        }
+                        rg = __fdiv_rn(rg, fg);
+                        if (rg < best) { best = rg; best_k = k; }
+                    }
+                    int kk = best_k;
+#pragma unroll
+                    for (int g = 0; g < SPRITE_MAX_GROUPS; g++)
+                        if (g < ng) { choice |= (uint32_t)(kk % ncopy[g]) << (4 * g); kk /= ncopy[g]; }
+                    v = sprite_rg2_of(P, s, seg0, nseg, seg_off, beads, seg_group, choice);       // all segments, chosen copies (:262-283)
+                }
+                cho[s] = choice;
+            }
+            val[s] = v; idx[s] = s < S ? s : 0x7fffffff;
+        }
+        __syncthreads();
+        // bitonic sort of (value, structure) ascending
+        for (int k = 2; k <= npow; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int t = threadIdx.x; t < npow; t += blockDim.x) {
+                    const int o = t ^ j;
+                    if (o > t) {
+                        const bool up = (t & k) == 0;
+                        const float a = val[t], b = val[o];
+                        const int ia = idx[t], ib = idx[o];
+                        const bool gt = a > b || (a == b && ia > ib);
+                        if (gt == up) { val[t] = b; val[o] = a; idx[t] = ib; idx[o] = ia; }
+                    }
+                }
+                __syncthreads();
+            }
+        for (int j = threadIdx.x; j < keep; j += blockDim.x) {
+            best_rg2[(size_t)c * keep + j] = val[j];
+            best_struct[(size_t)c * keep + j] = idx[j];
+        }
+        for (int q = threadIdx.x; q < nseg * keep; q += blockDim.x) {
+            const int i = q / keep, j = q % keep;
+            const uint32_t choice = cho[idx[j]];
+            best_beads[(size_t)(seg0 + i) * keep + j] = beads[seg_off[seg0 + i] + ((choice >> (4 * seg_group[seg0 + i])) & 15)];
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace igmk

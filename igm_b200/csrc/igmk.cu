@@ -470,6 +470,8 @@ extern "C" int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* 
         if (ex->bond_off && ex->bond_off[n_struct] > ex->bond_off[0] &&
             (!ex->bond_i || !ex->bond_j || !ex->bond_k || !ex->bond_r0 || !ex->bond_style))
             return fail("igmk_submit_population: NULL bond arguments in extras");
+        if (ex->atom_off && ex->atom_off[n_struct] > ex->atom_off[0] && (!ex->atom_xyz || !ex->atom_radius || !ex->atom_kind))
+            return fail("igmk_submit_population: NULL atom arguments in extras");
     }
     if (n_bead < 1 || n_bead > tmpl->n_atoms) return fail("igmk_submit_population: n_bead must be 1..tmpl->n_atoms");
     if (n_struct < 0 || s_begin < 0 || s_begin + n_struct > n_struct_total) return fail("igmk_submit_population: bad structure range");
@@ -531,13 +533,22 @@ extern "C" int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* 
                 ph->bond_ptr.reserve((size_t)(hi - lo) * (na + 1)); ph->bond_items.reserve(2 * nb);
                 ph->sub_bonds.reserve(nb); ph->sub_bond_atom_off.reserve(nb);
             }
+            std::vector<float> xrad; std::vector<uint8_t> xkind;
             for (int sl = lo; sl < hi; sl++) {
                 const int sg = s_begin + sl;
+                const int nx = (ex && ex->atom_off) ? (int)(ex->atom_off[sl + 1] - ex->atom_off[sl]) : 0;     // this structure's own particles
+                xyz.resize((size_t)(na + nx) * 3);
                 for (int a = 0; a < n_bead; a++) {
                     const float* src = crd + ((size_t)a * n_struct_total + sg) * 3;
                     xyz[3 * a] = src[0]; xyz[3 * a + 1] = src[1]; xyz[3 * a + 2] = src[2];
                 }
                 for (int a = n_bead; a < na; a++) { xyz[3 * a] = tmpl->xyz[3 * a]; xyz[3 * a + 1] = tmpl->xyz[3 * a + 1]; xyz[3 * a + 2] = tmpl->xyz[3 * a + 2]; }
+                if (nx > 0) {                          // e.g. the centroid particles of the SPRITE clusters assigned to this structure (sprite.py:57-58)
+                    const int64_t o = ex->atom_off[sl];
+                    memcpy(xyz.data() + (size_t)na * 3, ex->atom_xyz + o * 3, (size_t)nx * 3 * sizeof(float));
+                    xrad.assign(tmpl->radius, tmpl->radius + na); xrad.insert(xrad.end(), ex->atom_radius + o, ex->atom_radius + o + nx);
+                    xkind.assign(tmpl->kind, tmpl->kind + na); xkind.insert(xkind.end(), ex->atom_kind + o, ex->atom_kind + o + nx);
+                }
                 bi.assign(tmpl->bond_i, tmpl->bond_i + tmpl->n_bonds); bj.assign(tmpl->bond_j, tmpl->bond_j + tmpl->n_bonds);
                 bk.assign(tmpl->bond_k, tmpl->bond_k + tmpl->n_bonds); br.assign(tmpl->bond_r0, tmpl->bond_r0 + tmpl->n_bonds);
                 bs.assign(tmpl->bond_style, tmpl->bond_style + tmpl->n_bonds);
@@ -565,6 +576,7 @@ extern "C" int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* 
                     sys.env_abck = eabck.data(); sys.env_off = eoff.data(); sys.env_members = emem.data();
                 }
                 sys.xyz = xyz.data();
+                if (nx > 0) { sys.n_atoms = na + nx; sys.radius = xrad.data(); sys.kind = xkind.data(); }
                 sys.n_bonds = (int32_t)bi.size();
                 sys.bond_i = bi.data(); sys.bond_j = bj.data(); sys.bond_k = bk.data(); sys.bond_r0 = br.data(); sys.bond_style = bs.data();
                 sys.struct_id = tmpl->struct_id + sg;
@@ -1890,6 +1902,80 @@ extern "C" int igmk_pop_sprite_rg2(igmk_pop_t* p, int32_t n_clusters, const int3
     if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
     if (e == cudaSuccess) e = cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1);
     d_cl.release(); d_rg.release(); d_b.release(); d_ms.release(); d_v.release(); d_ci.release();
+    CU(e);
+    return 0;
+}
+
+extern "C" int igmk_pop_sprite_select(igmk_pop_t* p, int32_t n_clusters, const int32_t* cl_off, const int32_t* seg_off,
+                                      const int32_t* beads, const int32_t* seg_group, const int32_t* rep, int32_t keep,
+                                      float* best_rg2, int32_t* best_struct, int32_t* best_beads)
+{
+    if (!p) return fail("igmk_pop_sprite_select: NULL handle");
+    if (n_clusters == 0) return 0;
+    if (!cl_off || !seg_off || !beads || !seg_group || !rep || !best_rg2 || !best_struct || !best_beads)
+        return fail("igmk_pop_sprite_select: NULL argument");
+    if (cl_off[0] != 0 || seg_off[0] != 0) return fail("igmk_pop_sprite_select: offsets must start at 0");
+    if (keep < 1 || keep >= p->n_struct) return fail("igmk_pop_sprite_select: keep_best must be 1 .. n_struct - 1 (np.argpartition, SpriteAssignmentStep.py:148)");
+    if (p->n_struct > SPRITE_SORT_MAX) return fail("igmk_pop_sprite_select: more than 4096 structures");
+    if (!p->d_crd) return fail("igmk_pop_sprite_select: no coordinates uploaded or attached");
+    const int32_t n_seg = cl_off[n_clusters];
+    std::vector<int32_t> ngroups((size_t)n_clusters);
+    for (int c = 0; c < n_clusters; c++) {
+        if (cl_off[c + 1] <= cl_off[c]) return fail("igmk_pop_sprite_select: empty cluster");
+        int ng = 0;
+        for (int i = cl_off[c]; i < cl_off[c + 1]; i++) {
+            const int k = seg_off[i + 1] - seg_off[i];
+            if (k < 1 || k > 15) return fail("igmk_pop_sprite_select: a segment needs 1..15 copies");
+            if (seg_group[i] < 0 || seg_group[i] >= SPRITE_MAX_GROUPS) return fail("igmk_pop_sprite_select: more than 8 chromosomes in one cluster");
+            ng = std::max(ng, seg_group[i] + 1);
+        }
+        ngroups[c] = ng;
+        long long comb = 1;
+        for (int g = 0; g < ng; g++) {
+            const int r = rep[c * SPRITE_MAX_GROUPS + g];
+            if (r < 0 || r >= cl_off[c + 1] - cl_off[c] || seg_group[cl_off[c] + r] != g)
+                return fail("igmk_pop_sprite_select: representative segment does not belong to its group");
+            comb *= seg_off[cl_off[c] + r + 1] - seg_off[cl_off[c] + r];
+        }
+        if (comb > 65536) return fail("igmk_pop_sprite_select: more than 65536 copy combinations in one cluster");
+    }
+    const int32_t n_beads = seg_off[n_seg];
+    for (int i = 0; i < n_beads; i++)
+        if (beads[i] < 0 || beads[i] >= p->n_bead) return fail("igmk_pop_sprite_select: bead index out of range");
+    CU(cudaSetDevice(p->device));
+    DevBuf<int32_t> d_cl, d_so, d_b, d_sg, d_ng, d_rep, d_bs, d_bb; DevBuf<float> d_v;
+    cudaError_t e = d_cl.reserve(n_clusters + 1);
+    if (e == cudaSuccess) e = d_so.reserve(n_seg + 1);
+    if (e == cudaSuccess) e = d_b.reserve(std::max(n_beads, 1));
+    if (e == cudaSuccess) e = d_sg.reserve(n_seg);
+    if (e == cudaSuccess) e = d_ng.reserve(n_clusters);
+    if (e == cudaSuccess) e = d_rep.reserve((size_t)n_clusters * SPRITE_MAX_GROUPS);
+    if (e == cudaSuccess) e = d_v.reserve((size_t)n_clusters * keep);
+    if (e == cudaSuccess) e = d_bs.reserve((size_t)n_clusters * keep);
+    if (e == cudaSuccess) e = d_bb.reserve((size_t)n_seg * keep);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_cl.p, cl_off, (n_clusters + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_so.p, seg_off, (n_seg + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_b.p, beads, n_beads * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_sg.p, seg_group, n_seg * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_ng.p, ngroups.data(), n_clusters * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_rep.p, rep, (size_t)n_clusters * SPRITE_MAX_GROUPS * sizeof(int32_t), cudaMemcpyHostToDevice, p->stream);
+    int npow = 1;
+    while (npow < p->n_struct) npow <<= 1;
+    const size_t smem = (size_t)npow * 8 + (size_t)p->n_struct * 4;
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sprite_select, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaEventRecord(p->ev0, p->stream);
+    if (e == cudaSuccess) {
+        k_sprite_select<<<std::min<int>(n_clusters, p->sm_count * 4), 256, smem, p->stream>>>(
+            p->view(), n_clusters, d_cl.p, d_so.p, d_b.p, d_sg.p, d_ng.p, d_rep.p, keep, d_v.p, d_bs.p, d_bb.p);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaEventRecord(p->ev1, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(best_rg2, d_v.p, (size_t)n_clusters * keep * sizeof(float), cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(best_struct, d_bs.p, (size_t)n_clusters * keep * sizeof(int32_t), cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(best_beads, d_bb.p, (size_t)n_seg * keep * sizeof(int32_t), cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&p->last_ms, p->ev0, p->ev1);
+    d_cl.release(); d_so.release(); d_b.release(); d_sg.release(); d_ng.release(); d_rep.release(); d_v.release(); d_bs.release(); d_bb.release();
     CU(e);
     return 0;
 }

@@ -136,6 +136,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int np = K * MD2_T;
+    static_assert((size_t)np * 16 >= (size_t)MAX_CELLS * 4, "the cell cursors of the rebuild live in the cell-ordered copy");
     const StructDesc* d = B.desc + blockIdx.x;
     const Md2Desc md = mdesc[blockIdx.x];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -289,7 +290,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         __syncthreads();
         // drop atoms unordered behind the cell start, then sort each (tiny) cell by index so that the
         // row order, and with it the floating-point summation order, is independent of the race.
-        uint32_t* cursor = (uint32_t*)xbx;          // aliases the build coordinates, which are rewritten below
+        uint32_t* cursor = (uint32_t*)xsort;        // np * 16 bytes >= 4 * MAX_CELLS for every K; the cell-ordered copy is written later
         for (int c = tid; c < ncell; c += MD2_T) cursor[c] = 0;
         __syncthreads();
 #pragma unroll

@@ -195,10 +195,22 @@ class PopulationExtras(object):
 
     bonds: (off i8 [S+1], i i4, j i4, k f8, r0 f8, style u1) or None -- structure s owns entries off[s]..off[s+1];
     envelopes: list of (abck (a, b, c, k), bead ids i4 [n_rows], bits u4 [n_rows][ceil(S/32)]) -- bit s of row r set
-    means bead ids[r] belongs to the group in structure s (the matrix Population.damid_assign returns)."""
+    means bead ids[r] belongs to the group in structure s (the matrix Population.damid_assign returns);
+    atoms: (off i8 [S+1], xyz, radius, kind) -- particles a structure has on top of the template's (SPRITE centroids)."""
 
-    def __init__(self, n_struct, bonds=None, envelopes=()):
+    def __init__(self, n_struct, bonds=None, envelopes=(), atoms=None):
         self.n_struct = int(n_struct)
+        if atoms is not None:                      # (off i8 [S+1], xyz f4 [n][3], radius f4, kind u1): a structure's own particles
+            off, xyz, rad, kind = atoms
+            self.atom_off = np.ascontiguousarray(off, dtype=np.int64)
+            self.atom_xyz = np.ascontiguousarray(xyz, dtype=np.float32).reshape(-1, 3)
+            self.atom_radius = np.ascontiguousarray(rad, dtype=np.float32)
+            self.atom_kind = np.ascontiguousarray(kind, dtype=np.uint8)
+            if self.atom_off.size != self.n_struct + 1 or not (self.atom_xyz.shape[0] == self.atom_radius.size ==
+                                                                 self.atom_kind.size == int(self.atom_off[-1])):
+                raise ValueError("per-structure atom arrays are inconsistent")
+        else:
+            self.atom_off = None
         if bonds is not None:
             off, bi, bj, bk, br0, bs = bonds
             self.bond_off = np.ascontiguousarray(off, dtype=np.int64)
@@ -237,6 +249,13 @@ class PopulationExtras(object):
             ex.bond_k = self.bond_k.ctypes.data_as(_abi.c_f64p)
             ex.bond_r0 = self.bond_r0.ctypes.data_as(_abi.c_f64p)
             ex.bond_style = self.bond_style.ctypes.data_as(_abi.c_u8p)
+        if self.atom_off is not None:
+            aoff = np.ascontiguousarray(self.atom_off[s_begin:s_begin + n_struct + 1])
+            keep.append(aoff)
+            ex.atom_off = aoff.ctypes.data_as(_abi.c_i64p)
+            ex.atom_xyz = self.atom_xyz.ctypes.data_as(_abi.c_f32p)
+            ex.atom_radius = self.atom_radius.ctypes.data_as(_abi.c_f32p)
+            ex.atom_kind = self.atom_kind.ctypes.data_as(_abi.c_u8p)
         ex.n_env = int(self.env_abck.shape[0])
         if ex.n_env:
             if s_begin % 32:
@@ -247,6 +266,27 @@ class PopulationExtras(object):
             ex.env_bits = C.cast(self.env_bits.ctypes.data + 4 * (s_begin // 32), _abi.c_u32p)
             ex.env_bits_words = self._nw
         return ex, keep
+
+
+def merge_bond_lists(n_struct, *lists):
+    """several per-structure bond lists (off, i, j, k, r0, style) -> one, structure by structure in the order given
+    (ModelingStep.task adds Sprite before Fish, igm/steps/ModelingStep.py:285-330)"""
+    lists = [b for b in lists if b is not None]
+    if not lists:
+        return None
+    if len(lists) == 1:
+        return lists[0]
+    counts = np.sum([np.diff(b[0]) for b in lists], axis=0)
+    off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    out = [np.empty(int(off[-1]), dtype=np.asarray(lists[0][c]).dtype) for c in range(1, 6)]
+    cur = off[:-1].copy()
+    for b in lists:
+        n = np.diff(b[0])
+        dst = (np.repeat(cur, n) + (np.arange(int(n.sum())) - np.repeat(b[0][:-1], n))).astype(np.int64)
+        for c in range(5):
+            out[c][dst] = np.asarray(b[c + 1])
+        cur = cur + n
+    return (off,) + tuple(out)
 
 
 def info_from_result(res):

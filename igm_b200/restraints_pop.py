@@ -123,5 +123,5 @@ def damid_envelope(bead, bits, semiaxes, contact_range, k):
     return ((float(abc[0]), float(abc[1]), float(abc[2]), -float(k)), np.asarray(bead, dtype=np.int32), np.asarray(bits, dtype=np.uint32))
 
 
-def extras(n_struct, bonds=None, envelopes=()):
-    return PopulationExtras(n_struct, bonds=bonds, envelopes=envelopes)
+def extras(n_struct, bonds=None, envelopes=(), atoms=None):
+    return PopulationExtras(n_struct, bonds=bonds, envelopes=envelopes, atoms=atoms)

@@ -178,6 +178,13 @@ typedef struct igmk_pop_extras {
     const int32_t*  env_bead;
     const uint32_t* env_bits;
     int32_t         env_bits_words;
+    /* particles of a structure's own, appended after the template's atoms: structure k gets atom_xyz / atom_radius /
+     * atom_kind[atom_off[k] .. atom_off[k+1]) as atoms tmpl->n_atoms, tmpl->n_atoms + 1, ... (SPRITE: one DUMMY_DYNAMIC
+     * centroid per cluster assigned to the structure, igm/restraints/sprite.py:52-65; its bonds come through bond_*) */
+    const int64_t*  atom_off;       /* [n_struct + 1] or NULL */
+    const float*    atom_xyz;       /* [..][3] */
+    const float*    atom_radius;
+    const uint8_t*  atom_kind;      /* IGMK_KIND_* */
 } igmk_pop_extras_t;
 int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* tmpl, int32_t n_bead,
                               int32_t n_struct_total, int32_t s_begin, int32_t n_struct, const float* crd,
@@ -403,6 +410,21 @@ int igmk_pop_fish_ranks(igmk_pop_t* p, int64_t n_items, const int32_t* hap_i, co
  */
 int igmk_pop_sprite_rg2(igmk_pop_t* p, int32_t n_clusters, const int32_t* cl_off, const int32_t* rg_off,
                         const int32_t* beads, float* rg2, int8_t* copy_idx, int32_t* min_struct);
+
+/*
+ * SPRITE A-step for a batch of clusters: compute_gyration_radius (igm/cython_compiled/sprite.pyx:104-283) followed by
+ * the keep-best selection of SpriteAssignmentStep.task (igm/steps/SpriteAssignmentStep.py:148-160).  Cluster c has the
+ * segments cl_off[c]..cl_off[c+1] (haploid ids in ascending order, i.e. grouped by chromosome); segment i has the
+ * copies beads[seg_off[i]..seg_off[i+1]) and belongs to chromosome group seg_group[i] (0.. within its cluster, at most
+ * 8); rep[c][g] = the representative segment (position within the cluster) on which the copy of group g is chosen --
+ * the reference draws it with np.random.choice (:222-223), here the caller does, so that a run can be replayed.
+ * Outputs per cluster: the `keep` structures with the smallest squared radius of gyration in ascending order
+ * (best_rg2, best_struct: [n_clusters][keep]) and, per segment, the bead selected in each of them
+ * (best_beads [n_segments][keep]).  float32 arithmetic in the reference's order: bit-identical values.
+ */
+int igmk_pop_sprite_select(igmk_pop_t* p, int32_t n_clusters, const int32_t* cl_off, const int32_t* seg_off,
+                           const int32_t* beads, const int32_t* seg_group, const int32_t* rep /* [n_clusters][8] */,
+                           int32_t keep, float* best_rg2, int32_t* best_struct, int32_t* best_beads);
 
 #ifdef __cplusplus
 }

@@ -62,3 +62,50 @@ def reference_get_rgs2():
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod.get_rgs2
+
+
+def reduce_assignment(rg2_values, structure_indexes, n_struct, batch_size, kT, seed):
+    """SpriteAssignmentStep.reduce (igm/steps/SpriteAssignmentStep.py:176-272) statement by statement on in-memory batch
+    results, drawing from the GLOBAL numpy state like the reference (seeded here so that it can be replayed).
+    -> (assignment, pos)"""
+    np.random.seed(seed)
+    n_clusters = len(rg2_values)
+    n_batches = n_clusters // batch_size + (1 if n_clusters % batch_size != 0 else 0)
+    random_order = np.random.permutation(range(n_batches))
+    occupancy = np.zeros(n_struct, dtype=np.int32)
+    assignment = np.zeros(n_clusters, dtype=np.int32)
+    positions = np.zeros(n_clusters, dtype=np.int32)
+    aveN = float(n_clusters) / n_struct
+    stdN = np.sqrt(aveN)
+    for batch_id in random_order:
+        lo = batch_id * batch_size
+        results = zip(rg2_values[lo:lo + batch_size], structure_indexes[lo:lo + batch_size])
+        for i, (best_rg2s, curr_idx) in enumerate(results):
+            ci = i + batch_id * batch_size
+            if best_rg2s[0] < 0:
+                pos = 0
+                si = -1
+            else:
+                best_rgs = np.sqrt(best_rg2s)
+                structure_penalizations = np.clip(occupancy[curr_idx] - aveN, 0., None) / stdN
+                E = (best_rgs - best_rgs[0]) / kT + structure_penalizations
+                P = np.cumsum(np.exp(-(E - E[0])))
+                Z = P[-1]
+                e = np.random.rand() * Z
+                pos = np.searchsorted(P, e, side='left')
+                si = curr_idx[pos]
+                occupancy[si] += 1
+            assignment[ci] = si
+            positions[ci] = pos
+    return assignment, positions
+
+
+def reference_module():
+    """the reference's compiled Cython module (get_rgs2, compute_gyration_radius), or None"""
+    so = glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "sprite*.so"))
+    if not so:
+        return None
+    spec = importlib.util.spec_from_file_location("sprite", so[0])
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod

@@ -73,6 +73,25 @@ def main():
             rows.append((style, f.i, f.j, f.d, f.k))
         out["fish_forces_%d" % s] = np.array(rows, dtype=np.float64)
         out["dummies_%d" % s] = np.array([k for k, p in enumerate(model.particles) if p.ptype == Particle.DUMMY_STATIC])
+    # ---- Sprite._apply (igm/restraints/sprite.py:41-69): centroids + bead-centroid bonds of the clusters assigned to a structure
+    from igm.restraints import Sprite
+    rng = np.random.default_rng(5)
+    n_cl = 40
+    sizes = 2 + rng.geometric(0.3, n_cl)
+    indptr = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    selected = np.concatenate([rng.choice(n_bead, int(k), replace=False) for k in sizes]).astype(np.int32)
+    assignment = rng.choice(np.array(structs + [7, 8]), n_cl).astype(np.int32)
+    refstub.FAKE_FILES["golden_sprite_assignment"] = {"assignment": assignment, "indptr": indptr, "selected": selected}
+    out.update(sprite_assignment=assignment, sprite_indptr=indptr, sprite_selected=selected, sprite_volume_occupancy=0.05, sprite_k=1.7)
+    for s in structs:
+        model = Model(uid=s)
+        for b in range(n_bead):
+            model.addParticle(crd[b, s], rad[b], Particle.NORMAL)
+        model.addRestraint(Sprite("golden_sprite_assignment", 0.05, s, k=1.7))
+        out["sprite_forces_%d" % s] = np.array([(f.i, f.j, f.d, f.k) for f in model.forces], dtype=np.float64).reshape(-1, 4)
+        cen = [p for p in model.particles if p.ptype == Particle.DUMMY_DYNAMIC]
+        out["sprite_centroids_%d" % s] = np.array([p.pos for p in cen], dtype=np.float32).reshape(-1, 3)
+        assert all(isinstance(f, HarmonicUpperBound) for f in model.forces)
     np.savez_compressed(os.path.join(HERE, "restraints_golden.npz"), **out)
     print("restraints golden: %d FISH forces per structure, DamID members %s"
           % (out["fish_forces_0"].shape[0], [out["damid_members_%d" % s].size for s in structs]))

@@ -82,3 +82,43 @@ def test_subset_of_restraint_types_and_empty(astep_golden, rg):
     assert off[1] == 3 * len(rg["probes"]) and set(bi.tolist()) == {702}
     env = rp.damid_envelope([1, 2, 3], np.zeros((3, 1), dtype=np.uint32), (5000.0, 4000.0, 3000.0), 0.05, 0.3)
     assert env[0] == (4750.0, 3800.0, 2850.0, -0.3)
+
+
+def test_sprite_centroids_and_bonds_equal_the_reference(astep_golden, rg):
+    """Sprite._apply (igm/restraints/sprite.py:41-69) for a block of structures against the reference's own Model"""
+    from igm_b200 import sprite
+    g = astep_golden
+    crd = np.ascontiguousarray(g["coordinates"])
+    n_bead = crd.shape[0]
+    indptr, sel = rg["sprite_indptr"], rg["sprite_selected"]
+    beads = [sel[indptr[c]:indptr[c + 1]] for c in range(len(indptr) - 1)]
+    atoms, bonds = sprite.centroid_restraints(crd, g["radii"], rg["sprite_assignment"], beads, 0, n_bead,
+                                              float(rg["sprite_volume_occupancy"]), float(rg["sprite_k"]))
+    aoff, xyz, arad, akind = atoms
+    boff, bi, bj, bk, br0, bs = bonds
+    for s in rg["structs"]:
+        s = int(s)
+        want_f, want_c = rg["sprite_forces_%d" % s], rg["sprite_centroids_%d" % s]
+        assert np.array_equal(xyz[aoff[s]:aoff[s + 1]].view(np.uint32), want_c.view(np.uint32))
+        sl = slice(boff[s], boff[s + 1])
+        got = np.stack([bi[sl], bj[sl], br0[sl], bk[sl]], axis=1).astype(np.float64)
+        assert np.array_equal(got, want_f)
+        assert (akind[aoff[s]:aoff[s + 1]] == 2).all() and (arad[aoff[s]:aoff[s + 1]] == 0).all() and (bs[sl] == 0).all()
+    assert aoff[-1] == np.isin(rg["sprite_assignment"], np.arange(crd.shape[1])).sum()
+
+
+def test_gibbs_assignment_replays_the_reference_random_stream():
+    """SpriteAssignmentStep.reduce (:176-272) draws from the global numpy state; assign_clusters takes a RandomState and
+    must consume it with the same calls in the same order: np.random.seed(k) + the restatement == RandomState(k) + product"""
+    from igm_b200 import sprite
+    from oracle import sprite_oracle as so
+    rng = np.random.default_rng(3)
+    n_cl, keep, S = 137, 12, 40
+    rg2 = np.sort(rng.uniform(100.0, 5e5, (n_cl, keep)).astype(np.float32), axis=1)
+    idx = np.stack([rng.choice(S, keep, replace=False) for _ in range(n_cl)]).astype(np.int32)
+    rg2[[5, 77]] = -1.0; idx[[5, 77]] = -1                                         # clusters skipped by the A-step
+    for seed, bs, kT in ((1, 10, 100.0), (9, 7, 30.0)):
+        want = so.reduce_assignment(rg2, idx, S, bs, kT, seed)
+        got = sprite.assign_clusters(rg2, idx, S, np.random.RandomState(seed), batch_size=bs, kT=kT)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        assert got[0][5] == -1 and np.bincount(got[0][got[0] >= 0], minlength=S).max() <= 12
