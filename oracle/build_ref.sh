@@ -19,6 +19,19 @@ if [ -f "$DEMO/WTC11_HiC_2Mb.hcs" ]; then
         [ -f "$OUT/demo/$(basename "$f")" ] || cp "$f" "$OUT/demo/"
     done
 fi
+# The pure-Python data model of the reference (igm/model, igm/restraints, igm/utils/log.py) for the test that drives the
+# b200 kernel through the REAL Model / Particle / Force / Restraint classes on the GPU box (tests/test_gpu_real_classes.py).
+# Staged copies, git-ignored like everything under oracle/_ref; the package __init__ files written here are empty so that
+# nothing else of igm is imported.
+SRC=${IGM_REFERENCE_ROOT:-/root/reference}/igm
+if [ -d "$SRC/model" ] && [ ! -f "$OUT/igm_py/igm/model/model.py" ]; then
+    mkdir -p "$OUT/igm_py/igm/model" "$OUT/igm_py/igm/restraints" "$OUT/igm_py/igm/utils"
+    cp "$SRC/model/__init__.py" "$SRC/model/model.py" "$SRC/model/particle.py" "$SRC/model/forces.py" "$OUT/igm_py/igm/model/"
+    cp "$SRC"/restraints/*.py "$OUT/igm_py/igm/restraints/"
+    cp "$SRC/utils/log.py" "$OUT/igm_py/igm/utils/"
+    : > "$OUT/igm_py/igm/__init__.py"
+    : > "$OUT/igm_py/igm/utils/__init__.py"
+fi
 TMP=$(mktemp -d)
 PY=${PYTHON:-python}
 EXT=$($PY -c "import sysconfig; print(sysconfig.get_config_var('EXT_SUFFIX'))")

@@ -121,3 +121,19 @@ def import_reference():
     import igm
     igm.cython_compiled = pkg
     return igm
+
+
+def import_staged(root):
+    """Import the staged pure-Python part of the reference (igm.model, igm.restraints; oracle/build_ref.sh copies it to
+    oracle/_ref/igm_py) with the h5py stand-in above -- what the GPU box has instead of /root/reference."""
+    import os
+    if "igm" in sys.modules:
+        return sys.modules["igm"]
+    h5py = types.ModuleType("h5py")
+    h5py.File = _FakeH5File
+    sys.modules["h5py"] = h5py
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    import igm.model          # noqa: F401
+    import igm.restraints     # noqa: F401
+    return sys.modules["igm"]
