@@ -49,6 +49,7 @@ def parse_args():
                     help="write the first %d structures of the workload (M-step inputs: coordinates + assigned Hi-C bonds) to this "
                          ".npz; commit it as tests/golden/bench_c2_structures.npz" % N_FIXTURE)
     ap.add_argument("--no-plugin", action="store_true", help="skip the e2e_plugin leg (B200Controller + optimize(model, cfg))")
+    ap.add_argument("--no-extra", action="store_true", help="skip the configs[2] / configs[3] iterations (tools/bench_configs.py)")
     return ap.parse_args()
 
 
@@ -694,6 +695,19 @@ def main():
                 line["astep"]["cpu_baseline"] = cpu_astep_baseline(wl)
             except Exception as e:          # the A-step baseline must never cost the bench line
                 line["astep"]["cpu_baseline"] = {"error": repr(e)}
+        if world == 1 and not args.no_extra:
+            # BASELINE configs[2] and configs[3] at their genome sizes on a reduced number of structures (tools/bench_configs.py)
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            line["extra_configs"] = {}
+            try:
+                import bench_configs
+                for name, fn in (("c3", bench_configs.run_c3), ("c4", bench_configs.run_c4)):
+                    try:
+                        line["extra_configs"][name] = fn(device)
+                    except Exception as e:                      # never at the cost of the headline line
+                        line["extra_configs"][name] = {"error": repr(e)}
+            except Exception as e:
+                line["extra_configs"] = {"error": repr(e)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

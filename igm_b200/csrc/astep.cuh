@@ -88,6 +88,7 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
     __shared__ uint32_t s_hist[2][AD_THREADS], s_wsum[2][AD_THREADS / 32], s_pick[2][3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = P.n_struct;
+    const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(P.crd) & 15) == 0;     // whole groups of four, 16-byte aligned rows
     if (tid < AD_THREADS) { s_hist[0][tid] = 0; s_hist[1][tid] = 0; }   // radix_pick leaves them zeroed again
     __syncthreads();
 
@@ -114,15 +115,40 @@ k_actdist(PopView P, int64_t n_pairs, const int32_t* __restrict__ pair_i, const 
             const int bj = P.copy_beads[jo + (intra ? c : c % nj)];
             const float* xi = P.crd + (size_t)bi * S * 3;
             const float* xj = P.crd + (size_t)bj * S * 3;
-            for (int s = tid; s < S; s += NT) {
-                const float dx = __fsub_rn(xi[3 * s], xj[3 * s]);
-                const float dy = __fsub_rn(xi[3 * s + 1], xj[3 * s + 1]);
-                const float dz = __fsub_rn(xi[3 * s + 2], xj[3 * s + 2]);
-                const float v = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-                dsq[c * S + s] = v;
-                cnt += (v <= rcutsq);
-                const uint32_t k = fkey(v);
-                kmin = min(kmin, k); kmax = max(kmax, k);
+            if (vec) {
+                // four structures at a time: 12 consecutive floats of either bead row = three 16-byte loads each
+                // (a warp reads 1.5 KB contiguous per row), one 16-byte store of the four squared distances
+                const float4* ri4 = reinterpret_cast<const float4*>(xi);
+                const float4* rj4 = reinterpret_cast<const float4*>(xj);
+                for (int g4 = tid; g4 < (S >> 2); g4 += NT) {
+                    const float4 a0 = __ldg(ri4 + 3 * g4), a1 = __ldg(ri4 + 3 * g4 + 1), a2 = __ldg(ri4 + 3 * g4 + 2);
+                    const float4 b0 = __ldg(rj4 + 3 * g4), b1 = __ldg(rj4 + 3 * g4 + 1), b2 = __ldg(rj4 + 3 * g4 + 2);
+                    const float pa[12] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w};
+                    const float pb[12] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y, b2.z, b2.w};
+                    float v[4];
+#pragma unroll
+                    for (int w = 0; w < 4; w++) {
+                        const float dx = __fsub_rn(pa[3 * w], pb[3 * w]);
+                        const float dy = __fsub_rn(pa[3 * w + 1], pb[3 * w + 1]);
+                        const float dz = __fsub_rn(pa[3 * w + 2], pb[3 * w + 2]);
+                        v[w] = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                        cnt += (v[w] <= rcutsq);
+                        const uint32_t k = fkey(v[w]);
+                        kmin = min(kmin, k); kmax = max(kmax, k);
+                    }
+                    *reinterpret_cast<float4*>(dsq + c * S + 4 * g4) = make_float4(v[0], v[1], v[2], v[3]);
+                }
+            } else {
+                for (int s = tid; s < S; s += NT) {
+                    const float dx = __fsub_rn(xi[3 * s], xj[3 * s]);
+                    const float dy = __fsub_rn(xi[3 * s + 1], xj[3 * s + 1]);
+                    const float dz = __fsub_rn(xi[3 * s + 2], xj[3 * s + 2]);
+                    const float v = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                    dsq[c * S + s] = v;
+                    cnt += (v <= rcutsq);
+                    const uint32_t k = fkey(v);
+                    kmin = min(kmin, k); kmax = max(kmax, k);
+                }
             }
         }
 #pragma unroll

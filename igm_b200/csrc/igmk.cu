@@ -721,6 +721,7 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
         const int32_t* bp = h->bond_ptr.data() + d.bond_ptr_off;
         const uint32_t* bi = h->bond_items.data() + d.bond_item_off;
         const bool a_ok = h->btype_f[d.btype_off].y > 0.f;              // type 0 is an upper bound: block A may be used
+        const uint8_t* kindp = h->kind.data() + d.atom_off;
         // ---- orientation: the owner is the end that owns fewer items so far; the other end must have a free inbox slot ----
         struct Own { int32_t other; uint32_t type; int8_t q; };         // q < 0: SYM
         std::vector<std::vector<Own>> rows((size_t)n);
@@ -732,6 +733,15 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
                 if (b <= a) continue;                                   // every bond once (b == a: a bond to oneself has no force)
                 if (t >= MAXT) { errs[s] = "too many distinct bond types in one structure for the MD kernel's item format"; return; }
                 nbond[s]++;
+                // a frozen particle (the static centre of an Envelope / Damid / Fish restraint, hundreds of bonds in a FISH run)
+                // discards its force: the bond lives at the moving end only, without inbox (SYM item); a thread that owned
+                // all bonds of such a hub would walk them alone, one dependent load after the other
+                const bool fa = kindp[a] == IGMK_KIND_STATIC, fb = kindp[b] == IGMK_KIND_STATIC;
+                if (fa || fb) {
+                    if (!fa) { rows[a].push_back({b, t, -1}); own[a]++; }
+                    if (!fb) { rows[b].push_back({a, t, -1}); own[b]++; }
+                    continue;
+                }
                 const int da = bp[a + 1] - bp[a], db = bp[b + 1] - bp[b];
                 int o = (own[a] < own[b] || (own[a] == own[b] && da >= db)) ? a : b, r = o == a ? b : a;
                 if (indeg[r] >= MD2_INBOX - 1) std::swap(o, r);
