@@ -552,12 +552,28 @@ def main():
     t0 = time.perf_counter()
     for _ in range(args.steps):
         out = run_population(wl["template"], crd, len(g), row, col, r0_all, 1.0, wl["bits"], prot, device=device, seeds=wl["seeds"])
+        h2d_host = out[3]["h2d_bytes"]
+    torch.cuda.synchronize(device)
+    e2e_host_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    if not all(r.status == 0 for r in out[1]):
+        raise RuntimeError("bench: a structure of the end-to-end pass came back non-finite")
+    host_crd = out[0]
+    del out
+    # ---- e2e, hand-off on the device (igm_b200.iteration.mstep_population): coordinates and actdist rows from host
+    #      buffers every step, assignment + assembly + optimisation on the GPU, coordinates back ----
+    from igm_b200.iteration import mstep_population
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = mstep_population(crd, g, rad, wl["template"], row, col, dst, prot, device=device, seeds=wl["seeds"])
         h2d = out[3]["h2d_bytes"]
     torch.cuda.synchronize(device)
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
     if not all(r.status == 0 for r in out[1]):
         raise RuntimeError("bench: a structure of the end-to-end pass came back non-finite")
-    del out
+    e2e_same = bool(np.array_equal(out[0].view(np.uint32), host_crd.view(np.uint32)))
+    e2e_dev_chunks = out[3].get("assembled_on_device", 0)
+    del out, host_crd
     # ---- one full A/M iteration from host coordinates: upload -> all-gather -> activation distances
     #      (this rank's pair chunk) -> gather rows -> assignment -> bond build + submit -> M-step -> fetch ----
     from igm_b200.iteration import hic_iteration
@@ -584,11 +600,11 @@ def main():
 
     tt = torch.tensor([ms_step, e2e_ms, wl["astep"]["actdist_kernel_ms"], wl["astep"]["actdist_e2e_ms"],
                        wl["astep"]["assign_kernel_ms"], wl["astep"]["assign_e2e_ms"], iter_s, t_astep, t_build, ns_s, ns_a, ns_m,
-                       plug_s or 0.0],
+                       plug_s or 0.0, e2e_host_ms],
                       dtype=torch.float64, device="cuda:%d" % device)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_step, e2e_ms, ad_k, ad_e, as_k, as_e, iter_s, t_astep, t_build, ns_s, ns_a, ns_m, plug_s = [float(v) for v in tt.tolist()]
+    ms_step, e2e_ms, ad_k, ad_e, as_k, as_e, iter_s, t_astep, t_build, ns_s, ns_a, ns_m, plug_s, e2e_host_ms = [float(v) for v in tt.tolist()]
     if rank == 0:
         peaks = {}
         try:
@@ -626,7 +642,15 @@ def main():
             "workload_stats": {"sigma": a["sigma"], "pairs_kept": a["pairs_total"], "hic_bonds_per_structure": a["hic_bonds_per_structure"],
                                "cg_evals_mean": cg_evals, "fixture_check": wl["fixture_check"]},
             "e2e": {"value": S * world / (e2e_ms * 1e-3), "unit": "structures/s", "h2d_bytes_per_step": int(h2d),
-                    "d2h_bytes_per_step": int(d2h)},
+                    "d2h_bytes_per_step": int(d2h),
+                    "what": "igm_b200.iteration.mstep_population per step: coordinates + actdist rows from host buffers, contact "
+                            "assignment, assembly of every structure on the device (igmk_submit_population_dev), annealing MD + CG, "
+                            "coordinates back to the host",
+                    "chunks_assembled_on_device": int(e2e_dev_chunks), "bit_identical_to_host_assembly": e2e_same},
+            "e2e_host_assembly": {"value": S * world / (e2e_host_ms * 1e-3), "unit": "structures/s", "h2d_bytes_per_step": int(h2d_host),
+                                  "d2h_bytes_per_step": int(d2h),
+                                  "what": "igm_b200.kernel.run_population with the assignment bit matrix on the host: structures "
+                                          "assembled by igmk_submit_population on the host threads (round-1 path)"},
             "e2e_plugin": None if args.no_plugin else {
                 "value": plug_n * world / plug_s, "unit": "structures/s", "structures": plug_n, "seconds": plug_s, "launches": plug_batches,
                 "what": "B200Controller.map over one task per structure, each calling igm_b200.kernel.optimize(model, cfg) on a "
@@ -637,7 +661,7 @@ def main():
             "am_iteration": {"seconds": iter_s, "structures_per_s": S * world / iter_s, "astep_seconds": t_astep,
                              "mstep_seconds": t_build,
                              "what": "host coordinates -> upload, all-gather, activation distances, row gather, assignment, "
-                                     "bond build + submit, annealing MD + CG, coordinates back on the host"},
+                                     "assembly on the device, annealing MD + CG, coordinates back on the host"},
             "am_iteration_north_star": {"seconds": ns_s, "structures": ns_S * world, "structures_per_gpu": ns_S, "astep_seconds": ns_a,
                                         "mstep_seconds": ns_m,
                                         "what": "the same iteration with 1000 / n_gpus structures per GPU: north_star's 'full 2 Mb "

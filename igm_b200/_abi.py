@@ -237,6 +237,9 @@ _SIGNATURES = {
     "igmk_pop_set_rows": (C.c_int, [_vp, C.c_int64, c_i32p, c_i32p, c_f32p]),
     "igmk_pop_assign_launch": (C.c_int, [_vp]),
     "igmk_pop_assign_collect": (C.c_int, [_vp, c_u32p]),
+    "igmk_pop_set_row_bounds": (C.c_int, [_vp, C.c_int64, c_f64p, C.c_double]),
+    "igmk_submit_population_dev": (C.c_int, [_vp, C.POINTER(System), _vp, C.c_int32, C.c_int32, c_i64p, c_i32p]),
+    "igmk_debug_fetch_array": (C.c_int, [_vp, C.c_int32, _vp, C.c_int64, c_i64p]),
 }
 
 

@@ -169,6 +169,13 @@ class Population(object):
     def assign_launch(self):
         _abi.check(self._lib.igmk_pop_assign_launch(self._p), "igmk_pop_assign_launch")
 
+    def set_row_bounds(self, row_r0, row_k):
+        """bound distance of every staged row (contact_range * (r_i + r_j), inter_hic.py:55) and the spring constant,
+        for the device-side hand-off to the M-step (MStepBatch.submit_population_device)"""
+        r0 = np.ascontiguousarray(row_r0, dtype=np.float64)
+        _abi.check(self._lib.igmk_pop_set_row_bounds(self._p, r0.size, r0.ctypes.data_as(_abi.c_f64p), float(row_k)),
+                   "igmk_pop_set_row_bounds")
+
     def assign_collect(self):
         nw = (self.n_struct + 31) // 32
         bits = np.zeros((self._n_rows, nw), dtype=np.uint32)

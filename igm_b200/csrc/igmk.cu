@@ -22,6 +22,7 @@
 #include "md_cluster.cuh"
 #include "astep.cuh"
 #include "astep_shard.cuh"
+#include "assemble.cuh"
 #include "probe.cuh"
 
 using namespace igmk;
@@ -104,6 +105,15 @@ struct igmk_handle {
     double* d_md2_dbg = nullptr;
     bool md_big = false; float* d_big_state = nullptr; double* d_big = nullptr;
     bool dirty = true;
+    // batch assembled on the device (igmk_submit_population_dev, assemble.cuh): the host vectors above hold desc / struct_id /
+    // xyzr only; the bond list stays on the device
+    bool dev_built = false;
+    std::vector<int32_t> dev_nb;                       // bonds per structure
+    std::vector<double> dev_env_abck; std::vector<int32_t> dev_env_off, dev_env_mem;   // the template's envelopes (violation report)
+    unsigned char* d_asm_blob = nullptr; int32_t* d_asm_cnt = nullptr;
+    int32_t* d_asm_bl = nullptr; int32_t* d_asm_csr = nullptr; uint8_t* d_asm_dec = nullptr; uint16_t* d_asm_atom = nullptr;
+    const double* d_asm_key_r0 = nullptr; const double* d_asm_key_k = nullptr; const int32_t* d_asm_key_style = nullptr;
+    int64_t dev_bonds = 0;
     // device
     StructDesc* d_desc = nullptr; float4* d_xyzr = nullptr; float4* d_xyzr0 = nullptr; uint8_t* d_kind = nullptr; uint32_t* d_envmask = nullptr;
     int32_t* d_bond_ptr = nullptr; uint32_t* d_bond_items = nullptr; float2* d_btype_f = nullptr; double2* d_btype_d = nullptr;
@@ -125,6 +135,8 @@ struct igmk_handle {
         cudaFree(d_big_state); cudaFree(d_big); d_big_state = nullptr; d_big = nullptr;
         cudaFree(d_md2_desc); cudaFree(d_md2_perm); cudaFree(d_md2_ell_off); cudaFree(d_md2_ell_items); cudaFree(d_md2_ell_act); cudaFree(d_md2_nl); d_md2_ell_act = nullptr;
         cudaFree(d_md2_eblk); cudaFree(d_md2_gf); cudaFree(d_md2_dbg);
+        cudaFree(d_asm_blob); cudaFree(d_asm_cnt); cudaFree(d_asm_bl); cudaFree(d_asm_csr); cudaFree(d_asm_dec); cudaFree(d_asm_atom);
+        d_asm_blob = nullptr; d_asm_cnt = nullptr; d_asm_bl = nullptr; d_asm_csr = nullptr; d_asm_dec = nullptr; d_asm_atom = nullptr;
         d_md2_eblk = nullptr; d_md2_gf = nullptr; d_md2_dbg = nullptr;
         cudaFree(d_mdc_xall); cudaFree(d_mdc_xsorted); cudaFree(d_mdc_sorted); cudaFree(d_mdc_cells); cudaFree(d_mdc_rowlen); cudaFree(d_mdc_bbox);
         d_mdc_xall = nullptr; d_mdc_xsorted = nullptr; d_mdc_sorted = nullptr; d_mdc_cells = nullptr; d_mdc_rowlen = nullptr; d_mdc_bbox = nullptr;
@@ -206,12 +218,14 @@ extern "C" int igmk_clear(igmk_handle_t* h)
     h->viol_valid = false;
     h->res.clear(); h->flags.clear(); h->forces.clear();
     h->max_atoms = 0; h->dirty = true; h->have_forces = false;
+    h->dev_built = false; h->dev_nb.clear(); h->dev_bonds = 0;
     return 0;
 }
 
 extern "C" int igmk_submit(igmk_handle_t* h, const igmk_system_t* s, int32_t* slot_out)
 {
     if (!h || !s) return fail("igmk_submit: NULL argument");
+    if (h->dev_built) return fail("igmk_submit: this batch was assembled on the device; igmk_clear it first");
     char msg[256];
     const int n = s->n_atoms;
     if (n <= 0 || n > 65534) {
@@ -837,10 +851,13 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
     for (auto& th : pool) th.join();
 }
 
+static int upload_dev_rebuild(igmk_handle* h);
+
 static int upload(igmk_handle* h)
 {
     if (h->device < 0) return fail("igmk: this handle was created with IGMK_STAGING_ONLY and cannot touch a GPU");
     if (!h->dirty) return 0;
+    if (h->dev_built) return upload_dev_rebuild(h);
     h->free_device();
     const size_t na = h->xyzr.size(), ns = h->desc.size();
     CU(dev_alloc_copy(&h->d_desc, h->desc, h->stream));
@@ -941,6 +958,7 @@ extern "C" int igmk_layout_stats(igmk_handle_t* h, int32_t* slots_per_thread, in
 {
     if (!h) return fail("igmk_layout_stats: NULL handle");
     if (h->desc.empty()) return fail("igmk_layout_stats: nothing submitted");
+    if (h->dev_built) return fail("igmk_layout_stats: not available for a batch assembled on the device");
     int K = md2_pick_K(h->max_atoms);
     if (K == 0) K = (h->max_atoms + MD2_T - 1) / MD2_T;           // global-memory path (md_big.cuh): same layout, more slots
     const int keep_K = h->md2_K;
@@ -963,6 +981,11 @@ extern "C" int igmk_slot_sizes(igmk_handle_t* h, int32_t slot, int32_t* n_atoms,
     if (slot < 0 || slot >= (int)h->desc.size()) return fail("igmk_slot_sizes: bad slot");
     const bool last = slot + 1 >= (int)h->desc.size();
     if (n_atoms) *n_atoms = h->desc[slot].n_atoms;
+    if (h->dev_built) {
+        if (n_bonds) *n_bonds = h->dev_nb[slot];
+        if (n_env_members) *n_env_members = h->dev_env_off.empty() ? 0 : h->dev_env_off.back();
+        return 0;
+    }
     if (n_bonds) *n_bonds = (last ? (int64_t)h->sub_bonds.size() : h->sub_bond_start[slot + 1]) - h->sub_bond_start[slot];
     if (n_env_members) *n_env_members = (last ? (int64_t)h->sub_env.size() : h->sub_env_start[slot + 1]) - h->sub_env_start[slot];
     return 0;
@@ -977,11 +1000,39 @@ extern "C" int igmk_violation_ratios(igmk_handle_t* h, int32_t slot, double* bon
     CU(cudaSetDevice(h->device));
     if (!h->viol_valid) {
         if (int rc = upload(h)) return rc;
-        const int64_t nb = (int64_t)h->sub_bonds.size(), ne = (int64_t)h->sub_env.size();
+        if (h->dev_built && h->sub_env_start.empty()) {       // envelope members of a device-assembled batch: the template's, per structure
+            for (size_t s = 0; s < h->desc.size(); s++) {
+                h->sub_env_start.push_back((int64_t)h->sub_env.size());
+                for (size_t e = 0; e + 1 < h->dev_env_off.size(); e++)
+                    for (int q = h->dev_env_off[e]; q < h->dev_env_off[e + 1]; q++) {
+                        EnvMember m;
+                        m.atom = h->desc[s].atom_off + h->dev_env_mem[q]; m.pad = 0;
+                        m.a = h->dev_env_abck[4 * e]; m.b = h->dev_env_abck[4 * e + 1]; m.c = h->dev_env_abck[4 * e + 2]; m.k = h->dev_env_abck[4 * e + 3];
+                        h->sub_env.push_back(m);
+                    }
+            }
+        }
+        const int64_t nb = h->dev_built ? h->dev_bonds : (int64_t)h->sub_bonds.size(), ne = (int64_t)h->sub_env.size();
         h->viol_bond.assign((size_t)nb, 0.0); h->viol_env.assign((size_t)ne, 0.0);
         SubBond* d_b = nullptr; int32_t* d_o = nullptr; EnvMember* d_e = nullptr; double* d_r = nullptr;
-        cudaError_t e = dev_alloc_copy(&d_b, h->sub_bonds, h->stream);
-        if (e == cudaSuccess) e = dev_alloc_copy(&d_o, h->sub_bond_atom_off, h->stream);
+        cudaError_t e = cudaSuccess;
+        if (h->dev_built) {                                   // the bond list never left the device
+            int64_t* d_start = nullptr;
+            e = cudaMalloc((void**)&d_b, (size_t)std::max<int64_t>(nb, 1) * sizeof(SubBond));
+            if (e == cudaSuccess) e = cudaMalloc((void**)&d_o, (size_t)std::max<int64_t>(nb, 1) * sizeof(int32_t));
+            if (e == cudaSuccess) e = dev_alloc_copy(&d_start, h->sub_bond_start, h->stream);
+            if (e == cudaSuccess && nb > 0) {
+                k_asm_sub_bonds<<<(int)std::min<int64_t>((nb + 255) / 256, 148 * 16), 256, 0, h->stream>>>(
+                    nb, h->d_asm_bl, h->d_asm_bl + nb, h->d_asm_bl + 2 * nb, h->d_asm_key_r0, h->d_asm_key_k, h->d_asm_key_style,
+                    d_start, (int32_t)h->desc.size(), h->d_desc, d_b, d_o);
+                e = cudaGetLastError();
+                if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+            }
+            cudaFree(d_start);
+        } else {
+            e = dev_alloc_copy(&d_b, h->sub_bonds, h->stream);
+            if (e == cudaSuccess) e = dev_alloc_copy(&d_o, h->sub_bond_atom_off, h->stream);
+        }
         if (e == cudaSuccess) e = dev_alloc_copy(&d_e, h->sub_env, h->stream);
         if (e == cudaSuccess) e = cudaMalloc((void**)&d_r, (size_t)std::max<int64_t>(std::max(nb, ne), 1) * sizeof(double));
         if (e == cudaSuccess && nb > 0) {
@@ -998,7 +1049,8 @@ extern "C" int igmk_violation_ratios(igmk_handle_t* h, int32_t slot, double* bon
         CU(e);
         h->viol_valid = true;
     }
-    const int64_t b0 = h->sub_bond_start[slot], b1 = slot + 1 < (int)h->desc.size() ? h->sub_bond_start[slot + 1] : (int64_t)h->sub_bonds.size();
+    const int64_t b0 = h->sub_bond_start[slot], b1 = slot + 1 < (int)h->desc.size() ? h->sub_bond_start[slot + 1]
+                                                   : (h->dev_built ? h->dev_bonds : (int64_t)h->sub_bonds.size());
     const int64_t e0 = h->sub_env_start[slot], e1 = slot + 1 < (int)h->desc.size() ? h->sub_env_start[slot + 1] : (int64_t)h->sub_env.size();
     if (bond_ratio && b1 > b0) memcpy(bond_ratio, h->viol_bond.data() + b0, (size_t)(b1 - b0) * sizeof(double));
     if (env_u && e1 > e0) memcpy(env_u, h->viol_env.data() + e0, (size_t)(e1 - e0) * sizeof(double));
@@ -1018,10 +1070,10 @@ extern "C" int igmk_reset_coordinates(igmk_handle_t* h)
 {
     if (!h) return fail("igmk_reset_coordinates: NULL handle");
     h->viol_valid = false;
-    h->xyzr = h->xyzr0;
+    if (!h->dev_built) h->xyzr = h->xyzr0;       // (a device-assembled batch keeps its submitted coordinates on the device only)
     if (!h->dirty && h->d_xyzr) {
         CU(cudaSetDevice(h->device));
-        CU(copy_on(h->stream, h->d_xyzr, h->d_xyzr0, h->xyzr0.size() * sizeof(float4), cudaMemcpyDeviceToDevice));
+        CU(copy_on(h->stream, h->d_xyzr, h->d_xyzr0, h->xyzr.size() * sizeof(float4), cudaMemcpyDeviceToDevice));
     }
     return 0;
 }
@@ -1375,6 +1427,9 @@ struct igmk_pop {
     int64_t n_rows = 0;
     DevBuf<int32_t> d_row, d_col; DevBuf<float> d_rdist; DevBuf<uint32_t> d_bits;
     bool assign_done = false;
+    // bound distance of every staged row as an index into a table of distinct values (igmk_pop_set_row_bounds), for the
+    // device-side hand-off to the M-step
+    DevBuf<int32_t> d_rkey; std::vector<double> key_r0; double row_k = 0.0; int64_t bounds_rows = -1;
 
     PopView view() const
     {
@@ -1389,6 +1444,7 @@ struct igmk_pop {
         cudaFree(d_radii); cudaFree(d_chrom); cudaFree(d_copy_off); cudaFree(d_copy_beads);
         d_pi.release(); d_pj.release(); d_pw.release(); d_pl.release(); d_dist.release(); d_prob.release();
         d_valid.release(); d_den.release(); d_meta.release(); d_row.release(); d_col.release(); d_rdist.release(); d_bits.release();
+        d_rkey.release();
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
         if (stream) cudaStreamDestroy(stream);
@@ -1994,7 +2050,7 @@ extern "C" int igmk_pop_set_rows(igmk_pop_t* p, int64_t n_rows, const int32_t* r
 {
     if (!p) return fail("igmk_pop_set_rows: NULL handle");
     if (n_rows < 0) return fail("igmk_pop_set_rows: negative row count");
-    p->n_rows = 0; p->assign_done = false;
+    p->n_rows = 0; p->assign_done = false; p->bounds_rows = -1;
     if (n_rows == 0) return 0;
     if (!row || !col || !dist) return fail("igmk_pop_set_rows: NULL argument");
     for (int64_t r = 0; r < n_rows; r++)
@@ -2049,6 +2105,302 @@ extern "C" int igmk_pop_assign(igmk_pop_t* p, int64_t n_rows, const int32_t* row
     if (int rc = igmk_pop_set_rows(p, n_rows, row, col, dist)) return rc;
     if (int rc = igmk_pop_assign_launch(p)) return rc;
     return igmk_pop_assign_collect(p, bits);
+}
+
+// =========================================================================================
+// Assignment -> M-step batch without leaving the device (assemble.cuh)
+
+extern "C" int igmk_pop_set_row_bounds(igmk_pop_t* p, int64_t n_rows, const double* row_r0, double row_k)
+{
+    if (!p) return fail("igmk_pop_set_row_bounds: NULL handle");
+    if (n_rows != p->n_rows) return fail("igmk_pop_set_row_bounds: one bound per row staged with igmk_pop_set_rows is needed");
+    if (!(row_k >= 0.0)) return fail("igmk_pop_set_row_bounds: the spring constant must be >= 0");
+    p->bounds_rows = -1; p->key_r0.clear(); p->row_k = row_k;
+    if (n_rows == 0) { p->bounds_rows = 0; return 0; }
+    if (!row_r0) return fail("igmk_pop_set_row_bounds: NULL argument");
+    std::vector<int32_t> key((size_t)n_rows);
+    std::map<double, int32_t> seen;
+    int32_t last = -1;
+    for (int64_t r = 0; r < n_rows; r++) {
+        if (last >= 0 && row_r0[r] == row_r0[r - 1]) { key[r] = last; continue; }     // runs of equal bounds skip the map
+        if (!(row_r0[r] >= 0.0)) return fail("igmk_pop_set_row_bounds: negative bound distance");
+        auto it = seen.find(row_r0[r]);
+        if (it == seen.end()) { last = (int32_t)p->key_r0.size(); seen[row_r0[r]] = last; p->key_r0.push_back(row_r0[r]); }
+        else last = it->second;
+        key[r] = last;
+    }
+    CU(cudaSetDevice(p->device));
+    CU(p->d_rkey.reserve((size_t)n_rows));
+    CU(copy_on(p->stream, p->d_rkey.p, key.data(), (size_t)n_rows * sizeof(int32_t), cudaMemcpyHostToDevice));
+    p->bounds_rows = n_rows;
+    return 0;
+}
+
+// neighbour tables and work areas of a device-assembled batch (what upload() allocates after its copies)
+static int alloc_run_buffers(igmk_handle* h)
+{
+    const size_t na = h->xyzr.size(), ns = h->desc.size();
+    CU(cudaMalloc((void**)&h->d_nl, std::max<size_t>(na, 1) * h->nl_width * sizeof(uint16_t)));
+    CU(cudaMalloc((void**)&h->d_md2_nl, ns * (size_t)h->md2_K * MD2_T * (size_t)h->md2_nlw * sizeof(uint16_t)));
+    return 0;
+}
+
+// after a neighbour-table overflow: wider tables, submitted coordinates back in place
+static int upload_dev_rebuild(igmk_handle* h)
+{
+    cudaFree(h->d_nl); cudaFree(h->d_md2_nl); h->d_nl = nullptr; h->d_md2_nl = nullptr;
+    if (int rc = alloc_run_buffers(h)) return rc;
+    CU(copy_on(h->stream, h->d_xyzr, h->d_xyzr0, h->xyzr.size() * sizeof(float4), cudaMemcpyDeviceToDevice));
+    h->dirty = false;
+    return 0;
+}
+
+extern "C" int igmk_submit_population_dev(igmk_handle_t* h, const igmk_system_t* tmpl, igmk_pop_t* pop, int32_t s_begin,
+                                          int32_t n_struct, const int64_t* seeds, int32_t* first_slot_out)
+{
+    if (!h || !tmpl || !pop) return fail("igmk_submit_population_dev: NULL argument");
+    if (h->device < 0 || h->device != pop->device) return fail("igmk_submit_population_dev: batch and population must live on the same GPU");
+    if (!h->desc.empty()) return fail("igmk_submit_population_dev: the batch must be empty (igmk_clear)");
+    if (n_struct <= 0 || s_begin < 0 || s_begin + n_struct > pop->n_struct) return fail("igmk_submit_population_dev: bad structure range");
+    if (!pop->d_crd) return fail("igmk_submit_population_dev: the population has no coordinates");
+    if (pop->n_rows > 0 && !pop->assign_done) return fail("igmk_submit_population_dev: no assignment on the device (igmk_pop_assign_launch)");
+    if (pop->bounds_rows != pop->n_rows) return fail("igmk_submit_population_dev: no bound distances for the staged rows (igmk_pop_set_row_bounds)");
+    const int n = tmpl->n_atoms, n_bead = pop->n_bead;
+    if (n_bead > n) return fail("igmk_submit_population_dev: the template has fewer atoms than the population has beads");
+    // what this path does not cover is left to igmk_submit_population (status 2: the caller falls back)
+    if (n > ASM_MAX_ATOMS || md2_pick_K(n) == 0 || getenv("IGMK_FORCE_BIG") || getenv("IGMK_FORCE_CLUSTER")) {
+        fail("igmk_submit_population_dev: structures of this size are assembled on the host");
+        return 2;
+    }
+    if (tmpl->n_env < 0 || tmpl->n_env > IGMK_MAX_ENVELOPES) return fail("igmk_submit_population_dev: too many envelopes");
+    {
+        const size_t need = std::max(ctx_smem_bytes<float>(n, true), ctx_smem_bytes<double>(n, false));
+        if ((long long)need > (long long)h->smem_optin) return fail("igmk_submit_population_dev: structure too large for one CTA");
+    }
+    CU(cudaSetDevice(h->device));
+    const bool trace_sp = getenv("IGMK_TRACE") != nullptr;
+    auto tnow = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double tsp0 = tnow();
+    // ---- the template: atoms, envelope masks, bonds, and the table of distinct (r0, k, style) over rows and template ----
+    std::vector<float4> t_xyzr((size_t)n);
+    std::vector<uint8_t> t_kind(tmpl->kind, tmpl->kind + n);
+    std::vector<uint32_t> t_mask((size_t)n, 0u);
+    float maxrad = 0.f; int nonfixed = 0;
+    for (int i = 0; i < n; i++) {
+        if (tmpl->kind[i] > 2) return fail("igmk_submit_population_dev: unknown particle kind");
+        t_xyzr[i] = make_float4(tmpl->xyz[3 * i], tmpl->xyz[3 * i + 1], tmpl->xyz[3 * i + 2], tmpl->radius[i]);
+        if (tmpl->kind[i] == IGMK_KIND_BEAD) maxrad = std::max(maxrad, tmpl->radius[i]);
+        if (tmpl->kind[i] != IGMK_KIND_STATIC) nonfixed++;
+    }
+    for (int e = 0; e < tmpl->n_env; e++)
+        for (int q = tmpl->env_off[e]; q < tmpl->env_off[e + 1]; q++) {
+            const int i = tmpl->env_members[q];
+            if (i < 0 || i >= n) return fail("igmk_submit_population_dev: envelope member out of range");
+            t_mask[i] |= 1u << e;
+        }
+    std::vector<double> key_r0(pop->key_r0), key_k(pop->key_r0.size(), pop->row_k);
+    std::vector<int32_t> key_style(pop->key_r0.size(), IGMK_BOND_UPPER);
+    std::map<std::tuple<double, double, int>, int32_t> keys;
+    for (size_t g = 0; g < key_r0.size(); g++) keys[std::make_tuple(key_r0[g], key_k[g], (int)IGMK_BOND_UPPER)] = (int32_t)g;
+    const int nt = tmpl->n_bonds;
+    std::vector<int32_t> t_i((size_t)nt), t_j((size_t)nt), t_key((size_t)nt);
+    for (int b = 0; b < nt; b++) {
+        const int i = tmpl->bond_i[b], j = tmpl->bond_j[b];
+        if (i < 0 || i >= n || j < 0 || j >= n) return fail("igmk_submit_population_dev: bond index out of range");
+        if (tmpl->bond_style[b] > 1) return fail("igmk_submit_population_dev: unknown bond style");
+        if (!(tmpl->bond_k[b] >= 0.0)) return fail("igmk_submit_population_dev: bond spring constants must be >= 0");
+        if (!(tmpl->bond_r0[b] >= 0.0)) return fail("igmk_submit_population_dev: negative bound distance in the template");
+        const auto key = std::make_tuple(tmpl->bond_r0[b], tmpl->bond_k[b], (int)tmpl->bond_style[b]);
+        auto it = keys.find(key);
+        if (it == keys.end()) {
+            it = keys.emplace(key, (int32_t)key_r0.size()).first;
+            key_r0.push_back(tmpl->bond_r0[b]); key_k.push_back(tmpl->bond_k[b]); key_style.push_back((int32_t)tmpl->bond_style[b]);
+        }
+        t_i[b] = i; t_j[b] = j; t_key[b] = it->second;
+    }
+    const int G = (int)key_r0.size();
+    if (G > ASM_MAX_KEYS) {
+        fail("igmk_submit_population_dev: more distinct bound distances than the device path handles; assemble on the host");
+        return 2;
+    }
+    // one device blob for all of it (offsets 16-byte aligned)
+    auto al = [](size_t v) { return (v + 15) / 16 * 16; };
+    size_t o_xyzr = 0, o_kind = al(o_xyzr + (size_t)n * sizeof(float4)), o_mask = al(o_kind + (size_t)n), o_ti = al(o_mask + (size_t)n * 4),
+           o_tj = al(o_ti + (size_t)nt * 4), o_tk = al(o_tj + (size_t)nt * 4), o_kr = al(o_tk + (size_t)nt * 4), o_kk = al(o_kr + (size_t)G * 8),
+           o_ks = al(o_kk + (size_t)G * 8), total = al(o_ks + (size_t)G * 4);
+    std::vector<unsigned char> blob(total, 0);
+    memcpy(blob.data() + o_xyzr, t_xyzr.data(), (size_t)n * sizeof(float4));
+    memcpy(blob.data() + o_kind, t_kind.data(), (size_t)n);
+    memcpy(blob.data() + o_mask, t_mask.data(), (size_t)n * 4);
+    if (nt) { memcpy(blob.data() + o_ti, t_i.data(), (size_t)nt * 4); memcpy(blob.data() + o_tj, t_j.data(), (size_t)nt * 4); memcpy(blob.data() + o_tk, t_key.data(), (size_t)nt * 4); }
+    if (G) { memcpy(blob.data() + o_kr, key_r0.data(), (size_t)G * 8); memcpy(blob.data() + o_kk, key_k.data(), (size_t)G * 8); memcpy(blob.data() + o_ks, key_style.data(), (size_t)G * 4); }
+    h->free_device();
+    CU(cudaMalloc((void**)&h->d_asm_blob, total));
+    CU(cudaMemcpyAsync(h->d_asm_blob, blob.data(), total, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMalloc((void**)&h->d_asm_cnt, (size_t)3 * n_struct * sizeof(int32_t)));
+    AsmIn I;
+    memset(&I, 0, sizeof I);
+    I.n_atoms = n; I.n_bead = n_bead; I.n_tbonds = nt; I.n_keys = G;
+    I.t_xyzr = (const float4*)(h->d_asm_blob + o_xyzr); I.t_kind = h->d_asm_blob + o_kind; I.t_envmask = (const uint32_t*)(h->d_asm_blob + o_mask);
+    I.t_i = (const int32_t*)(h->d_asm_blob + o_ti); I.t_j = (const int32_t*)(h->d_asm_blob + o_tj); I.t_key = (const int32_t*)(h->d_asm_blob + o_tk);
+    I.key_r0 = (const double*)(h->d_asm_blob + o_kr); I.key_k = (const double*)(h->d_asm_blob + o_kk); I.key_style = (const int32_t*)(h->d_asm_blob + o_ks);
+    h->d_asm_key_r0 = I.key_r0; h->d_asm_key_k = I.key_k; h->d_asm_key_style = I.key_style;
+    I.crd = pop->d_crd; I.n_struct_total = pop->n_struct; I.s_begin = s_begin;
+    I.n_rows = pop->n_rows; I.row = pop->d_row.p; I.col = pop->d_col.p; I.row_key = pop->d_rkey.p;
+    I.bits = pop->d_bits.p; I.bits_words = (pop->n_struct + 31) / 32;
+    // ---- sizes ----
+    k_asm_count<<<n_struct, ASM_T, 0, h->stream>>>(I, h->d_asm_cnt, h->d_asm_cnt + n_struct);
+    CU(cudaGetLastError());
+    std::vector<int32_t> cnt((size_t)2 * n_struct);
+    CU(copy_on(h->stream, cnt.data(), h->d_asm_cnt, cnt.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    h->desc.resize((size_t)n_struct); h->struct_id.resize((size_t)n_struct); h->sub_bond_start.resize((size_t)n_struct);
+    h->dev_nb.assign(cnt.begin(), cnt.begin() + n_struct);
+    int64_t bonds = 0; int32_t btypes = 0;
+    for (int sl = 0; sl < n_struct; sl++) {
+        StructDesc d;
+        memset(&d, 0, sizeof d);
+        d.atom_off = sl * n; d.n_atoms = n; d.n_nonfixed = nonfixed;
+        d.bond_ptr_off = sl * (n + 1); d.bond_item_off = 2 * bonds; d.btype_off = btypes;
+        d.n_env = tmpl->n_env;
+        for (int e = 0; e < tmpl->n_env; e++) for (int k = 0; k < 4; k++) d.env[e][k] = tmpl->env_abck[4 * e + k];
+        d.evfactor = tmpl->evfactor;
+        const int64_t sid = tmpl->struct_id + s_begin + sl;
+        d.seed = seeds ? seeds[sl] : (int64_t)(((__int128)std::max<int64_t>(tmpl->seed, 1) * sid) % 9190037) + 1;
+        d.maxrad = maxrad;
+        h->desc[sl] = d; h->struct_id[sl] = sid; h->sub_bond_start[sl] = bonds;
+        bonds += cnt[sl]; btypes += std::max(cnt[(size_t)n_struct + sl], 2);
+    }
+    h->dev_bonds = bonds; h->max_atoms = n;
+    if ((size_t)n_struct * (size_t)(n + 1) > (size_t)INT32_MAX) return fail("igmk_submit_population_dev: batch too large");
+    const size_t na = (size_t)n_struct * n;
+    h->md2_K = md2_pick_K(n); h->md_big = false; h->mdc_CL = 0;
+    const int K = h->md2_K, np = K * MD2_T, GW = K * MD2_NW;
+    // ---- batch arrays ----
+    CU(cudaMalloc((void**)&h->d_desc, (size_t)n_struct * sizeof(StructDesc)));
+    CU(cudaMemcpyAsync(h->d_desc, h->desc.data(), (size_t)n_struct * sizeof(StructDesc), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMalloc((void**)&h->d_xyzr, na * sizeof(float4))); CU(cudaMalloc((void**)&h->d_xyzr0, na * sizeof(float4)));
+    CU(cudaMalloc((void**)&h->d_kind, na)); CU(cudaMalloc((void**)&h->d_envmask, na * sizeof(uint32_t)));
+    CU(cudaMalloc((void**)&h->d_bond_ptr, (size_t)n_struct * (n + 1) * sizeof(int32_t)));
+    CU(cudaMalloc((void**)&h->d_bond_items, (size_t)std::max<int64_t>(2 * bonds, 1) * sizeof(uint32_t)));
+    CU(cudaMalloc((void**)&h->d_btype_f, (size_t)btypes * sizeof(float2))); CU(cudaMalloc((void**)&h->d_btype_d, (size_t)btypes * sizeof(double2)));
+    CU(cudaMalloc((void**)&h->d_asm_bl, (size_t)std::max<int64_t>(3 * bonds, 1) * sizeof(int32_t)));
+    CU(cudaMalloc((void**)&h->d_asm_csr, (size_t)std::max<int64_t>(4 * bonds, 1) * sizeof(int32_t)));
+    CU(cudaMalloc((void**)&h->d_asm_dec, (size_t)std::max<int64_t>(2 * bonds, 1)));
+    CU(cudaMalloc((void**)&h->d_asm_atom, na * 3 * sizeof(uint16_t)));
+    CU(cudaMalloc((void**)&h->d_md2_perm, (size_t)n_struct * np * sizeof(uint16_t)));
+    CU(cudaMalloc((void**)&h->d_md2_eblk, (size_t)n_struct * GW * sizeof(int4)));
+    CU(cudaMalloc((void**)&h->d_md2_desc, (size_t)n_struct * sizeof(Md2Desc)));
+    CU(cudaMemsetAsync(h->d_asm_dec, 0, (size_t)std::max<int64_t>(2 * bonds, 1), h->stream));
+    AsmOut O;
+    memset(&O, 0, sizeof O);
+    O.desc = h->d_desc; O.xyzr = h->d_xyzr; O.xyzr0 = h->d_xyzr0; O.kind = h->d_kind; O.envmask = h->d_envmask;
+    O.bond_ptr = h->d_bond_ptr; O.bond_items = h->d_bond_items; O.btype_f = h->d_btype_f; O.btype_d = h->d_btype_d;
+    O.bl_i = h->d_asm_bl; O.bl_j = h->d_asm_bl + bonds; O.bl_key = h->d_asm_bl + 2 * bonds;
+    O.bidx = h->d_asm_csr; O.twin = h->d_asm_csr + 2 * bonds; O.dec = h->d_asm_dec;
+    O.cntA = h->d_asm_atom; O.cntB = h->d_asm_atom + na; O.pos = h->d_asm_atom + 2 * na;
+    O.perm = h->d_md2_perm; O.eblk = h->d_md2_eblk; O.ell_size = h->d_asm_cnt + 2 * n_struct; O.mdesc = h->d_md2_desc; O.K = K;
+    const size_t sm_b = asm_bonds_smem(G, n), sm_o = asm_orient_smem(n), sm_l = asm_layout_smem(n, K);
+    CU(cudaFuncSetAttribute(k_asm_bonds, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_b));
+    CU(cudaFuncSetAttribute(k_asm_orient, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_o));
+    CU(cudaFuncSetAttribute(k_asm_layout, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_l));
+    k_asm_bonds<<<n_struct, ASM_T, sm_b, h->stream>>>(I, O);
+    CU(cudaGetLastError());
+    k_asm_orient<<<n_struct, 32, sm_o, h->stream>>>(I, O);
+    CU(cudaGetLastError());
+    k_asm_layout<<<n_struct, ASM_T, sm_l, h->stream>>>(I, O);
+    CU(cudaGetLastError());
+    std::vector<int32_t> ell((size_t)n_struct);
+    CU(copy_on(h->stream, ell.data(), h->d_asm_cnt + 2 * n_struct, ell.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    h->md2_desc.assign((size_t)n_struct, Md2Desc());
+    int64_t ell_total = 0;
+    for (int sl = 0; sl < n_struct; sl++) {
+        Md2Desc& m = h->md2_desc[sl];
+        m.ell_item_off = ell_total; m.perm_off = sl * np; m.ell_desc_off = sl * GW; m.K = K; m.pad = 0;
+        ell_total += ell[sl];
+    }
+    CU(cudaMemcpyAsync(h->d_md2_desc, h->md2_desc.data(), (size_t)n_struct * sizeof(Md2Desc), cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMalloc((void**)&h->d_md2_ell_items, (size_t)std::max<int64_t>(ell_total, 1) * sizeof(uint32_t)));
+    CU(cudaMalloc((void**)&h->d_md2_ell_act, (size_t)std::max<int64_t>(ell_total, 1) * sizeof(uint32_t)));
+    O.ell_items = h->d_md2_ell_items;
+    k_asm_ell<<<n_struct, ASM_T, 0, h->stream>>>(I, O);
+    CU(cudaGetLastError());
+    // ---- what upload() allocates besides ----
+    h->xyzr.resize(na);
+    CU(cudaMalloc((void**)&h->d_nl_cnt, na * sizeof(uint16_t)));
+    CU(cudaMalloc((void**)&h->d_xd, na * 3 * sizeof(double))); CU(cudaMalloc((void**)&h->d_fd, na * 3 * sizeof(double)));
+    CU(cudaMalloc((void**)&h->d_work, na * 12 * sizeof(double)));
+    CU(cudaMalloc((void**)&h->d_res, (size_t)n_struct * sizeof(igmk_result_t))); CU(cudaMalloc((void**)&h->d_flags, (size_t)n_struct * sizeof(int32_t)));
+    CU(cudaMemsetAsync(h->d_res, 0, (size_t)n_struct * sizeof(igmk_result_t), h->stream));
+    CU(cudaMemsetAsync(h->d_flags, 0, (size_t)n_struct * sizeof(int32_t), h->stream));
+    if (ctx_is_big<double>(n, false) || ctx_is_big<float>(n, false)) CU(cudaMalloc((void**)&h->d_big, (na + 32 * (size_t)n_struct) * 10 * sizeof(double)));
+    CU(cudaMalloc((void**)&h->d_md2_gf, (size_t)n_struct * np * MD2_INBOX * sizeof(float4)));
+    if (int rc = alloc_run_buffers(h)) return rc;
+    h->dev_env_abck.assign(tmpl->env_abck, tmpl->env_abck + 4 * (size_t)tmpl->n_env);
+    h->dev_env_off.assign(tmpl->env_off, tmpl->env_off + tmpl->n_env + 1);
+    h->dev_env_mem.assign(tmpl->env_members, tmpl->env_members + tmpl->env_off[tmpl->n_env]);
+    h->h2d_bytes = total + (size_t)n_struct * (sizeof(StructDesc) + sizeof(Md2Desc));
+    h->dev_built = true; h->dirty = false; h->viol_valid = false;
+    if (first_slot_out) *first_slot_out = 0;
+    if (trace_sp)
+        fprintf(stderr, "[igmk trace] submit_population_dev of %d: %.1f ms in all (%lld bonds, %lld sliced-ELL items)\n",
+                n_struct, tnow() - tsp0, (long long)bonds, (long long)ell_total);
+    return 0;
+}
+
+// One array of the staged batch as it sits on the device, for tests that compare the two assembly paths
+// (0 desc, 1 xyzr, 2 xyzr0, 3 kind, 4 envmask, 5 bond_ptr, 6 bond_items, 7 btype_f, 8 btype_d, 9 md2_desc, 10 perm,
+// 11 eblk, 12 ell_items).  *n_bytes = size of the array; the copy is made when it fits max_bytes.
+extern "C" int igmk_debug_fetch_array(igmk_handle_t* h, int32_t which, void* out, int64_t max_bytes, int64_t* n_bytes)
+{
+    if (!h || !n_bytes) return fail("igmk_debug_fetch_array: NULL argument");
+    if (h->device < 0) return fail("igmk_debug_fetch_array: staging-only handle");
+    CU(cudaSetDevice(h->device));
+    if (int rc = upload(h)) return rc;
+    const size_t ns = h->desc.size(), na = h->xyzr.size();
+    if (ns == 0) return fail("igmk_debug_fetch_array: nothing submitted");
+    const StructDesc& dl = h->desc.back();
+    int64_t items = 0, btypes = 0, ell = 0;
+    {
+        int32_t last_ptr = 0;
+        CU(copy_on(h->stream, &last_ptr, h->d_bond_ptr + dl.bond_ptr_off + dl.n_atoms, sizeof(int32_t), cudaMemcpyDeviceToHost));
+        items = dl.bond_item_off + last_ptr;
+        btypes = h->dev_built ? -1 : (int64_t)h->btype_f.size();
+        if (btypes < 0) {            // last structure's offset + max(its types, 2): the count sits in d_asm_cnt
+            int32_t nty = 0;
+            CU(copy_on(h->stream, &nty, h->d_asm_cnt + ns + (ns - 1), sizeof(int32_t), cudaMemcpyDeviceToHost));
+            btypes = dl.btype_off + std::max(nty, 2);
+        }
+        if (h->md2_K > 0 && !h->md_big && h->mdc_CL == 0) {
+            const int GW = h->md2_K * MD2_NW;
+            int4 e;
+            CU(copy_on(h->stream, &e, h->d_md2_eblk + ns * (size_t)GW - 1, sizeof(int4), cudaMemcpyDeviceToHost));
+            ell = h->md2_desc.back().ell_item_off + e.z + (int64_t)e.w * 4 * 32;
+        }
+    }
+    const void* src = nullptr; int64_t bytes = 0;
+    const int K = h->md2_K;
+    switch (which) {
+        case 0: src = h->d_desc; bytes = ns * sizeof(StructDesc); break;
+        case 1: src = h->d_xyzr; bytes = na * sizeof(float4); break;
+        case 2: src = h->d_xyzr0; bytes = na * sizeof(float4); break;
+        case 3: src = h->d_kind; bytes = na; break;
+        case 4: src = h->d_envmask; bytes = na * sizeof(uint32_t); break;
+        case 5: src = h->d_bond_ptr; bytes = (dl.bond_ptr_off + dl.n_atoms + 1) * sizeof(int32_t); break;
+        case 6: src = h->d_bond_items; bytes = items * sizeof(uint32_t); break;
+        case 7: src = h->d_btype_f; bytes = btypes * sizeof(float2); break;
+        case 8: src = h->d_btype_d; bytes = btypes * sizeof(double2); break;
+        case 9: src = h->d_md2_desc; bytes = ns * sizeof(Md2Desc); break;
+        case 10: src = h->d_md2_perm; bytes = ns * (size_t)K * MD2_T * sizeof(uint16_t); break;
+        case 11: src = h->d_md2_eblk; bytes = ns * (size_t)K * MD2_NW * sizeof(int4); break;
+        case 12: src = h->d_md2_ell_items; bytes = ell * sizeof(uint32_t); break;
+        default: return fail("igmk_debug_fetch_array: no such array");
+    }
+    *n_bytes = bytes;
+    if (out && bytes > 0 && bytes <= max_bytes) {
+        if (!src) return fail("igmk_debug_fetch_array: array not allocated on this path");
+        CU(copy_on(h->stream, out, src, (size_t)bytes, cudaMemcpyDeviceToHost));
+    }
+    return 0;
 }
 
 // =========================================================================================

@@ -23,13 +23,15 @@ from .kernel import info_from_result, run_population
 
 
 def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, device=0, contact_range=2.0,
-                  k_hic=1.0, seeds=None, bond_prefactor=1.0, violations=False, tol=0.05, astep="gather"):
+                  k_hic=1.0, seeds=None, bond_prefactor=1.0, violations=False, tol=0.05, astep="gather", assemble="device"):
     """crd_local: float32 [n_bead][S_local][3] (host).  genome: object with chrom, copy_off, copy_beads.
     template: PackedSystem of the shared particles and restraints (Steric, Envelope, Polymer).
     pairs: (pair_i, pair_j, pwish, plast) haploid pairs kept at this sigma -- identical on every rank.
     astep: "gather" = all-gather the coordinate slab, shard the pair list (every rank sees the whole population);
            "reduce" = the population stays sharded by structure, per-pair counts and radix histograms are all-reduced
            (``parallel.sharded_actdist``; BASELINE configs[4]).  Both give the same rows, bit for bit.
+    assemble: "device" = the assignment bit matrix stays on the GPU and the M-step batches are assembled there
+           (igmk_submit_population_dev); "host" = bit matrix to the host, igmk_submit_population.  Same batches, byte for byte.
     -> dict(coordinates [n_bead][S_local][3], infos [S_local], rows (row, col, dist, prob), timings,
             violations = per-structure (n_imposed, n_violated) of the harmonic restraints if asked)."""
     import torch
@@ -53,13 +55,18 @@ def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, 
         if astep == "reduce":
             rows = parallel.sharded_actdist(popl, parallel.total_structures(S, device=dev), pi, pj, pw, pl, contact_range)
         row, col, dist, prob = rows
-        bits = popl.assign(row, col, dist)
-    t_astep = time.perf_counter() - t0
-    r0 = (contact_range * (radii[row] + radii[col])).astype(np.float64)      # float32 product like inter_hic.py:55
-    protocol = _abi.make_protocol(optimizer_options, bond_prefactor=bond_prefactor)
-    out = {"rows": rows, "timings": {"astep_s": t_astep}}
-    new, results, viol, tim = run_population(template, crd_local, n_bead, row, col, r0, k_hic, bits, protocol, device=device,
-                                             seeds=seeds, violations_tol=tol if violations else None)
+        if assemble not in ("device", "host"):
+            raise ValueError("assemble must be 'device' or 'host'")
+        popl.set_rows(row, col, dist)
+        popl.assign_launch()
+        bits = popl.assign_collect() if assemble == "host" else None
+        t_astep = time.perf_counter() - t0
+        r0 = (contact_range * (radii[row] + radii[col])).astype(np.float64)      # float32 product like inter_hic.py:55
+        protocol = _abi.make_protocol(optimizer_options, bond_prefactor=bond_prefactor)
+        out = {"rows": rows, "timings": {"astep_s": t_astep}}
+        new, results, viol, tim = run_population(template, crd_local, n_bead, row, col, r0, k_hic, bits, protocol, device=device,
+                                                 seeds=seeds, violations_tol=tol if violations else None,
+                                                 pop=popl if assemble == "device" else None)
     infos = []
     for k, res in enumerate(results):
         if res.status != 0 or not np.isfinite(res.final_energy):
@@ -70,8 +77,28 @@ def hic_iteration(crd_local, genome, radii, template, pairs, optimizer_options, 
     md_ms, cg_ms, h2d = tim["md_kernel_ms"], tim["cg_kernel_ms"], tim["h2d_bytes"]
     out["coordinates"], out["infos"] = new, infos
     out["timings"].update({"mstep_s": time.perf_counter() - t0 - t_astep, "md_kernel_ms": md_ms, "cg_kernel_ms": cg_ms,
-                           "h2d_bytes": h2d, "total_s": time.perf_counter() - t0})
+                           "h2d_bytes": h2d, "total_s": time.perf_counter() - t0,
+                           "chunks_assembled_on_device": tim.get("assembled_on_device", 0)})
     return out
+
+
+def mstep_population(crd, genome, radii, template, row, col, dist, protocol, device=0, contact_range=2.0, k_hic=1.0,
+                     seeds=None, violations_tol=None):
+    """Assignment + M-step of one block of structures from HOST buffers with the hand-off on the device: coordinates
+    (float32 [n_bead][S][3]) and the actdist rows (row, col, dist) go up once, the contact assignment
+    (inter_hic.py:49-64), the assembly of every structure (ModelingStep.py:184-264) and the optimisation run on the
+    GPU, the optimised coordinates come back.  -> (coordinates, [Result], violations or None, timings dict)"""
+    crd = np.ascontiguousarray(crd, dtype=np.float32)
+    n_bead, S = crd.shape[0], crd.shape[1]
+    with Population(S, radii, genome.chrom, genome.copy_off, genome.copy_beads, device=device) as pop:
+        pop.upload(crd)
+        pop.set_rows(row, col, dist)
+        pop.assign_launch()
+        r0 = (contact_range * (radii[row] + radii[col])).astype(np.float64)
+        new, results, viol, tim = run_population(template, crd, n_bead, row, col, r0, k_hic, None, protocol, device=device,
+                                                 seeds=seeds, violations_tol=violations_tol, pop=pop)
+    tim["h2d_bytes"] += crd.nbytes + 3 * 4 * int(np.size(row)) + 4 * int(np.size(row))     # slab, rows, bound keys
+    return new, results, viol, tim
 
 
 def assemble_restraints(crd_local, genome, radii, hic=None, damid=None, fish=None, device=0):

@@ -118,6 +118,32 @@ class MStepBatch(object):
         self._packed.extend([template] * n_struct)        # sizes for fetch(); bond arrays differ per structure
         return first.value
 
+    def submit_population_device(self, template, pop, s_begin=0, n_struct=None, seeds=None):
+        """The same for structures of a device-resident population whose assignment is still on the GPU
+        (``pop``: an astep.Population after set_rows + assign_launch + set_row_bounds): nothing but the template
+        crosses the bus, the batch is assembled by kernels (igmk_submit_population_dev).  -> True, or False when
+        the input is outside what the device path covers and has to go through submit_population."""
+        if n_struct is None:
+            n_struct = pop.n_struct - s_begin
+        sd = None if seeds is None else np.ascontiguousarray(seeds, dtype=np.int64)
+        first = C.c_int32(-1)
+        rc = self._lib.igmk_submit_population_dev(self._h, C.byref(template.c), pop._p, int(s_begin), int(n_struct),
+                                                  None if sd is None else sd.ctypes.data_as(_abi.c_i64p), C.byref(first))
+        if rc == 2:
+            return False
+        _abi.check(rc, "igmk_submit_population_dev")
+        self._packed.extend([template] * n_struct)
+        return True
+
+    def debug_array(self, which, dtype=np.uint8):
+        """array `which` of the staged batch as it sits on the device (igmk_debug_fetch_array)"""
+        n = C.c_int64(0)
+        _abi.check(self._lib.igmk_debug_fetch_array(self._h, int(which), None, 0, C.byref(n)), "igmk_debug_fetch_array")
+        buf = np.zeros(max(n.value, 1), dtype=np.uint8)
+        _abi.check(self._lib.igmk_debug_fetch_array(self._h, int(which), buf.ctypes.data_as(C.c_void_p), buf.size, C.byref(n)),
+                   "igmk_debug_fetch_array")
+        return buf[:n.value].view(dtype)
+
     def upload(self):
         _abi.check(self._lib.igmk_upload(self._h), "igmk_upload")
 
@@ -324,7 +350,7 @@ PIPELINE_CHUNK = 128     # structures per launch sequence of run_population: a m
 
 
 def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protocol, device=0, seeds=None,
-                   chunk=PIPELINE_CHUNK, violations_tol=None, extras=None):
+                   chunk=PIPELINE_CHUNK, violations_tol=None, extras=None, pop=None):
     """M-step of a whole assigned population, host buffers in, host buffers out: the population-wide
     form of ``ModelingStep.task`` (igm/steps/ModelingStep.py:184-264 build, :266 optimize, :341-382 results).
 
@@ -332,6 +358,12 @@ def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protoco
     (``igmk_submit_population``, multi-threaded C++) while worker threads upload, run and fetch the
     chunks before it, each batch on its own stream -- the SMs always have CTAs of some chunk to run, so
     the host-side assembly, the copies in and the copies out disappear behind the MD kernel.
+
+    ``pop``: the astep.Population these structures and rows were assigned in (set_rows + assign_launch done on it,
+    same structure indices as ``crd``).  Then the batches are assembled on the device from the population's slab, rows
+    and bit matrix (igmk_submit_population_dev) -- ``crd`` and ``bits`` are not read, ``bits`` may be None -- unless
+    the input is outside what that path covers (per-structure extras, very many distinct bounds), in which case the
+    bit matrix is fetched and the host path runs.
 
     -> (coordinates float32 [n_bead][S][3], [Result] * S, violations or None, timings dict);
     violations = per-structure (n_imposed, n_violated) of the harmonic restraints and (n_imposed, n_violated) of the
@@ -361,8 +393,25 @@ def run_population(template, crd, n_bead, row, col, row_r0, row_k, bits, protoco
     # The batches stay open until every chunk is done: freeing device memory waits for the whole device
     # (and holds up the other threads' launches while it does), which would stall the pipeline.
     batches = []
+    tim["assembled_on_device"] = 0
     try:
-        for lo in range(0, S, chunk):
+        if pop is not None and extras is None:
+            # Assembly on the device costs milliseconds and its kernels would queue behind the MD CTAs of the chunks before
+            # them (an MD CTA fills its SM), so there is nothing to pipeline: one batch, one launch sequence.
+            pop.set_row_bounds(row_r0, row_k)
+            batches.append((MStepBatch(device), 0, S))
+            if batches[0][0].submit_population_device(template, pop, 0, S, seeds=seeds):
+                tim["assembled_on_device"] = 1
+                finish(*batches[0])
+                if errors:
+                    raise errors[0]
+            else:
+                batches.pop()[0].close()
+        if not tim["assembled_on_device"] and bits is None:
+            if pop is None:
+                raise ValueError("run_population needs the assignment bit matrix or the population it was computed in")
+            bits = pop.assign_collect()
+        for lo in ([] if tim["assembled_on_device"] else range(0, S, chunk)):
             hi = min(S, lo + chunk)
             batches.append((MStepBatch(device), lo, hi))
             batches[-1][0].submit_population(template, crd, n_bead, row, col, row_r0, row_k, bits, s_begin=lo, n_struct=hi - lo,

@@ -373,6 +373,36 @@ int igmk_pop_assign_launch(igmk_pop_t* p);
 int igmk_pop_assign_collect(igmk_pop_t* p, uint32_t* bits);
 
 /*
+ * Assignment -> M-step batch without leaving the device.  The reference turns every
+ * satisfied actdist row of a structure into a HarmonicUpperBound Python object (inter_hic.py:49-64,
+ * intra_hic.py:50-65) that LammpsModel re-walks (lammps_model.py:279-301); igmk_submit_population does the same
+ * from a downloaded bit matrix on the host threads.  Here the slab, the rows and the bit matrix stay in the
+ * igmk_pop_t the A-step used:
+ *   igmk_pop_set_rows + igmk_pop_assign_launch      the bit matrix, on the device
+ *   igmk_pop_set_row_bounds                          row_r0[r] = contact_range * (radius_i + radius_j) of every staged
+ *                                                    row (inter_hic.py:55-62) and the common spring constant
+ *   igmk_submit_population_dev(h, tmpl, pop, ...)    structures s_begin .. s_begin+n_struct-1 of the population into the
+ *                                                    EMPTY batch h (same GPU): template + slab coordinates + one upper
+ *                                                    bound per row whose bit is set, in row order -- five kernels
+ *                                                    (assemble.cuh) write the atoms, the bond CSR, the bond type tables
+ *                                                    and the MD kernel's layout.  The arrays are byte-identical to what
+ *                                                    igmk_submit_population + igmk_upload build from the same inputs.
+ * Seeds as in igmk_submit_population.  Returns 0, 1 (error) or 2: this input is outside what the device path covers
+ * (more than 8192 atoms, more than 1024 distinct bound distances, per-structure extras) and must go through
+ * igmk_submit_population; igmk_last_error says which.  Afterwards the batch behaves like any other (run, fetch,
+ * violation ratios); igmk_submit cannot add to it.
+ */
+int igmk_pop_set_row_bounds(igmk_pop_t* p, int64_t n_rows, const double* row_r0, double row_k);
+int igmk_submit_population_dev(igmk_handle_t* h, const igmk_system_t* tmpl, igmk_pop_t* pop, int32_t s_begin,
+                               int32_t n_struct, const int64_t* seeds, int32_t* first_slot_out);
+/*
+ * Test aid: one array of the staged batch as it sits on the device (0 desc, 1 xyzr, 2 xyzr0, 3 kind, 4 envmask,
+ * 5 bond_ptr, 6 bond_items, 7 btype_f, 8 btype_d, 9 md2 descriptors, 10 atom permutation, 11 block descriptors,
+ * 12 sliced-ELL items).  *n_bytes = its size; copied to `out` when it fits max_bytes.
+ */
+int igmk_debug_fetch_array(igmk_handle_t* h, int32_t which, void* out, int64_t max_bytes, int64_t* n_bytes);
+
+/*
  * DamID (lamina) A-step.  igmk_pop_damid_actdist = get_damid_actdist
  * (igm/steps/DamidActivationDistanceStep.py:285-356) for a batch of loci (haploid indices), with
  * the "%6d %10.2f %.5f" text round trip (:31, :229).  ellipsoid = 0: nucleus_param[0] is the
