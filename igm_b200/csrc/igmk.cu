@@ -87,7 +87,7 @@ struct igmk_handle {
     // thread-per-atom MD layout (md2.cuh), built at upload time
     int md2_K = 0, md2_nlw = MD2_NLW0;
     float skin_factor = 0.7f;   // k_md_big: single-level neighbour skin in bead radii
-    float skin_inner = 0.7f;    // k_md2: neighbour skin in bead radii (profiles/)
+    float skin_inner = 0.6f;    // k_md2: neighbour skin in bead radii (measured optimum once the rebuild got cheaper: 0.5 / 0.6 / 0.7 / 0.8 -> 73.8 / 72.4 / 73.6 / 75.2 ms, tools/prof_md.py 148 0.06)
     std::vector<Md2Desc> md2_desc;
     std::vector<uint16_t> md2_perm;
     std::vector<int32_t>  md2_ell_off;
@@ -1141,7 +1141,9 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
         double a[16] = {0};
         for (int s = 0; s < ns; s++) for (int k = 0; k < 16; k++) a[k] += (double)t[16 * (size_t)s + k] / ns;
         fprintf(stderr, "[igmk prof] k_md2 mean cycles per structure (thread 0): force evaluations %.3g (pair loops %.3g, bond block A %.3g, "
-                "barrier + receive %.3g); rebuilds %.3g (of which search %.3g), %.1f rebuilds\n", a[0], a[5], a[6], a[4], a[2], a[1], a[3]);
+                "barrier + receive %.3g; loops before the barrier: slowest warp %.3g, mean warp %.3g); rebuilds %.3g (of which search %.3g: slowest warp %.3g, "
+                "mean warp %.3g), %.1f rebuilds; bond batches walked by thread 0: %.0f candidate, %.0f full; neighbour batches %.0f\n",
+                a[0], a[5], a[6], a[4], a[9], a[10], a[2], a[1], a[7], a[8], a[3], a[11], a[12], a[13]);
     }
     return 0;
 }
@@ -1231,7 +1233,7 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
         CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
         CU(cudaEventRecord(e0, h->stream));
         MdParams P; P.prot = *prot; P.skin_factor = h->md_big ? h->skin_factor : h->skin_inner;
-        P.debug_stage = -1;
+        P.debug_stage = -1; P.general_pairs = getenv("IGMK_GENERAL_PAIRS") != nullptr;
         if (int rc = launch_md2(h, B, P, ns)) return rc;
         CU(cudaEventRecord(e1, h->stream));
         CU(cudaStreamWaitEvent(h->stream_hi, e1, 0));
@@ -1281,7 +1283,7 @@ extern "C" int igmk_md_forces(igmk_handle_t* h, const igmk_protocol_t* prot, int
         CU(cudaMemsetAsync(h->d_md2_dbg, 0, h->xyzr.size() * 3 * sizeof(double), h->stream));
         Batch B = make_batch(h);
         CU(cudaMemsetAsync(h->d_flags, 0, ns * sizeof(int32_t), h->stream));
-        MdParams P; P.prot = *prot; P.skin_factor = h->skin_inner; P.debug_stage = stage;
+        MdParams P; P.prot = *prot; P.skin_factor = h->skin_inner; P.debug_stage = stage; P.general_pairs = getenv("IGMK_GENERAL_PAIRS") != nullptr;
         if (int rc = launch_md2(h, B, P, ns)) return rc;
         CU(cudaStreamSynchronize(h->stream));
         const int rc = collect(h, "igmk_md_forces");

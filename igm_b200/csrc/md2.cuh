@@ -99,6 +99,7 @@ __host__ __device__ inline size_t md2_smem_bytes(int K)
     b += IGMK_MAX_ENVELOPES * 4 * 4;          // envelope parameters
     b += (size_t)K * MD2_NW * 16;             // bond block descriptors
     b += (size_t)K * MD2_NW * 8;              // candidate batches per warp-slot (A, B)
+    b += 16 * 16;                             // compaction table of the neighbour search
     return (b + 255) / 256 * 256;
 }
 
@@ -129,6 +130,37 @@ struct Md2Row {
     }
 };
 
+// The same row filled up to four entries at a time from the neighbour search: `packed` holds n (0..4) indices in its low
+// 16-bit lanes, the other lanes zero.  No loop over the hits, no branch but the store.
+struct Md2RowPacked {
+    uint2* base; size_t stride; uint64_t acc; int fill, batches, cap4;
+    __device__ __forceinline__ Md2RowPacked(uint16_t* table, int p, int np, int width)
+        : base((uint2*)table + p), stride((size_t)np), acc(0ull), fill(0), batches(0), cap4(width >> 2) {}
+    __device__ __forceinline__ void append(uint64_t packed, int n)
+    {
+        const uint64_t comb = acc | (packed << (fill << 4));
+        const int tot = fill + n;
+        if (tot >= 4) {
+            if (batches < cap4) base[(size_t)batches * stride] = make_uint2((uint32_t)comb, (uint32_t)(comb >> 32));
+            batches++;
+            acc = (packed >> ((3 - fill) << 4)) >> 16;       // what did not fit (two shifts: fill may be 0)
+            fill = tot - 4;
+        } else { acc = comb; fill = tot; }
+    }
+    // pad the last batch with `self`; -> entries kept, *ovf set when the row did not fit
+    __device__ __forceinline__ int finish(uint32_t self, int* ovf)
+    {
+        const int n = (batches << 2) + fill;
+        if (fill > 0) {
+            const uint64_t s4 = (uint64_t)self * 0x0001000100010001ull;
+            const uint64_t comb = acc | (s4 << (fill << 4));
+            if (batches < cap4) base[(size_t)batches * stride] = make_uint2((uint32_t)comb, (uint32_t)(comb >> 32));
+        }
+        if (n > (cap4 << 2)) { *ovf = 1; return cap4 << 2; }
+        return n;
+    }
+};
+
 // PROF: per-phase clock64 counters (IGMK_PROF=1); a separate instantiation, because the counters cost ~14 registers
 template <int K, bool PROF = false>
 __global__ void __launch_bounds__(MD2_T, 1)
@@ -153,6 +185,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     float* envp = rbuf + 2 * 256;
     int4* eblk = (int4*)(envp + IGMK_MAX_ENVELOPES * 4);    // [K*32]
     int2* bact = (int2*)(eblk + K * MD2_NW);                 // [K*32] candidate batches (A, B)
+    uint4* lut = (uint4*)(bact + K * MD2_NW);                // [16] hit mask of four candidates -> byte selectors that pack the hits
     unsigned char* flagb = (unsigned char*)inbox;
     int rb_par = 0;
 
@@ -182,8 +215,21 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         x[p] = q;
         vx[k] = vy[k] = vz[k] = 0.f; fx[k] = fy[k] = fz[k] = 0.f;
     }
+    int uni = 1;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const int p = k * MD2_T + tid;
+        if ((meta[k] & 3u) == IGMK_KIND_BEAD && x[p].w != d->maxrad) uni = 0;
+    }
     if (tid < K * MD2_NW) { eblk[tid] = V.eblk[md.ell_desc_off + tid]; bact[tid] = make_int2(0, 0); }
     if (tid == 0) x[np] = make_float4(1e18f, 1e18f, 1e18f, 0.f);
+    if (tid < 16) {          // candidates j = 0..3 sit in 16-bit lane j of (i01, i23); lane t of the output takes the t-th set bit
+        uint32_t sel[4] = {0u, 0u, 0u, 0u};
+        int n = 0;
+        for (int j = 0; j < 4; j++) if (tid & (1 << j)) sel[n++] = (uint32_t)(2 * j) | ((uint32_t)(2 * j + 1) << 4);
+        lut[tid] = make_uint4(sel[0] | (sel[1] << 8), sel[2] | (sel[3] << 8),
+                              n >= 2 ? 0xffffffffu : (n == 1 ? 0xffffu : 0u), n >= 4 ? 0xffffffffu : (n == 3 ? 0xffffu : 0u));
+    }
     const float2 bt0 = btype[0];       // block A's type: the most frequent one (the host orders the table by use)
     const float skin = d->maxrad * P.skin_factor;
     const float lim = 0.25f * skin * skin;
@@ -191,7 +237,8 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     float ev_c = -1.f;                 // evfactor * stage scale / pi  (force prefactor / rc), < 0: no sterics
     int n_rebuild = 0, overflow = 0;
     bool bond_build = true;
-    long long t_search = 0, t_recv = 0, t_bondA = 0, t_pair = 0, t_force = 0, t_build = 0;
+    const bool uniform_rc = __syncthreads_and(uni) != 0 && !P.general_pairs;
+    long long t_search = 0, t_recv = 0, t_bondA = 0, t_pair = 0, t_force = 0, t_build = 0, t_smax = 0, t_ssum = 0, t_fmax = 0, t_fsum = 0, n_cand = 0, n_full = 0, n_nbr = 0;
     auto tick = [&]() -> long long { return PROF ? clock64() : 0ll; };
     __syncthreads();
 
@@ -321,19 +368,25 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         // positions in cell order: the search below walks them contiguously
         const long long ts0 = tick();
         const int nbead = cell_start[ncell];
-        for (int s0 = tid; s0 < nbead; s0 += MD2_T) xsort[s0] = x[cell_atoms[s0]];
+        for (int s0 = tid; s0 < nbead; s0 += MD2_T) {      // (the radius is not needed here: w carries the atom's position index)
+            const uint32_t a = cell_atoms[s0];
+            float4 v = x[a];
+            v.w = __uint_as_float(a);
+            xsort[s0] = v;
+        }
         __syncthreads();
         // Thread t takes the t-th bead IN CELL ORDER (not one of its own atoms), so the lanes of a warp sit in
         // the same or adjacent cells, scan nearly the same ranges (little divergence, broadcast shared-memory
         // reads) and need no index indirection until a candidate is accepted.
         int ovf = 0;
+        const uint32_t xsa = (uint32_t)__cvta_generic_to_shared(xsort);
         for (int s0 = tid; s0 < nbead; s0 += MD2_T) {
             const int p = cell_atoms[s0];
             const float4 q = xsort[s0];
             const int c = cell_of[p];
             const int cx = c % dim[0], cy = (c / dim[0]) % dim[1], cz = c / (dim[0] * dim[1]);
             const int ax0 = max(cx - 1, 0), ax1 = min(cx + 1, dim[0] - 1);
-            Md2Row row(nl, p, np, nlw);
+            Md2RowPacked row(nl, p, np, nlw);
             for (int dz = -1; dz <= 1; dz++) {
                 const int az = cz + dz;
                 if (az < 0 || az >= dim[2]) continue;
@@ -343,24 +396,36 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                     const int cb = (az * dim[1] + ay) * dim[0];
                     const int b = cell_start[cb + ax0], e = cell_start[cb + ax1 + 1];   // 3 cells, contiguous
                     for (int s1 = b; s1 < e; s1 += 4) {
+                        // four candidates at once, branch-free: the four loads go out together (a test that short-circuits on
+                        // s2 < e compiles to a branch around each load and serialises the four shared-memory latencies)
+                        float4 pj[4];
+#pragma unroll
+                        for (int u = 0; u < 4; u++) pj[u] = lds_f4(xsa + ((uint32_t)(s1 + u) << 4));   // may run past e: still inside this CTA's shared memory, masked below
                         uint32_t hits = 0u;
 #pragma unroll
                         for (int u = 0; u < 4; u++) {
-                            const int s2 = s1 + u;                      // may run past e: still inside this CTA's shared memory, masked below
-                            const float4 pj = xsort[s2];
-                            const float ddx = q.x - pj.x, ddy = q.y - pj.y, ddz = q.z - pj.z;
+                            const float ddx = q.x - pj[u].x, ddy = q.y - pj[u].y, ddz = q.z - pj[u].z;
                             // list radius of the largest beads: a superset of cutoff + skin of this pair when radii differ
-                            const bool hit = (s2 < e) && (s2 != s0) && (ddx * ddx + ddy * ddy + ddz * ddz < rlist2);
-                            hits |= hit ? (1u << u) : 0u;
+                            hits |= (uint32_t)(ddx * ddx + ddy * ddy + ddz * ddz < rlist2) << u;
                         }
-                        while (hits) {                       // ~15 % of the tests hit
-                            const int u = __ffs(hits) - 1; hits &= hits - 1;
-                            row.add(cell_atoms[s1 + u]);
-                        }
+                        const int rem = e - s1;
+                        const uint32_t me = (uint32_t)(s0 - s1);
+                        hits &= (rem >= 4 ? 0xfu : (1u << rem) - 1u) & (me < 4u ? ~(1u << me) : ~0u);   // past the range; myself
+                        // the hits' indices (the w of the cell-ordered copy), packed in candidate order through the table
+                        const uint32_t i01 = __byte_perm(__float_as_uint(pj[0].w), __float_as_uint(pj[1].w), 0x5410);
+                        const uint32_t i23 = __byte_perm(__float_as_uint(pj[2].w), __float_as_uint(pj[3].w), 0x5410);
+                        const uint4 L = lut[hits];
+                        const uint32_t r0 = __byte_perm(i01, i23, L.x) & L.z, r1 = __byte_perm(i01, i23, L.y) & L.w;
+                        row.append(((uint64_t)r1 << 32) | r0, __popc(hits));
                     }
                 }
             }
             cell_of[p] = (uint16_t)row.finish((uint32_t)np, &ovf);  // padded with the sentinel; the row length stays here until the next rebuild
+        }
+        if (PROF) {                                   // how unevenly the search is spread over the warps
+            if (lane == 0) ((long long*)rbuf)[warp] = tick() - ts0;
+            __syncthreads();
+            if (tid == 0) { long long mx = 0, sm = 0; for (int q = 0; q < MD2_NW; q++) { const long long v = ((long long*)rbuf)[q]; mx = v > mx ? v : mx; sm += v; } t_smax += mx; t_ssum += sm / MD2_NW; }
         }
         __syncthreads();
         // the cell-ordered copy is dead: its memory becomes the bond inboxes (all flags clear); dummies / empty positions: no row
@@ -382,6 +447,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     // BUILD: first evaluation after a rebuild -- walk the full bond lists and write the candidate lists.
     auto forces = [&](auto build_tag) {
         constexpr bool BUILD = decltype(build_tag)::value;
+        const long long tf0 = tick();
 #pragma unroll
         for (int k = 0; k < K; k++) {
             const int p = k * MD2_T + tid;
@@ -392,9 +458,14 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             const int g = k * MD2_NW + warp;
             const int4 eb = eblk[g];
             const int2 ba = bact[g];
+            // first batch of my neighbour row: in flight while the bond loops run
+            const uint2* col = (const uint2*)nl + p;
+            const int nbp = ev_c >= 0.f ? ((int)cell_of[p] + 3) >> 2 : 0;
+            uint2 wn = nbp > 0 ? col[0] : make_uint2(0u, 0u);
             {   // block A: every item is of type 0, an upper bound, and has an inbox slot at the other end
                 const uint4* it = (const uint4*)((BUILD ? eitems : eact) + eb.x) + lane;   // [batch][lane][4 items]
                 const int nb4 = BUILD ? eb.y : ba.x;
+                if (PROF) { if (BUILD) n_full += nb4; else n_cand += nb4; n_nbr += nbp; }
                 uint32_t* out = eact + eb.x + (lane << 2);
                 const float r0 = bt0.x, r02 = r0 * r0, kf = -bond_pref2 * bt0.y;
                 const float cl = fmaxf(r0 - skin, 0.f), cl2 = cl * cl;
@@ -480,13 +551,29 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             // pair_style soft: F = A pi/rc sin(pi r/rc) r_hat, A = rc^2 ev/pi^2  =>  F/r = ev_c rc sin(pi r/rc) / r.  Branch-free:
             // at MD temperatures nearly every batch of four has an overlapping bead in some lane of the warp, so an early-out
             // only adds divergence here (measured, profiles/r02g: +8 % instructions).
-            if (ev_c >= 0.f) {
-                const uint2* col = (const uint2*)nl + p;
-                const int nb4 = ((int)cell_of[p] + 3) >> 2;
-                uint2 wn = nb4 > 0 ? col[0] : make_uint2(0u, 0u);
-                for (int q = 0; q < nb4; q++) {
+            if (uniform_rc) {
+                // every bead has the same radius (a genome binned at one resolution): the contact distance and with it
+                // pi / rc and ev rc are constants of the loop -- 21 instead of 29 instructions per candidate
+                const float rcu = 2.f * d->maxrad, rc2 = rcu * rcu, a1 = 3.14159265358979323846f / rcu, a2 = ev_c * rcu;
+                for (int q = 0; q < nbp; q++) {
                     const uint2 w = wn;
-                    if (q + 1 < nb4) wn = col[(size_t)(q + 1) * np];            // next batch in flight while this one is used
+                    if (q + 1 < nbp) wn = col[(size_t)(q + 1) * np];            // next batch in flight while this one is used
+                    const uint32_t j[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const float4 pj = lds_f4(xs + (j[u] << 4));
+                        const float dx = pi.x - pj.x, dy = pi.y - pj.y, dz = pi.z - pj.z;
+                        const float r2 = dx * dx + dy * dy + dz * dz;
+                        const float rinv = fast_rsqrt(r2);
+                        float fp = a2 * (fast_sin((r2 * rinv) * a1) * rinv);
+                        fp = (r2 < rc2 && r2 > 0.f) ? fp : 0.f;                   // (the padding sentinel is far away)
+                        ax += dx * fp; ay += dy * fp; az += dz * fp;
+                    }
+                }
+            } else {
+                for (int q = 0; q < nbp; q++) {
+                    const uint2 w = wn;
+                    if (q + 1 < nbp) wn = col[(size_t)(q + 1) * np];
                     const uint32_t j[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
@@ -497,7 +584,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                         const float rinv = fast_rsqrt(r2);
                         const float sn = fast_sin(3.14159265358979323846f * (r2 * rinv) * fast_rcp(rc));
                         float fp = ev_c * rc * sn * rinv;
-                        fp = (r2 < rc * rc && r2 > 0.f) ? fp : 0.f;               // (the padding sentinel is far away)
+                        fp = (r2 < rc * rc && r2 > 0.f) ? fp : 0.f;
                         ax += dx * fp; ay += dy * fp; az += dz * fp;
                     }
                 }
@@ -521,6 +608,11 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         }
         bond_build = false;
         const long long tr0 = tick();
+        if (PROF) {                                   // how unevenly the force loops are spread over the warps
+            if (lane == 0) ((long long*)rbuf)[64 + warp] = tr0 - tf0;
+            __syncthreads();
+            if (tid == 0) { long long mx = 0, sm = 0; for (int q = 0; q < MD2_NW; q++) { const long long v = ((long long*)rbuf)[64 + q]; mx = v > mx ? v : mx; sm += v; } t_fmax += mx; t_fsum += sm / MD2_NW; }
+        }
         __syncthreads();            // every inbox flag and mailbox of this evaluation is written
         // bonds I receive: the owner's (dx, dy, dz, f/r) with the opposite sign, in inbox order; then clear the inbox
 #pragma unroll
@@ -528,19 +620,20 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             const int p = k * MD2_T + tid;
             const uint4 fl = inbox[p];
             if (fl.x | fl.y | fl.z | fl.w) {
-                const uint32_t w[4] = {fl.x, fl.y, fl.z, fl.w};
+                // flag bytes (0 / 1) -> one bit per slot; the flagged mailboxes are fetched four at a time in slot order, so an
+                // atom with up to four violated incoming bonds (nearly all) pays one L2 latency, wherever its slots lie
+                uint32_t m = (((fl.x * 0x01020408u) >> 24) & 0xfu) | ((((fl.y * 0x01020408u) >> 24) & 0xfu) << 4) |
+                             ((((fl.z * 0x01020408u) >> 24) & 0xfu) << 8) | ((((fl.w * 0x01020408u) >> 24) & 0xfu) << 12);
+                const float4* box = gf + ((size_t)p << 4);
+                while (m) {
+                    float4 f[4];
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    if (w[u]) {                          // the (up to) four mailboxes of this word are fetched together: one L2 latency
-                        float4 f[4];
-#pragma unroll
-                        for (int b = 0; b < 4; b++) {
-                            f[b] = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if ((w[u] >> (b << 3)) & 0xffu) f[b] = __ldcg(gf + ((size_t)p << 4) + (u << 2) + b);
-                        }
-#pragma unroll
-                        for (int b = 0; b < 4; b++) { fx[k] -= f[b].x * f[b].w; fy[k] -= f[b].y * f[b].w; fz[k] -= f[b].z * f[b].w; }
+                    for (int b = 0; b < 4; b++) {
+                        f[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (m) { f[b] = __ldcg(box + (__ffs(m) - 1)); m &= m - 1; }
                     }
+#pragma unroll
+                    for (int b = 0; b < 4; b++) { fx[k] -= f[b].x * f[b].w; fy[k] -= f[b].y * f[b].w; fz[k] -= f[b].z * f[b].w; }
                 }
                 inbox[p] = make_uint4(0u, 0u, 0u, 0u);
             }
@@ -680,7 +773,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         if (PROF && V.prof) {
             long long* o = V.prof + 16 * (size_t)blockIdx.x;
             o[0] = t_force; o[1] = t_search; o[2] = t_build; o[3] = n_rebuild;
-            o[4] = t_recv; o[5] = t_pair; o[6] = t_bondA;
+            o[4] = t_recv; o[5] = t_pair; o[6] = t_bondA; o[7] = t_smax; o[8] = t_ssum; o[9] = t_fmax; o[10] = t_fsum; o[11] = n_cand; o[12] = n_full; o[13] = n_nbr;
         }
     }
 }

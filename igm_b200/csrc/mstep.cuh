@@ -621,6 +621,7 @@ struct MdParams {
     float skin_factor;       // neighbour skin = skin_factor * largest bead radius.  The LAMMPS script uses 1
                              // (`neighbor maxrad bin`, lammps.py:216); results do not depend on it, only the cost
     int   debug_stage;       // k_md2: >= 0: evaluate the forces of that stage's run setup once, store them and return
+    int   general_pairs;     // k_md2: 1 = never take the uniform-radius pair loop (IGMK_GENERAL_PAIRS; tests of the general one)
 };
 
 // ---------------------------------------------------------------------------------------

@@ -65,12 +65,15 @@ def test_single_point_stage_scales_and_prefactor(ff_golden):
 MD_FORCE_RTOL = 2e-4   # float32 sums of ~30 terms + MUFU rsqrt / sin / rcp approximations (~1e-6 each), relative to max |F|
 
 
-@pytest.mark.parametrize("stage", [0, 3])
-def test_md_kernel_force_routine_matches_oracle(ff_golden, stage):
-    """The force loop k_md2 itself runs (oriented bond lists, inboxes, two-level neighbour tables, float32, hardware
+@pytest.mark.parametrize("stage,general", [(0, False), (3, False), (1, True)])
+def test_md_kernel_force_routine_matches_oracle(ff_golden, stage, general, monkeypatch):
+    """The force loop k_md2 itself runs (oriented bond lists, inboxes, neighbour tables, float32, hardware
     approximations) against the double-precision oracle: 3008 beads, every term on, the stage's pair / envelope
-    scales.  Evaluated through the full bond lists and again through the candidate lists."""
+    scales.  Evaluated through the full bond lists and again through the candidate lists.  The demo beads all have one
+    radius, which selects the pair loop specialised for that; `general` forces the loop for mixed radii."""
     from helpers import short_protocol
+    if general:
+        monkeypatch.setenv("IGMK_GENERAL_PAIRS", "1")
     prot = short_protocol()
     systems = [demo_structure(ff_golden, k) for k in (0, 3, 6, 8)]
     ev, env = prot.evfactor[stage], prot.envfactor[stage]
