@@ -25,7 +25,7 @@ namespace igmk {
 
 constexpr int ASM_T = 1024;
 constexpr int ASM_MAX_KEYS = 1024;        // distinct (r0, k, style) over the template and all rows
-constexpr int ASM_MAX_ATOMS = 8192;       // the one-CTA MD kernel's limit
+constexpr int ASM_MAX_ATOMS = 4096;       // the one-CTA MD kernel's limit
 
 // decision byte of a bond, stored at its entry in the row of the smaller atom index a (partner b > a)
 constexpr uint8_t ASM_DEC_Q = 0x0f;       // inbox slot at the receiving end

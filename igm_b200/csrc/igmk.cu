@@ -617,9 +617,9 @@ extern "C" int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* 
 static int md2_pick_K(int max_atoms)
 {
     const int need = (max_atoms + MD2_T - 1) / MD2_T;
-    const int avail[] = {1, 2, 3, 4, 6, 8};
+    const int avail[] = {1, 2, 3, 4};        // 4 slots = 4096 atoms is what one SM's 227 KB of shared memory holds (md2_smem_bytes)
     for (int k : avail) if (k >= need) return k;
-    return 0;
+    return 0;                                  // larger structures: a thread-block cluster per structure or the global-memory kernel
 }
 
 // Atom ordering + sliced-ELL bond items for the thread-per-atom MD kernel: atoms sorted by bond
@@ -891,8 +891,8 @@ static int upload(igmk_handle* h)
         if (const char* e = getenv("IGMK_FORCE_CLUSTER")) want = atoi(e);
         if (want == 0 && h->md2_K == 0 && !getenv("IGMK_FORCE_BIG") && h->max_atoms <= 65535) {
             const long long nsl = (long long)ns;
-            if (nsl * 16 <= h->sm_count) want = 16;
-            else if (nsl * 8 <= h->sm_count && h->max_atoms <= 32768) want = 8;
+            for (int cl = 16; cl >= 2 && want == 0; cl >>= 1)           // the most CTAs per structure that still leaves every cluster resident
+                if (nsl * cl <= h->sm_count && (long long)cl * 4 * MD2_T >= h->max_atoms) want = cl;
         }
         if (want == 2 || want == 4 || want == 8 || want == 16) {
             int k = 1;
@@ -1203,8 +1203,6 @@ static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
         case 2: return launch_md2_k<2>(h, B, P, ns);
         case 3: return launch_md2_k<3>(h, B, P, ns);
         case 4: return launch_md2_k<4>(h, B, P, ns);
-        case 6: return launch_md2_k<6>(h, B, P, ns);
-        case 8: return launch_md2_k<8>(h, B, P, ns);
     }
     return fail("igmk_run: no MD kernel for this structure size");
 }

@@ -43,7 +43,7 @@ namespace igmk {
 #endif
 constexpr int MD2_T = MD2_THREADS;    // threads per CTA
 constexpr int MD2_NW = MD2_T / 32;    // warps per CTA
-constexpr int MD2_KMAX = 8;           // slots per thread supported (n_atoms <= 8192 on the 1-CTA path)
+constexpr int MD2_KMAX = 4;           // slots per thread supported (n_atoms <= 4096 on the 1-CTA path: shared memory)
 constexpr int MD2_NLW0 = 256;         // initial neighbour-table width (columns)
 constexpr uint16_t MD2_NONE = 0xffffu;
 constexpr int MD2_INBOX = 16;         // flag bytes per atom; slot 15 is never used (padding items point at it)

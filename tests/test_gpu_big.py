@@ -110,6 +110,39 @@ def test_single_point_and_cg_beyond_shared_memory():
     assert res.final_energy == pytest.approx(r_ref.final_energy, rel=1e-8)
 
 
+def test_structures_between_4096_and_8192_atoms_leave_the_one_cta_kernel():
+    """5700 beads (a 1 Mb genome) do not fit one SM's shared memory in the thread-per-atom layout: a lone structure takes
+    a thread-block cluster, a batch of many the global-memory kernel; both agree with the oracle's single point and
+    bring the energy down"""
+    g, rad, ps = _big_system(n_chain=6, chain=950, seed=8)
+    assert 4096 < len(g) <= 8192
+    f_ref, e0 = ff.single_point(ps)
+    prot = short_protocol(md=120, relax=20)
+    with MStepBatch(0) as b:
+        slot = b.submit(ps)
+        b.md_forces(prot, 1)
+        f = b.fetch_forces(slot)
+        f1, _ = ff.single_point(ps, prot.evfactor[1], prot.envfactor[1], 1.0)
+        assert np.abs(f - f1).max() <= 2e-4 * np.abs(f1).max()
+        b.run(prot)
+        xyz, res = b.fetch(slot)
+    assert res.status == 0 and np.isfinite(xyz).all() and res.final_energy < 0.05 * e0["total"]
+    with MStepBatch(0) as b:                       # 40 structures: clusters of two CTAs
+        for k in range(40):
+            b.submit(ps)
+        b.run(prot)
+        many = [b.fetch(k) for k in range(40)]
+    assert all(r.status == 0 and r.final_energy < 0.05 * e0["total"] for _, r in many)
+    assert all(np.array_equal(many[0][0], x) for x, _ in many[1:])
+    with MStepBatch(0) as b:                       # more structures than clusters fit the GPU: one CTA each, state in global memory
+        for k in range(80):
+            b.submit(ps)
+        b.run(prot)
+        many = [b.fetch(k) for k in (0, 41, 79)]
+    assert all(r.status == 0 and r.final_energy < 0.05 * e0["total"] for _, r in many)
+    assert all(np.array_equal(many[0][0], x) for x, _ in many[1:])
+
+
 def test_big_structure_full_protocol():
     g, rad, ps = _big_system(seed=4)
     _, e0 = ff.single_point(ps)
