@@ -87,6 +87,7 @@ struct igmk_handle {
     // thread-per-atom MD layout (md2.cuh), built at upload time
     int md2_K = 0, md2_nlw = MD2_NLW0;
     float skin_factor = 0.7f;   // k_md_big: single-level neighbour skin in bead radii
+    float skin_cluster = 1.0f;  // k_md2c: its cluster-wide rebuild is dearer (0.6 / 0.7 / 0.8 / 1.0 -> 86 / 78 / 75 / 73 us per evaluation at 29 838 beads, tools/prof_c4.py 4 0.02)
     float skin_inner = 0.6f;    // k_md2: neighbour skin in bead radii (measured optimum once the rebuild got cheaper: 0.5 / 0.6 / 0.7 / 0.8 -> 73.8 / 72.4 / 73.6 / 75.2 ms, tools/prof_md.py 148 0.06)
     std::vector<Md2Desc> md2_desc;
     std::vector<uint16_t> md2_perm;
@@ -182,7 +183,7 @@ extern "C" int igmk_create(int device, igmk_handle_t** out)
     }
     if (const char* e = getenv("IGMK_SKIN")) {              // neighbour skin in units of the bead radius (results do not depend on it)
         const float f = (float)atof(e);
-        if (f >= 0.05f && f <= 4.0f) { h->skin_factor = f; h->skin_inner = f; }
+        if (f >= 0.05f && f <= 4.0f) { h->skin_factor = f; h->skin_inner = f; h->skin_cluster = f; }
     }
 
     CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -1230,7 +1231,7 @@ extern "C" int igmk_run(igmk_handle_t* h, const igmk_protocol_t* prot)
         cudaEvent_t e0, e1, e2;
         CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1)); CU(cudaEventCreate(&e2));
         CU(cudaEventRecord(e0, h->stream));
-        MdParams P; P.prot = *prot; P.skin_factor = h->md_big ? h->skin_factor : h->skin_inner;
+        MdParams P; P.prot = *prot; P.skin_factor = h->md_big ? h->skin_factor : (h->mdc_CL > 0 ? h->skin_cluster : h->skin_inner);
         P.debug_stage = -1; P.general_pairs = getenv("IGMK_GENERAL_PAIRS") != nullptr;
         if (int rc = launch_md2(h, B, P, ns)) return rc;
         CU(cudaEventRecord(e1, h->stream));
@@ -1281,7 +1282,7 @@ extern "C" int igmk_md_forces(igmk_handle_t* h, const igmk_protocol_t* prot, int
         CU(cudaMemsetAsync(h->d_md2_dbg, 0, h->xyzr.size() * 3 * sizeof(double), h->stream));
         Batch B = make_batch(h);
         CU(cudaMemsetAsync(h->d_flags, 0, ns * sizeof(int32_t), h->stream));
-        MdParams P; P.prot = *prot; P.skin_factor = h->skin_inner; P.debug_stage = stage; P.general_pairs = getenv("IGMK_GENERAL_PAIRS") != nullptr;
+        MdParams P; P.prot = *prot; P.skin_factor = h->mdc_CL > 0 ? h->skin_cluster : h->skin_inner; P.debug_stage = stage; P.general_pairs = getenv("IGMK_GENERAL_PAIRS") != nullptr;
         if (int rc = launch_md2(h, B, P, ns)) return rc;
         CU(cudaStreamSynchronize(h->stream));
         const int rc = collect(h, "igmk_md_forces");
