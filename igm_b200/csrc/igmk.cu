@@ -741,6 +741,7 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
         struct Own { int32_t other; uint32_t type; int8_t q; };         // q < 0: SYM
         std::vector<std::vector<Own>> rows((size_t)n);
         std::vector<int> own((size_t)n, 0), indeg((size_t)n, 0);
+        const int per_cta0 = (n + CL - 1) / CL;                         // atoms per CTA of a cluster (index order)
         for (int a = 0; a < n; a++)
             for (int c = bp[a]; c < bp[a + 1]; c++) {
                 const int b = (int)(bi[c] & 0xffffu);
@@ -760,7 +761,10 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
                 const int da = bp[a + 1] - bp[a], db = bp[b + 1] - bp[b];
                 int o = (own[a] < own[b] || (own[a] == own[b] && da >= db)) ? a : b, r = o == a ? b : a;
                 if (indeg[r] >= MD2_INBOX - 1) std::swap(o, r);
-                if (indeg[r] >= MD2_INBOX - 1) {                        // both inboxes full: evaluate from both ends
+                // k_md2c: a bond between two CTAs of the cluster is evaluated at both ends, which keeps inboxes and mailboxes
+                // CTA-local and spares the kernel one of its three cluster barriers per step
+                const bool cross = CL > 1 && a / per_cta0 != b / per_cta0;
+                if (cross || indeg[r] >= MD2_INBOX - 1) {              // (or both inboxes full): evaluate from both ends
                     rows[a].push_back({b, t, -1}); rows[b].push_back({a, t, -1});
                     own[a]++; own[b]++; nsym[s]++;
                     continue;

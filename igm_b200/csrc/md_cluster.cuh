@@ -57,6 +57,7 @@ __host__ __device__ inline size_t mdc_smem_bytes(int K)
     b += IGMK_MAX_ENVELOPES * 4 * 4;          // envelope parameters
     b += (size_t)K * MD2_NW * 16;             // bond block descriptors
     b += (size_t)K * MD2_NW * 8;              // candidate batches per warp-slot (A, B)
+    b += 16 * 16;                             // compaction table of the neighbour search
     return (b + 255) / 256 * 256;
 }
 
@@ -110,6 +111,14 @@ k_md2c(Batch B, MdcView V, const Md2Desc* __restrict__ mdesc, MdParams P)
     float* envp = cbuf + 2 * MDC_MAX_CL * 4;
     int4* eblk = (int4*)(envp + IGMK_MAX_ENVELOPES * 4);
     int2* bact = (int2*)(eblk + K * MD2_NW);
+    uint4* lut = (uint4*)(bact + K * MD2_NW);     // hit mask of four candidates -> byte selectors that pack the hits (as in k_md2)
+    if (threadIdx.x < 16) {
+        uint32_t sel[4] = {0u, 0u, 0u, 0u};
+        int nsel = 0;
+        for (int j = 0; j < 4; j++) if (threadIdx.x & (1 << j)) sel[nsel++] = (uint32_t)(2 * j) | ((uint32_t)(2 * j + 1) << 4);
+        lut[threadIdx.x] = make_uint4(sel[0] | (sel[1] << 8), sel[2] | (sel[3] << 8),
+                                      nsel >= 2 ? 0xffffffffu : (nsel == 1 ? 0xffffu : 0u), nsel >= 4 ? 0xffffffffu : (nsel == 3 ? 0xffffu : 0u));
+    }
     int rb_par = 0, cb_par = 0;
 
     const igmk_protocol_t& pr = P.prot;
@@ -320,7 +329,12 @@ k_md2c(Batch B, MdcView V, const Md2Desc* __restrict__ mdesc, MdParams P)
             }
         }
         mdc_sync();
-        for (int s0 = gt; s0 < nbead; s0 += GT) xsorted[s0] = __ldcg(xall + __ldcg(sorted + s0));
+        for (int s0 = gt; s0 < nbead; s0 += GT) {      // (the radius is not needed in the search: w carries the position index)
+            const uint32_t a = __ldcg(sorted + s0);
+            float4 v = __ldcg(xall + a);
+            v.w = __uint_as_float(a);
+            xsorted[s0] = v;
+        }
         mdc_sync();
         // search: the cluster's threads take the beads in cell order
         int ovf = 0;
@@ -330,7 +344,7 @@ k_md2c(Batch B, MdcView V, const Md2Desc* __restrict__ mdesc, MdParams P)
             int cx = (int)((q.x - lo[0]) * inv[0]), cy = (int)((q.y - lo[1]) * inv[1]), cz = (int)((q.z - lo[2]) * inv[2]);
             cx = min(max(cx, 0), dim[0] - 1); cy = min(max(cy, 0), dim[1] - 1); cz = min(max(cz, 0), dim[2] - 1);
             const int ax0 = max(cx - 1, 0), ax1 = min(cx + 1, dim[0] - 1);
-            Md2Row row(nl, p, NPS, nlw);
+            Md2RowPacked row(nl, p, NPS, nlw);
             for (int dz = -1; dz <= 1; dz++) {
                 const int az = cz + dz;
                 if (az < 0 || az >= dim[2]) continue;
@@ -339,10 +353,24 @@ k_md2c(Batch B, MdcView V, const Md2Desc* __restrict__ mdesc, MdParams P)
                     if (ay < 0 || ay >= dim[1]) continue;
                     const int cb = (az * dim[1] + ay) * dim[0];
                     const int b = (int)cell_start[cb + ax0], e = (int)cell_start[cb + ax1 + 1];
-                    for (int s2 = b; s2 < e; s2++) {
-                        const float4 pj = xsorted[s2];
-                        const float ddx = q.x - pj.x, ddy = q.y - pj.y, ddz = q.z - pj.z;
-                        if (s2 != s0 && ddx * ddx + ddy * ddy + ddz * ddz < rlist2) row.add(sorted[s2]);
+                    for (int s1 = b; s1 < e; s1 += 4) {        // four candidates at once, branch-free, hits packed through the table (md2.cuh)
+                        float4 pj[4];
+#pragma unroll
+                        for (int u = 0; u < 4; u++) pj[u] = xsorted[min(s1 + u, nbead - 1)];
+                        uint32_t hits = 0u;
+#pragma unroll
+                        for (int u = 0; u < 4; u++) {
+                            const float ddx = q.x - pj[u].x, ddy = q.y - pj[u].y, ddz = q.z - pj[u].z;
+                            hits |= (uint32_t)(ddx * ddx + ddy * ddy + ddz * ddz < rlist2) << u;
+                        }
+                        const int rem = e - s1;
+                        const uint32_t me = (uint32_t)(s0 - s1);
+                        hits &= (rem >= 4 ? 0xfu : (1u << rem) - 1u) & (me < 4u ? ~(1u << me) : ~0u);
+                        const uint32_t i01 = __byte_perm(__float_as_uint(pj[0].w), __float_as_uint(pj[1].w), 0x5410);
+                        const uint32_t i23 = __byte_perm(__float_as_uint(pj[2].w), __float_as_uint(pj[3].w), 0x5410);
+                        const uint4 L = lut[hits];
+                        const uint32_t r0 = __byte_perm(i01, i23, L.x) & L.z, r1 = __byte_perm(i01, i23, L.y) & L.w;
+                        row.append(((uint64_t)r1 << 32) | r0, __popc(hits));
                     }
                 }
             }
@@ -501,7 +529,10 @@ k_md2c(Batch B, MdcView V, const Md2Desc* __restrict__ mdesc, MdParams P)
             fx[k] = ax; fy[k] = ay; fz[k] = az;
         }
         bond_build = false;
-        mdc_sync();                 // every inbox flag and mailbox of this evaluation is written, in every CTA
+        // Every inbox flag and mailbox of this evaluation is written: oriented bonds never cross CTAs (the host lists a bond
+        // between two CTAs at both ends, SYM), so this is a CTA barrier, not a cluster barrier.  The partner positions other
+        // CTAs still gather from this one stay untouched until the cluster barrier of the kinetic-energy sum (step 0: below).
+        __syncthreads();
 #pragma unroll
         for (int k = 0; k < K; k++) {
             const int p = k * MD2_T + tid;
@@ -595,6 +626,7 @@ k_md2c(Batch B, MdcView V, const Md2Desc* __restrict__ mdesc, MdParams P)
                     return;
                 }
                 float need_f = 0.f;
+                if (step == 0) mdc_sync();      // no kinetic-energy sum in the run setup: every CTA has read the positions before any drifts
                 if (step > 0) {
                     float ke = 0.f;
 #pragma unroll

@@ -29,7 +29,7 @@ sys.path.insert(0, HERE)
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
-import h5lite                      # noqa: E402
+from igm_b200 import h5lite     # noqa: E402
 import refstub                     # noqa: E402
 from oracle import astep_oracle    # noqa: E402
 
