@@ -857,6 +857,7 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
 }
 
 static int upload_dev_rebuild(igmk_handle* h);
+static int mdc_resident_clusters(int K, int CL);
 
 static int upload(igmk_handle* h)
 {
@@ -886,18 +887,28 @@ static int upload(igmk_handle* h)
     h->md2_K = md2_pick_K(h->max_atoms);
     h->md_big = h->md2_K == 0 || getenv("IGMK_FORCE_BIG") != nullptr;   // the variable routes small batches through md_big.cuh (tests)
     h->mdc_CL = 0;
-    {   // more than 8192 atoms: a thread-block cluster per structure (md_cluster.cuh); IGMK_FORCE_CLUSTER=<CTAs> sends smaller
-        // structures there too (tests, latency of small populations), IGMK_FORCE_BIG keeps the one-CTA global-memory kernel
-        // The cluster kernel gives the lowest time per structure (measured at 29 838 beads: 78 us per force evaluation on 16
-        // CTAs, 123 us on 8, against 860-1250 us for the one-CTA global-memory kernel), the one-CTA kernel the highest
-        // throughput once there are more structures than clusters fit the GPU (148 structures at once: 8.5 us per structure
-        // and evaluation against 13.6 us for 18 clusters of 8).  So: clusters while all of them are resident at once.
+    {   // more than 4096 atoms: a thread-block cluster per structure (md_cluster.cuh); IGMK_FORCE_CLUSTER=<CTAs> sends smaller
+        // structures there too (tests), IGMK_FORCE_BIG keeps the one-CTA global-memory kernel
         int want = 0;
         if (const char* e = getenv("IGMK_FORCE_CLUSTER")) want = atoi(e);
         if (want == 0 && h->md2_K == 0 && !getenv("IGMK_FORCE_BIG") && h->max_atoms <= 65535) {
+            // Cheapest of: one CTA per structure with the state in global memory (k_md_big: 29 ns per atom and evaluation,
+            // every SM busy once there are 148 structures), or clusters of 16 / 8 / 4 / 2 CTAs run in waves of as many
+            // clusters as the device holds at once (the driver's answer: a cluster must sit inside one GPC, so a B200 holds
+            // 8 clusters of 16, not 148 / 16 = 9).  Cluster cost per atom and evaluation measured at 29 838 beads
+            // (tools/prof_c4.py, round 2): 2.1 ns on 16 CTAs, 3.2 ns on 8; smaller clusters extrapolated with the same slope.
             const long long nsl = (long long)ns;
-            for (int cl = 16; cl >= 2 && want == 0; cl >>= 1)           // the most CTAs per structure that still leaves every cluster resident
-                if (nsl * cl <= h->sm_count && (long long)cl * 4 * MD2_T >= h->max_atoms) want = cl;
+            double best = (double)((nsl + h->sm_count - 1) / h->sm_count) * 29.0;
+            for (int cl = 16; cl >= 2; cl >>= 1) {
+                if ((long long)cl * 4 * MD2_T < h->max_atoms) continue;
+                int k = 1;
+                while (k < 4 && k * MD2_T * cl < h->max_atoms) k *= 2;
+                const int resident = mdc_resident_clusters(k, cl);
+                if (resident <= 0) continue;
+                const double cost = (double)((nsl + resident - 1) / resident) * 2.1 * pow(16.0 / cl, 0.585);
+                if (cost < best) { best = cost; want = cl; }
+                if (getenv("IGMK_TRACE")) fprintf(stderr, "[igmk trace] %d clusters of %d CTAs (K = %d) fit the device; cost %.1f\n", resident, cl, k, cost);
+            }
         }
         if (want == 2 || want == 4 || want == 8 || want == 16) {
             int k = 1;
@@ -1175,6 +1186,35 @@ static int launch_mdc_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
     cfg.attrs = at; cfg.numAttrs = 1;
     const Md2Desc* md = h->d_md2_desc;
     CU(cudaLaunchKernelEx(&cfg, kern, B, V, md, P));
+    return 0;
+}
+
+template <int K, int CL>
+static int mdc_resident_clusters_k()
+{
+    const size_t sm = mdc_smem_bytes(K);
+    auto kern = k_md2c<K, CL, false>;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (CL > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 0; }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3((unsigned)CL); cfg.blockDim = dim3(MD2_T); cfg.dynamicSmemBytes = sm;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// clusters of CL CTAs of k_md2c<K, CL> the device holds at once (0: no such kernel)
+static int mdc_resident_clusters(int K, int CL)
+{
+#define MDC_CASE(k, c) if (K == k && CL == c) return mdc_resident_clusters_k<k, c>()
+    MDC_CASE(1, 2); MDC_CASE(2, 2); MDC_CASE(4, 2); MDC_CASE(1, 4); MDC_CASE(2, 4); MDC_CASE(4, 4);
+    MDC_CASE(1, 8); MDC_CASE(2, 8); MDC_CASE(4, 8); MDC_CASE(1, 16); MDC_CASE(2, 16); MDC_CASE(4, 16);
+#undef MDC_CASE
     return 0;
 }
 

@@ -538,19 +538,19 @@ k_md2c(Batch B, MdcView V, const Md2Desc* __restrict__ mdesc, MdParams P)
             const int p = k * MD2_T + tid;
             const uint4 fl = inbox[p];
             if (fl.x | fl.y | fl.z | fl.w) {
-                const uint32_t w[4] = {fl.x, fl.y, fl.z, fl.w};
+                // one bit per slot; the flagged mailboxes are fetched four at a time in slot order (as in k_md2)
+                uint32_t m = (((fl.x * 0x01020408u) >> 24) & 0xfu) | ((((fl.y * 0x01020408u) >> 24) & 0xfu) << 4) |
+                             ((((fl.z * 0x01020408u) >> 24) & 0xfu) << 8) | ((((fl.w * 0x01020408u) >> 24) & 0xfu) << 12);
+                const float4* box = gf + ((size_t)(rank * np + p) << 4);
+                while (m) {
+                    float4 f[4];
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    if (w[u]) {
-                        float4 f[4];
-#pragma unroll
-                        for (int b = 0; b < 4; b++) {
-                            f[b] = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if ((w[u] >> (b << 3)) & 0xffu) f[b] = __ldcg(gf + ((size_t)(rank * np + p) << 4) + (u << 2) + b);
-                        }
-#pragma unroll
-                        for (int b = 0; b < 4; b++) { fx[k] -= f[b].x * f[b].w; fy[k] -= f[b].y * f[b].w; fz[k] -= f[b].z * f[b].w; }
+                    for (int b = 0; b < 4; b++) {
+                        f[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (m) { f[b] = __ldcg(box + (__ffs(m) - 1)); m &= m - 1; }
                     }
+#pragma unroll
+                    for (int b = 0; b < 4; b++) { fx[k] -= f[b].x * f[b].w; fy[k] -= f[b].y * f[b].w; fz[k] -= f[b].z * f[b].w; }
                 }
                 inbox[p] = make_uint4(0u, 0u, 0u, 0u);
             }

@@ -58,6 +58,7 @@ def test_cluster_md_kernel_follows_the_single_cta_one(monkeypatch, cl):
     prot.n_stage = 2
     prot.skip_minimize = 1
     out = []
+    monkeypatch.setenv("IGMK_SKIN", "0.7")                     # the two kernels default to different neighbour skins
     for force in (False, True, True):
         if force:
             monkeypatch.setenv("IGMK_FORCE_CLUSTER", str(cl))

@@ -5,7 +5,7 @@
 c3: 2 Mb diploid (3008 beads), Hi-C + lamina DamID + ellipsoidal envelope (7840, 6470, 2450) + FISH: 500 pairs and
     300 radial probes, rtype "rRpP" (restraint set of igm-config_all.json)
 c4: 200 kb diploid (29 838 beads), Hi-C + SPRITE, through the cluster-per-structure MD kernel (a thread-block cluster
-    of 16 CTAs per structure while all clusters are resident at once)
+    per structure: 16 CTAs up to 7 structures, 8 CTAs in waves of 15 beyond -- upload() in igmk.cu)
 Both are run on FEWER structures than the 1000 of the BASELINE text so that the default bench stays within minutes;
 the number is in the line.  Synthetic inputs, seeded."""
 import json
@@ -73,7 +73,7 @@ def run_c3(device=0, S=296, n_pairs=300000):
             "restraints_violated": int(v[:, 1].sum() + v[:, 3].sum())}
 
 
-def run_c4(device=0, S=9, n_clusters=2000):
+def run_c4(device=0, S=8, n_clusters=2000):
     g = synth.genome_200kb()
     n = len(g)
     rad = synth.bead_radii(n, 5500.0, 0.4)
@@ -130,7 +130,7 @@ def run_c4(device=0, S=9, n_clusters=2000):
             "structures": S, "beads": n, "seconds": t_astep + t_mstep, "astep_seconds": t_astep, "mstep_seconds": t_mstep,
             "md_kernel_ms": tim["md_kernel_ms"], "cg_kernel_ms": tim["cg_kernel_ms"], "md_force_evals": evals,
             "us_per_force_eval_and_structure": tim["md_kernel_ms"] * 1e3 / evals,
-            "cluster_ctas": 16 if S * 16 <= 148 else (8 if S * 8 <= 148 else 1),
+            "cluster_ctas": 16 if S <= 7 else 8,      # upload()'s choice at this size: a B200 holds 7 clusters of 16 CTAs or 15 of 8 at once
             "hic_pairs": int(pairs[0].size), "hic_bonds_per_structure": float(np.bitwise_count(bits).sum()) / S,
             "sprite_clusters": n_clusters, "sprite_select_kernel_ms": sprite_ms, "actdist_kernel_ms": actdist_ms,
             "sprite_centroids_per_structure": float(atoms[0][-1]) / S, "relax_init_seconds": t_relax,
