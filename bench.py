@@ -7,9 +7,13 @@ Workload (BASELINE.json configs[1]): 2 Mb diploid genome (3008 beads + the envel
 1000 structures PER GPU (weak scaling), spherical envelope, Hi-C restraints assigned at one
 sigma, the demo's full annealing protocol (4 x [relax 500 + 5k/15k/15k/10k MD steps] + CG).
 A "step" = one M-step over the rank's structures.  `value` = structures/s with everything
-resident in HBM; `e2e` = the same from host buffers through igm_b200.kernel.run_population
-(chunked submit -> upload -> run -> fetch over the C ABI, chunks pipelined on streams).  The A-step (activation distances + assignment over all structures x pairs) is
-timed in the same run and reported under "astep".
+resident in HBM; `e2e` = the same from HOST buffers through igm_b200.iteration.mstep_population:
+coordinates + actdist rows up, contact assignment and the assembly of every structure on the device
+(igmk_submit_population_dev), MD + CG, optimised coordinates back; `e2e_host_assembly` = the round-1 form,
+igm_b200.kernel.run_population with the assignment bit matrix on the host (chunked submit -> upload -> run ->
+fetch over the C ABI, chunks pipelined on streams); `e2e_plugin` = per-structure optimize(model, cfg) calls
+under B200Controller.  The A-step (activation distances + assignment over all structures x pairs) is
+timed in the same run and reported under "astep"; "am_iteration" is a whole A/M iteration from host coordinates.
 """
 import argparse
 import json

@@ -5,11 +5,14 @@
 // ordering that follows the genome (a chromosome territory is compact in space, so most partners of an atom live in
 // the same CTA) and, inside a CTA, sorts by owned bonds like k_md2.  Every CTA keeps ITS atoms' positions in its own
 // shared memory and their velocities / forces in registers; a partner position is read through distributed shared
-// memory (mapa + ld.shared::cluster: the owning CTA is encoded in the index), an inbox flag of a remote receiver is
-// set with st.shared::cluster, the mailboxes of violated bonds go through global memory as in k_md2.  The loops, the
-// arithmetic and the list layouts are those of md2.cuh (thread per atom, oriented bonds, inbox / mailbox, candidate
-// lists); what changes is the scope of the synchronisation -- three cluster barriers per step (positions written,
-// inboxes written, kinetic energy summed) instead of three CTA barriers -- and the neighbour rebuild, which needs
+// memory (mapa + ld.shared::cluster: the owning CTA is encoded in the index).  Oriented bonds (owner / receiver, inbox
+// flag + mailbox as in k_md2) exist only between atoms of ONE CTA; the host lists a bond between two CTAs at both ends
+// (SYM), so inboxes and mailboxes are CTA-local and the barrier before the receive is a __syncthreads.  (The
+// st.shared::cluster path for a remote inbox flag is still there; the layout no longer produces such items.)  The loops,
+// the arithmetic and the list layouts are those of md2.cuh (thread per atom, oriented bonds, candidate lists); what
+// changes is the scope of the synchronisation -- two cluster barriers per step (kinetic energy summed = every CTA has
+// read the positions; positions written + rebuild flag) and one CTA barrier instead of three CTA barriers -- and the
+// neighbour rebuild, which needs
 // the whole structure: the cluster bins all beads into ONE cell grid in global memory (counts, scan by CTA 0,
 // scatter, per-cell sort, cell-ordered copy of the positions), then every CTA searches its share of the beads IN CELL
 // ORDER (not its own atoms: even load, lanes of a warp scan the same cells so the reads hit L1) and writes their
