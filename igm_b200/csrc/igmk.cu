@@ -2200,12 +2200,27 @@ static int upload_dev_rebuild(igmk_handle* h)
     return 0;
 }
 
+static int submit_population_dev_impl(igmk_handle_t* h, const igmk_system_t* tmpl, igmk_pop_t* pop, int32_t s_begin,
+                                      int32_t n_struct, const int64_t* seeds, int32_t* first_slot_out);
+
 extern "C" int igmk_submit_population_dev(igmk_handle_t* h, const igmk_system_t* tmpl, igmk_pop_t* pop, int32_t s_begin,
                                           int32_t n_struct, const int64_t* seeds, int32_t* first_slot_out)
 {
     if (!h || !tmpl || !pop) return fail("igmk_submit_population_dev: NULL argument");
-    if (h->device < 0 || h->device != pop->device) return fail("igmk_submit_population_dev: batch and population must live on the same GPU");
     if (!h->desc.empty()) return fail("igmk_submit_population_dev: the batch must be empty (igmk_clear)");
+    const int rc = submit_population_dev_impl(h, tmpl, pop, s_begin, n_struct, seeds, first_slot_out);
+    if (rc != 0) {                         // leave no half-assembled batch behind (the message of the failure is kept)
+        const std::string msg = g_err;
+        igmk_clear(h);
+        g_err = msg;
+    }
+    return rc;
+}
+
+static int submit_population_dev_impl(igmk_handle_t* h, const igmk_system_t* tmpl, igmk_pop_t* pop, int32_t s_begin,
+                                      int32_t n_struct, const int64_t* seeds, int32_t* first_slot_out)
+{
+    if (h->device < 0 || h->device != pop->device) return fail("igmk_submit_population_dev: batch and population must live on the same GPU");
     if (n_struct <= 0 || s_begin < 0 || s_begin + n_struct > pop->n_struct) return fail("igmk_submit_population_dev: bad structure range");
     if (!pop->d_crd) return fail("igmk_submit_population_dev: the population has no coordinates");
     if (pop->n_rows > 0 && !pop->assign_done) return fail("igmk_submit_population_dev: no assignment on the device (igmk_pop_assign_launch)");
