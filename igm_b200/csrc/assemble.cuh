@@ -25,7 +25,7 @@ namespace igmk {
 
 constexpr int ASM_T = 1024;
 constexpr int ASM_MAX_KEYS = 1024;        // distinct (r0, k, style) over the template and all rows
-constexpr int ASM_MAX_ATOMS = 4096;       // the one-CTA MD kernel's limit
+constexpr int ASM_MAX_ATOMS = 3840;       // the one-CTA MD kernel's limit (5 atoms per thread x 768 threads)
 
 // decision byte of a bond, stored at its entry in the row of the smaller atom index a (partner b > a)
 constexpr uint8_t ASM_DEC_Q = 0x0f;       // inbox slot at the receiving end
@@ -294,14 +294,14 @@ k_asm_orient(AsmIn I, AsmOut O)
 }
 
 // dynamic shared memory: own uint16 [n_atoms], cols int [2 * K * 32]
-__host__ __device__ inline size_t asm_layout_smem(int n_atoms, int K) { return ((size_t)n_atoms + 1) / 2 * 4 + (size_t)2 * K * MD2_NW * sizeof(int); }
+__host__ __device__ inline size_t asm_layout_smem(int n_atoms, int K) { return ((size_t)n_atoms + 1) / 2 * 4 + (size_t)2 * K * MD2S_NW * sizeof(int); }
 
 __global__ void __launch_bounds__(ASM_T)
 k_asm_layout(AsmIn I, AsmOut O)
 {
     extern __shared__ int asm_sl[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int s = blockIdx.x, n = I.n_atoms, K = O.K, np = K * MD2_T, G = K * MD2_NW;
+    const int s = blockIdx.x, n = I.n_atoms, K = O.K, np = K * MD2S_T, G = K * MD2S_NW;
     const StructDesc d = O.desc[s];
     uint16_t* own = (uint16_t*)asm_sl;
     int* cols = asm_sl + (n + 1) / 2;                    // [G][2]
@@ -317,19 +317,18 @@ k_asm_layout(AsmIn I, AsmOut O)
         int q = 0;
         for (int x = 0; x < n; x++) { const int o = own[x]; q += (o > my) || (o == my && x < a); }
         const int g = q >> 5, l = q & 31;
-        const int k = g / MD2_NW, r = g % MD2_NW;
-        const int gi = k * MD2_NW + ((k & 1) ? MD2_NW - 1 - r : r);       // boustrophedon over the warps
+        const int k = g / MD2S_NW, r = g % MD2S_NW;
+        const int gi = k * MD2S_NW + ((k & 1) ? MD2S_NW - 1 - r : r);     // boustrophedon over the warps of the MD kernel
         const int p = gi * 32 + l;
         perm[p] = (uint16_t)a; pos[a] = (uint16_t)p;
     }
     __syncthreads();
-    for (int k = 0; k < K; k++) {
-        const int p = k * MD2_T + tid;
+    for (int p = tid; p < np; p += ASM_T) {              // a warp of this kernel = 32 consecutive positions = one warp-slot
         const uint16_t a = perm[p];
         int ca = 0, cb = 0;
         if (a != MD2_NONE) { ca = cA[a]; cb = cB[a]; }
         ca = warp_max(ca); cb = warp_max(cb);
-        if (lane == 0) { cols[2 * (k * MD2_NW + warp)] = (ca + 3) / 4 * 4; cols[2 * (k * MD2_NW + warp) + 1] = (cb + 3) / 4 * 4; }
+        if (lane == 0) { cols[2 * (p >> 5)] = (ca + 3) / 4 * 4; cols[2 * (p >> 5) + 1] = (cb + 3) / 4 * 4; }
     }
     __syncthreads();
     if (tid == 0) {
@@ -349,7 +348,7 @@ __global__ void __launch_bounds__(ASM_T)
 k_asm_ell(AsmIn I, AsmOut O)
 {
     const int tid = threadIdx.x, lane = tid & 31;
-    const int s = blockIdx.x, K = O.K, np = K * MD2_T, G = K * MD2_NW;
+    const int s = blockIdx.x, K = O.K, np = K * MD2S_T, G = K * MD2S_NW;
     const StructDesc d = O.desc[s];
     const Md2Desc md = O.mdesc[s];
     const uint16_t* perm = O.perm + (size_t)s * np;
@@ -361,8 +360,7 @@ k_asm_ell(AsmIn I, AsmOut O)
     const uint8_t* dec = O.dec + d.bond_item_off;
     const uint16_t* pos = O.pos + d.atom_off;
     const bool a_ok = O.btype_f[d.btype_off].y > 0.f;
-    for (int k = 0; k < K; k++) {
-        const int p = k * MD2_T + tid;
+    for (int p = tid; p < np; p += ASM_T) {
         const int4 eb = eblk[p >> 5];
         // padding = an item to oneself; layout [batch of 4 columns][lane][4]
         for (int c = 0; c < eb.y * 4; c++) out[eb.x + ((c >> 2) * 32 + lane) * 4 + (c & 3)] = ((uint32_t)p << 4) | 15u;

@@ -617,8 +617,8 @@ extern "C" int igmk_submit_population_ex(igmk_handle_t* h, const igmk_system_t* 
 // slots per thread the MD kernel is instantiated for
 static int md2_pick_K(int max_atoms)
 {
-    const int need = (max_atoms + MD2_T - 1) / MD2_T;
-    const int avail[] = {1, 2, 3, 4};        // 4 slots = 4096 atoms is what one SM's 227 KB of shared memory holds (md2_smem_bytes)
+    const int need = (max_atoms + MD2S_T - 1) / MD2S_T;
+    const int avail[] = {1, 2, 3, 4, 5};     // 5 slots x 768 threads = 3840 atoms is what one SM's 227 KB of shared memory holds (md2_smem_bytes)
     for (int k : avail) if (k >= need) return k;
     return 0;                                  // larger structures: a thread-block cluster per structure or the global-memory kernel
 }
@@ -717,7 +717,8 @@ static void md2_build(igmk_handle* h)
 // and the item fields are wider.
 static void md2_build_owner(igmk_handle* h, int CL = 1)
 {
-    const int K = h->md2_K, npc = K * MD2_T, np = npc * CL, NW = MD2_NW, G = K * NW * CL;
+    const int T = CL > 1 ? MD2_T : MD2S_T;                           // threads per CTA: k_md2c / k_md2
+    const int K = h->md2_K, npc = K * T, np = npc * CL, NW = T / 32, G = K * NW * CL;
     const uint32_t SYM = CL > 1 ? MDC_IT_SYM : MD2_IT_SYM;
     const int TSHIFT = CL > 1 ? MDC_IT_TSHIFT : MD2_IT_TSHIFT;
     const uint32_t MAXT = CL > 1 ? (uint32_t)MDC_MAX_TYPES : (uint32_t)MD2_MAX_TYPES;
@@ -786,7 +787,7 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
                 for (int l = 0; l < 32; l++) {
                     const int q = g * 32 + l;
                     if (q >= nr) break;
-                    const int p = r * npc + k * MD2_T + w * 32 + l;
+                    const int p = r * npc + k * T + w * 32 + l;
                     perm[p] = (uint16_t)order[a0 + q]; pos[order[a0 + q]] = p;
                 }
             }
@@ -798,7 +799,7 @@ static void md2_build_owner(igmk_handle* h, int CL = 1)
         int4* eb = h->md2_eblk.data() + m.ell_desc_off;
         std::vector<uint32_t>& out = items[s];
         for (int gi = 0; gi < G; gi++) {               // blocks in (CTA, slot, warp) order = the order the kernel indexes them
-            const int w = gi % NW, p0 = (gi / NW) * MD2_T + w * 32;       // first position of the warp-slot ((CTA * K + slot) * 1024 + warp * 32)
+            const int w = gi % NW, p0 = (gi / NW) * T + w * 32;           // first position of the warp-slot ((CTA * K + slot) * T + warp * 32)
             int cols[2] = {0, 0};
             for (int l = 0; l < 32; l++) {
                 const int a = perm[p0 + l];
@@ -1147,8 +1148,8 @@ static int launch_md2_k(igmk_handle* h, const Batch& B, const MdParams& P, int n
     V.prof = nullptr;
     const bool prof = getenv("IGMK_PROF") != nullptr && P.debug_stage < 0;
     if (prof) { CU(cudaMalloc((void**)&V.prof, (size_t)ns * 16 * sizeof(long long))); CU(cudaMemsetAsync(V.prof, 0, (size_t)ns * 16 * sizeof(long long), h->stream)); }
-    if (prof) k_md2<K, true><<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
-    else k_md2<K, false><<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
+    if (prof) k_md2<K, true><<<ns, MD2S_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
+    else k_md2<K, false><<<ns, MD2S_T, sm, h->stream>>>(B, V, h->d_md2_desc, P);
     CU(cudaGetLastError());
     if (prof) {                  // diagnostics only: per-phase SM cycles of thread 0, averaged over the structures
         std::vector<long long> t((size_t)ns * 16);
@@ -1248,6 +1249,7 @@ static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
         case 2: return launch_md2_k<2>(h, B, P, ns);
         case 3: return launch_md2_k<3>(h, B, P, ns);
         case 4: return launch_md2_k<4>(h, B, P, ns);
+        case 5: return launch_md2_k<5>(h, B, P, ns);
     }
     return fail("igmk_run: no MD kernel for this structure size");
 }
@@ -2186,7 +2188,7 @@ static int alloc_run_buffers(igmk_handle* h)
 {
     const size_t na = h->xyzr.size(), ns = h->desc.size();
     CU(cudaMalloc((void**)&h->d_nl, std::max<size_t>(na, 1) * h->nl_width * sizeof(uint16_t)));
-    CU(cudaMalloc((void**)&h->d_md2_nl, ns * (size_t)h->md2_K * MD2_T * (size_t)h->md2_nlw * sizeof(uint16_t)));
+    CU(cudaMalloc((void**)&h->d_md2_nl, ns * (size_t)h->md2_K * MD2S_T * (size_t)h->md2_nlw * sizeof(uint16_t)));
     return 0;
 }
 
@@ -2334,7 +2336,7 @@ static int submit_population_dev_impl(igmk_handle_t* h, const igmk_system_t* tmp
     if ((size_t)n_struct * (size_t)(n + 1) > (size_t)INT32_MAX) return fail("igmk_submit_population_dev: batch too large");
     const size_t na = (size_t)n_struct * n;
     h->md2_K = md2_pick_K(n); h->md_big = false; h->mdc_CL = 0;
-    const int K = h->md2_K, np = K * MD2_T, GW = K * MD2_NW;
+    const int K = h->md2_K, np = K * MD2S_T, GW = K * MD2S_NW;
     // ---- batch arrays ----
     CU(cudaMalloc((void**)&h->d_desc, (size_t)n_struct * sizeof(StructDesc)));
     CU(cudaMemcpyAsync(h->d_desc, h->desc.data(), (size_t)n_struct * sizeof(StructDesc), cudaMemcpyHostToDevice, h->stream));
@@ -2431,7 +2433,7 @@ extern "C" int igmk_debug_fetch_array(igmk_handle_t* h, int32_t which, void* out
             btypes = dl.btype_off + std::max(nty, 2);
         }
         if (h->md2_K > 0 && !h->md_big && h->mdc_CL == 0) {
-            const int GW = h->md2_K * MD2_NW;
+            const int GW = h->md2_K * MD2S_NW;
             int4 e;
             CU(copy_on(h->stream, &e, h->d_md2_eblk + ns * (size_t)GW - 1, sizeof(int4), cudaMemcpyDeviceToHost));
             ell = h->md2_desc.back().ell_item_off + e.z + (int64_t)e.w * 4 * 32;
@@ -2450,8 +2452,8 @@ extern "C" int igmk_debug_fetch_array(igmk_handle_t* h, int32_t which, void* out
         case 7: src = h->d_btype_f; bytes = btypes * sizeof(float2); break;
         case 8: src = h->d_btype_d; bytes = btypes * sizeof(double2); break;
         case 9: src = h->d_md2_desc; bytes = ns * sizeof(Md2Desc); break;
-        case 10: src = h->d_md2_perm; bytes = ns * (size_t)K * MD2_T * sizeof(uint16_t); break;
-        case 11: src = h->d_md2_eblk; bytes = ns * (size_t)K * MD2_NW * sizeof(int4); break;
+        case 10: src = h->d_md2_perm; bytes = ns * (size_t)K * (h->mdc_CL > 0 ? MD2_T * h->mdc_CL : MD2S_T) * sizeof(uint16_t); break;
+        case 11: src = h->d_md2_eblk; bytes = ns * (size_t)K * (h->mdc_CL > 0 ? MD2_NW * h->mdc_CL : MD2S_NW) * sizeof(int4); break;
         case 12: src = h->d_md2_ell_items; bytes = ell * sizeof(uint32_t); break;
         default: return fail("igmk_debug_fetch_array: no such array");
     }

@@ -1,6 +1,6 @@
 // md2.cuh -- the annealing-MD kernel of the M-step (lammps.py:285-351), one CTA per structure.
 //
-// Work decomposition: THREAD PER ATOM.  Thread t owns the atoms at positions t, t+1024, ...
+// Work decomposition: THREAD PER ATOM.  Thread t of 768 owns the atoms at positions t, t+768, ...
 // (K slots per thread) of a host-chosen ordering in which the 32 atoms of a warp-slot own similar
 // numbers of bonds.  Velocities and forces of a thread's atoms live in registers; shared memory holds
 // what other threads read: the positions (float4 x,y,z,radius), the coordinates of the last neighbour
@@ -41,9 +41,18 @@ namespace igmk {
 #ifndef MD2_THREADS
 #define MD2_THREADS 1024
 #endif
-constexpr int MD2_T = MD2_THREADS;    // threads per CTA
+constexpr int MD2_T = MD2_THREADS;    // threads per CTA of the cluster and global-memory kernels (md_cluster.cuh, md_big.cuh)
 constexpr int MD2_NW = MD2_T / 32;    // warps per CTA
-constexpr int MD2_KMAX = 4;           // slots per thread supported (n_atoms <= 4096 on the 1-CTA path: shared memory)
+// k_md2 runs 768 threads: 80 registers per thread instead of 64 (no spills in the force loops, loads further ahead of
+// their use) are worth more than a fourth more warps.  Measured on the 3008-bead bench structures, same positions per CTA
+// (3072): 512 x 6 / 640 x 5 / 768 x 4 / 1024 x 3 threads x atoms per thread -> 68.5 / 67.0 / 66.7 / 71.9 ms
+// (tools/prof_md.py 148 0.06); 896 x 4 = 3584 positions: 76.0.
+#ifndef MD2S_THREADS
+#define MD2S_THREADS 768
+#endif
+constexpr int MD2S_T = MD2S_THREADS;
+constexpr int MD2S_NW = MD2S_T / 32;
+constexpr int MD2_KMAX = 5;           // slots per thread supported (n_atoms <= 3840 on the 1-CTA path: shared memory)
 constexpr int MD2_NLW0 = 256;         // initial neighbour-table width (columns)
 constexpr uint16_t MD2_NONE = 0xffffu;
 constexpr int MD2_INBOX = 16;         // flag bytes per atom; slot 15 is never used (padding items point at it)
@@ -89,7 +98,7 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr)
 
 __host__ __device__ inline size_t md2_smem_bytes(int K)
 {
-    const size_t np = (size_t)K * MD2_T;
+    const size_t np = (size_t)K * MD2S_T;
     size_t b = (np + 1) * 16;                 // x + one sentinel position far away (padding of the neighbour rows)
     b += np * 16;                             // positions in cell order (neighbour search) / bond inboxes (between rebuilds)
     b += np * 12;                             // build coordinates
@@ -97,8 +106,8 @@ __host__ __device__ inline size_t md2_smem_bytes(int K)
     b += np * 2 * 2;                          // cell_atoms, cell_of (= row lengths between rebuilds)
     b += 2 * 32 * 8 * 4;                      // reduction scratch
     b += IGMK_MAX_ENVELOPES * 4 * 4;          // envelope parameters
-    b += (size_t)K * MD2_NW * 16;             // bond block descriptors
-    b += (size_t)K * MD2_NW * 8;              // candidate batches per warp-slot (A, B)
+    b += (size_t)K * MD2S_NW * 16;             // bond block descriptors
+    b += (size_t)K * MD2S_NW * 8;              // candidate batches per warp-slot (A, B)
     b += 16 * 16;                             // compaction table of the neighbour search
     return (b + 255) / 256 * 256;
 }
@@ -163,12 +172,12 @@ struct Md2RowPacked {
 
 // PROF: per-phase clock64 counters (IGMK_PROF=1); a separate instantiation, because the counters cost ~14 registers
 template <int K, bool PROF = false>
-__global__ void __launch_bounds__(MD2_T, 1)
+__global__ void __launch_bounds__(MD2S_T, 1)
 k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
 {
     extern __shared__ __align__(16) unsigned char smem[];
-    constexpr int np = K * MD2_T;
-    static_assert((size_t)np * 16 >= (size_t)MAX_CELLS * 4, "the cell cursors of the rebuild live in the cell-ordered copy");
+    constexpr int np = K * MD2S_T;
+    constexpr int CELL_CAP = (np * 4 < MAX_CELLS) ? np * 4 : MAX_CELLS;   // the cell cursors of the rebuild live in the cell-ordered copy (16 B per position)
     const StructDesc* d = B.desc + blockIdx.x;
     const Md2Desc md = mdesc[blockIdx.x];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -184,8 +193,8 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     float* rbuf = (float*)(cell_of + np);
     float* envp = rbuf + 2 * 256;
     int4* eblk = (int4*)(envp + IGMK_MAX_ENVELOPES * 4);    // [K*32]
-    int2* bact = (int2*)(eblk + K * MD2_NW);                 // [K*32] candidate batches (A, B)
-    uint4* lut = (uint4*)(bact + K * MD2_NW);                // [16] hit mask of four candidates -> byte selectors that pack the hits
+    int2* bact = (int2*)(eblk + K * MD2S_NW);                 // [K*32] candidate batches (A, B)
+    uint4* lut = (uint4*)(bact + K * MD2S_NW);                // [16] hit mask of four candidates -> byte selectors that pack the hits
     unsigned char* flagb = (unsigned char*)inbox;
     int rb_par = 0;
 
@@ -204,7 +213,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     float vx[K], vy[K], vz[K], fx[K], fy[K], fz[K];
 #pragma unroll
     for (int k = 0; k < K; k++) {
-        const int p = k * MD2_T + tid;
+        const int p = k * MD2S_T + tid;
         const uint16_t a = perm[p];
         float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
         meta[k] = 3u;
@@ -218,10 +227,10 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     int uni = 1;
 #pragma unroll
     for (int k = 0; k < K; k++) {
-        const int p = k * MD2_T + tid;
+        const int p = k * MD2S_T + tid;
         if ((meta[k] & 3u) == IGMK_KIND_BEAD && x[p].w != d->maxrad) uni = 0;
     }
-    if (tid < K * MD2_NW) { eblk[tid] = V.eblk[md.ell_desc_off + tid]; bact[tid] = make_int2(0, 0); }
+    if (tid < K * MD2S_NW) { eblk[tid] = V.eblk[md.ell_desc_off + tid]; bact[tid] = make_int2(0, 0); }
     if (tid == 0) x[np] = make_float4(1e18f, 1e18f, 1e18f, 0.f);
     if (tid < 16) {          // candidates j = 0..3 sit in 16-bit lane j of (i01, i23); lane t of the output takes the t-th set bit
         uint32_t sel[4] = {0u, 0u, 0u, 0u};
@@ -248,7 +257,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         v = warp_sum(v);
         if (lane == 0) buf[warp] = v;
         __syncthreads();
-        return warp_sum(lane < MD2_NW ? buf[lane] : 0.f);     // <= 32 partials: one per lane, same tree in every warp
+        return warp_sum(lane < MD2S_NW ? buf[lane] : 0.f);     // <= 32 partials: one per lane, same tree in every warp
     };
 
     auto set_stage = [&](double ev_scale, double env_scale) {
@@ -268,7 +277,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
+            const int p = k * MD2S_T + tid;
             const float4 q = x[p];
             if ((meta[k] & 3u) == IGMK_KIND_BEAD) {
                 lo[0] = fminf(lo[0], q.x); hi[0] = fmaxf(hi[0], q.x);
@@ -283,11 +292,11 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
 #pragma unroll
             for (int c = 0; c < 3; c++) { rb[warp * 6 + c] = lo[c]; rb[warp * 6 + 3 + c] = hi[c]; }
         }
-        for (int c = tid; c <= MAX_CELLS; c += MD2_T) cell_start[c] = 0;
+        for (int c = tid; c <= MAX_CELLS; c += MD2S_T) cell_start[c] = 0;
         __syncthreads();
 #pragma unroll
         for (int c = 0; c < 3; c++) {
-            lo[c] = warp_min(lane < MD2_NW ? rb[lane * 6 + c] : 1e30f); hi[c] = warp_max(lane < MD2_NW ? rb[lane * 6 + 3 + c] : -1e30f);
+            lo[c] = warp_min(lane < MD2S_NW ? rb[lane * 6 + c] : 1e30f); hi[c] = warp_max(lane < MD2S_NW ? rb[lane * 6 + 3 + c] : -1e30f);
         }
         const float rlist = 2.f * d->maxrad + skin, rlist2 = rlist * rlist;
         int dim[3]; float inv[3];
@@ -301,11 +310,20 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             if (cw < rlist) cw = rlist;
             dim[c] = m; inv[c] = 1.f / cw;
         }
+        while (dim[0] * dim[1] * dim[2] > CELL_CAP) {            // (one-slot structures only: fewer, wider cells)
+            const int c = dim[0] >= dim[1] && dim[0] >= dim[2] ? 0 : (dim[1] >= dim[2] ? 1 : 2);
+            dim[c]--;
+            float ext = hi[c] - lo[c];
+            if (!(ext > 0.f)) ext = 0.f;
+            float cw = ext / (float)dim[c];
+            if (cw < rlist) cw = rlist;
+            inv[c] = 1.f / cw;
+        }
         const int ncell = dim[0] * dim[1] * dim[2];
         // counts per cell (integer atomics: the counts do not depend on the order)
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
+            const int p = k * MD2S_T + tid;
             int c = MD2_NONE;
             if ((meta[k] & 3u) == IGMK_KIND_BEAD) {
                 const float4 q = x[p];
@@ -319,7 +337,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         __syncthreads();
         // inclusive scan of cell_start[1..ncell] (cell_start[c+1] held the count of cell c)
         {
-            const int per = (ncell + MD2_T - 1) / MD2_T;
+            const int per = (ncell + MD2S_T - 1) / MD2S_T;
             const int c0 = min(tid * per, ncell), c1 = min(c0 + per, ncell);
             int s = 0;
             for (int c = c0; c < c1; c++) s += cell_start[c + 1];
@@ -338,11 +356,11 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         // drop atoms unordered behind the cell start, then sort each (tiny) cell by index so that the
         // row order, and with it the floating-point summation order, is independent of the race.
         uint32_t* cursor = (uint32_t*)xsort;        // np * 16 bytes >= 4 * MAX_CELLS for every K; the cell-ordered copy is written later
-        for (int c = tid; c < ncell; c += MD2_T) cursor[c] = 0;
+        for (int c = tid; c < ncell; c += MD2S_T) cursor[c] = 0;
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
+            const int p = k * MD2S_T + tid;
             const int c = cell_of[p];
             if (c != MD2_NONE) {
                 const uint32_t pos = atomicAdd(&cursor[c], 1u);
@@ -350,7 +368,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
             }
         }
         __syncthreads();
-        for (int c = tid; c < ncell; c += MD2_T) {
+        for (int c = tid; c < ncell; c += MD2S_T) {
             const int b = cell_start[c], e = cell_start[c + 1];
             for (int q = b + 1; q < e; q++) {
                 const uint16_t v = cell_atoms[q]; int r = q - 1;
@@ -361,14 +379,14 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
+            const int p = k * MD2S_T + tid;
             const float4 q = x[p];
             xbx[p] = q.x; xby[p] = q.y; xbz[p] = q.z;
         }
         // positions in cell order: the search below walks them contiguously
         const long long ts0 = tick();
         const int nbead = cell_start[ncell];
-        for (int s0 = tid; s0 < nbead; s0 += MD2_T) {      // (the radius is not needed here: w carries the atom's position index)
+        for (int s0 = tid; s0 < nbead; s0 += MD2S_T) {      // (the radius is not needed here: w carries the atom's position index)
             const uint32_t a = cell_atoms[s0];
             float4 v = x[a];
             v.w = __uint_as_float(a);
@@ -380,7 +398,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         // reads) and need no index indirection until a candidate is accepted.
         int ovf = 0;
         const uint32_t xsa = (uint32_t)__cvta_generic_to_shared(xsort);
-        for (int s0 = tid; s0 < nbead; s0 += MD2_T) {
+        for (int s0 = tid; s0 < nbead; s0 += MD2S_T) {
             const int p = cell_atoms[s0];
             const float4 q = xsort[s0];
             const int c = cell_of[p];
@@ -425,13 +443,13 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         if (PROF) {                                   // how unevenly the search is spread over the warps
             if (lane == 0) ((long long*)rbuf)[warp] = tick() - ts0;
             __syncthreads();
-            if (tid == 0) { long long mx = 0, sm = 0; for (int q = 0; q < MD2_NW; q++) { const long long v = ((long long*)rbuf)[q]; mx = v > mx ? v : mx; sm += v; } t_smax += mx; t_ssum += sm / MD2_NW; }
+            if (tid == 0) { long long mx = 0, sm = 0; for (int q = 0; q < MD2S_NW; q++) { const long long v = ((long long*)rbuf)[q]; mx = v > mx ? v : mx; sm += v; } t_smax += mx; t_ssum += sm / MD2S_NW; }
         }
         __syncthreads();
         // the cell-ordered copy is dead: its memory becomes the bond inboxes (all flags clear); dummies / empty positions: no row
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
+            const int p = k * MD2S_T + tid;
             inbox[p] = make_uint4(0u, 0u, 0u, 0u);
             if (cell_of[p] == MD2_NONE) cell_of[p] = 0;
         }
@@ -450,12 +468,12 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         const long long tf0 = tick();
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
+            const int p = k * MD2S_T + tid;
             const float4 pi = x[p];
             float ax = 0.f, ay = 0.f, az = 0.f;
             const long long tp1 = tick();
             // harmonic upper / lower bounds I own: F = -2 pref k (r - r0) r_hat when violated
-            const int g = k * MD2_NW + warp;
+            const int g = k * MD2S_NW + warp;
             const int4 eb = eblk[g];
             const int2 ba = bact[g];
             // first batch of my neighbour row: in flight while the bond loops run
@@ -611,31 +629,43 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
         if (PROF) {                                   // how unevenly the force loops are spread over the warps
             if (lane == 0) ((long long*)rbuf)[64 + warp] = tr0 - tf0;
             __syncthreads();
-            if (tid == 0) { long long mx = 0, sm = 0; for (int q = 0; q < MD2_NW; q++) { const long long v = ((long long*)rbuf)[64 + q]; mx = v > mx ? v : mx; sm += v; } t_fmax += mx; t_fsum += sm / MD2_NW; }
+            if (tid == 0) { long long mx = 0, sm = 0; for (int q = 0; q < MD2S_NW; q++) { const long long v = ((long long*)rbuf)[64 + q]; mx = v > mx ? v : mx; sm += v; } t_fmax += mx; t_fsum += sm / MD2S_NW; }
         }
         __syncthreads();            // every inbox flag and mailbox of this evaluation is written
-        // bonds I receive: the owner's (dx, dy, dz, f/r) with the opposite sign, in inbox order; then clear the inbox
+        // bonds I receive: the owner's (dx, dy, dz, f/r) with the opposite sign, in inbox order; then clear the inbox.
+        // Flag bytes (0 / 1) -> one bit per slot.  The first flagged mailbox of EVERY slot of this thread is requested before
+        // any is used (the K round trips to L2 overlap); what is left of an atom's flags (few atoms have more than one
+        // violated incoming bond at a time) follows four at a time in slot order.
+        uint32_t mk[K];
+        float4 f0[K];
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            const int p = k * MD2_T + tid;
+            const int p = k * MD2S_T + tid;
             const uint4 fl = inbox[p];
-            if (fl.x | fl.y | fl.z | fl.w) {
-                // flag bytes (0 / 1) -> one bit per slot; the flagged mailboxes are fetched four at a time in slot order, so an
-                // atom with up to four violated incoming bonds (nearly all) pays one L2 latency, wherever its slots lie
-                uint32_t m = (((fl.x * 0x01020408u) >> 24) & 0xfu) | ((((fl.y * 0x01020408u) >> 24) & 0xfu) << 4) |
-                             ((((fl.z * 0x01020408u) >> 24) & 0xfu) << 8) | ((((fl.w * 0x01020408u) >> 24) & 0xfu) << 12);
-                const float4* box = gf + ((size_t)p << 4);
-                while (m) {
-                    float4 f[4];
-#pragma unroll
-                    for (int b = 0; b < 4; b++) {
-                        f[b] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (m) { f[b] = __ldcg(box + (__ffs(m) - 1)); m &= m - 1; }
-                    }
-#pragma unroll
-                    for (int b = 0; b < 4; b++) { fx[k] -= f[b].x * f[b].w; fy[k] -= f[b].y * f[b].w; fz[k] -= f[b].z * f[b].w; }
-                }
+            mk[k] = (((fl.x * 0x01020408u) >> 24) & 0xfu) | ((((fl.y * 0x01020408u) >> 24) & 0xfu) << 4) |
+                    ((((fl.z * 0x01020408u) >> 24) & 0xfu) << 8) | ((((fl.w * 0x01020408u) >> 24) & 0xfu) << 12);
+            f0[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (mk[k]) {
+                f0[k] = __ldcg(gf + ((size_t)p << 4) + (__ffs(mk[k]) - 1));
+                mk[k] &= mk[k] - 1;
                 inbox[p] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int p = k * MD2S_T + tid;
+            fx[k] -= f0[k].x * f0[k].w; fy[k] -= f0[k].y * f0[k].w; fz[k] -= f0[k].z * f0[k].w;
+            uint32_t m = mk[k];
+            const float4* box = gf + ((size_t)p << 4);
+            while (m) {
+                float4 f[4];
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    f[b] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (m) { f[b] = __ldcg(box + (__ffs(m) - 1)); m &= m - 1; }
+                }
+#pragma unroll
+                for (int b = 0; b < 4; b++) { fx[k] -= f[b].x * f[b].w; fy[k] -= f[b].y * f[b].w; fz[k] -= f[b].z * f[b].w; }
             }
             if (!MOVES(k)) { fx[k] = 0.f; fy[k] = 0.f; fz[k] = 0.f; }   // frozen / empty
         }
@@ -666,7 +696,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                 for (int k = 0; k < K; k++) {
                     float a = 0.f, b = 0.f, c = 0.f;
                     if (MOVES(k)) {
-                        uint32_t r = ranpark_jump(seed, 3u * (uint32_t)perm[k * MD2_T + tid] + 1u);
+                        uint32_t r = ranpark_jump(seed, 3u * (uint32_t)perm[k * MD2S_T + tid] + 1u);
                         const double AM = 1.0 / 2147483647.0;
                         a = (float)(AM * r - 0.5);
                         r = (uint32_t)(((uint64_t)r * 16807ull) % 2147483647ull); b = (float)(AM * r - 0.5);
@@ -701,7 +731,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
                     if (dbg_pass++ == 0) { step = -1; __syncthreads(); continue; }   // once through the full bond lists, once through the candidates
 #pragma unroll
                     for (int k = 0; k < K; k++) {
-                        const uint16_t a = perm[k * MD2_T + tid];
+                        const uint16_t a = perm[k * MD2S_T + tid];
                         if (a != MD2_NONE && V.dbg_forces) {
                             double* o = V.dbg_forces + 3 * (size_t)(d->atom_off + a);
                             o[0] = fx[k]; o[1] = fy[k]; o[2] = fz[k];
@@ -736,7 +766,7 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
 #pragma unroll
                 for (int k = 0; k < K; k++) {           // rescale + first half kick + drift
                     if (MOVES(k)) {
-                        const int p = k * MD2_T + tid;
+                        const int p = k * MD2S_T + tid;
                         float a = vx[k] * scale + dtf * fx[k], b = vy[k] * scale + dtf * fy[k], c = vz[k] * scale + dtf * fz[k];
                         const float vsq = a * a + b * b + c * c;
                         if (vsq > vlim2) { const float sc = sqrtf(vlim2 / vsq); a *= sc; b *= sc; c *= sc; }
@@ -756,9 +786,9 @@ k_md2(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P)
     int bad = 0;
 #pragma unroll
     for (int k = 0; k < K; k++) {
-        const uint16_t a = perm[k * MD2_T + tid];
+        const uint16_t a = perm[k * MD2S_T + tid];
         if (a != MD2_NONE) {
-            const float4 q = x[k * MD2_T + tid];
+            const float4 q = x[k * MD2S_T + tid];
             xg[a] = q;
             bad |= !(isfinite(q.x) && isfinite(q.y) && isfinite(q.z));
         }

@@ -388,7 +388,7 @@ int igmk_pop_assign_collect(igmk_pop_t* p, uint32_t* bits);
  *                                                    and the MD kernel's layout.  The arrays are byte-identical to what
  *                                                    igmk_submit_population + igmk_upload build from the same inputs.
  * Seeds as in igmk_submit_population.  Returns 0, 1 (error) or 2: this input is outside what the device path covers
- * (more than 4096 atoms, more than 1024 distinct bound distances, per-structure extras) and must go through
+ * (more than 3840 atoms, more than 1024 distinct bound distances, per-structure extras) and must go through
  * igmk_submit_population; igmk_last_error says which.  Afterwards the batch behaves like any other (run, fetch,
  * violation ratios); igmk_submit cannot add to it.
  */
