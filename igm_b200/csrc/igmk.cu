@@ -2415,7 +2415,36 @@ static int submit_population_dev_impl(igmk_handle_t* h, const igmk_system_t* tmp
 extern "C" int igmk_debug_fetch_array(igmk_handle_t* h, int32_t which, void* out, int64_t max_bytes, int64_t* n_bytes)
 {
     if (!h || !n_bytes) return fail("igmk_debug_fetch_array: NULL argument");
-    if (h->device < 0) return fail("igmk_debug_fetch_array: staging-only handle");
+    if (h->device < 0) {                   // staging-only handle: the layout the upload would build, from the host vectors
+        if (h->desc.empty()) return fail("igmk_debug_fetch_array: nothing submitted");
+        if (h->md2_perm.empty() || h->dirty) {
+            h->md2_K = md2_pick_K(h->max_atoms);
+            if (h->md2_K == 0) return fail("igmk_debug_fetch_array: structure too large for the one-CTA layout");
+            md2_build_owner(h);
+            if (!h->md2_error.empty()) return fail("igmk: " + h->md2_error);
+            h->dirty = false;
+        }
+        const void* src = nullptr; int64_t bytes = 0;
+        switch (which) {
+            case 0: src = h->desc.data(); bytes = h->desc.size() * sizeof(StructDesc); break;
+            case 1: src = h->xyzr.data(); bytes = h->xyzr.size() * sizeof(float4); break;
+            case 2: src = h->xyzr0.data(); bytes = h->xyzr0.size() * sizeof(float4); break;
+            case 3: src = h->kind.data(); bytes = h->kind.size(); break;
+            case 4: src = h->envmask.data(); bytes = h->envmask.size() * sizeof(uint32_t); break;
+            case 5: src = h->bond_ptr.data(); bytes = h->bond_ptr.size() * sizeof(int32_t); break;
+            case 6: src = h->bond_items.data(); bytes = h->bond_items.size() * sizeof(uint32_t); break;
+            case 7: src = h->btype_f.data(); bytes = h->btype_f.size() * sizeof(float2); break;
+            case 8: src = h->btype_d.data(); bytes = h->btype_d.size() * sizeof(double2); break;
+            case 9: src = h->md2_desc.data(); bytes = h->md2_desc.size() * sizeof(Md2Desc); break;
+            case 10: src = h->md2_perm.data(); bytes = h->md2_perm.size() * sizeof(uint16_t); break;
+            case 11: src = h->md2_eblk.data(); bytes = h->md2_eblk.size() * sizeof(int4); break;
+            case 12: src = h->md2_ell_items.data(); bytes = h->md2_ell_items.size() * sizeof(uint32_t); break;
+            default: return fail("igmk_debug_fetch_array: no such array");
+        }
+        *n_bytes = bytes;
+        if (out && bytes > 0 && bytes <= max_bytes) memcpy(out, src, (size_t)bytes);
+        return 0;
+    }
     CU(cudaSetDevice(h->device));
     if (int rc = upload(h)) return rc;
     const size_t ns = h->desc.size(), na = h->xyzr.size();
