@@ -1233,13 +1233,13 @@ static int launch_md2(igmk_handle* h, const Batch& B, const MdParams& P, int ns)
 {
     if (h->mdc_CL > 0) return launch_mdc(h, B, P, ns);
     if (h->md_big) {
-        if (P.debug_stage >= 0) return fail("igmk_md_forces: not available on the global-memory MD path");
         const size_t sm = md_big_smem_bytes(h->md2_K);
         CU(cudaFuncSetAttribute(k_md_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
         Md2View V;
         memset(&V, 0, sizeof V);
         V.perm = h->d_md2_perm; V.ell_off = h->d_md2_ell_off; V.ell_items = h->d_md2_ell_items;
         V.nl = h->d_md2_nl; V.nl_width = h->md2_nlw; V.prof = nullptr; V.ell_act = h->d_md2_ell_act;
+        V.dbg_forces = h->d_md2_dbg;
         k_md_big<<<ns, MD2_T, sm, h->stream>>>(B, V, h->d_md2_desc, P, h->d_big_state);
         CU(cudaGetLastError());
         return 0;

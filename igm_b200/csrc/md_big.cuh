@@ -305,8 +305,23 @@ k_md_big(Batch B, Md2View V, const Md2Desc* __restrict__ mdesc, MdParams P, floa
     const float dof = 3.f * (float)d->n_nonfixed - 3.f;
     float last_temp = 0.f;
 
-    for (int st = 0; st < pr.n_stage; st++) {
+    for (int st = (P.debug_stage >= 0 ? P.debug_stage : 0); st < pr.n_stage; st++) {
         set_stage(pr.evfactor[st], pr.envfactor[st]);
+        if (P.debug_stage >= 0) {        // forces of one run-setup evaluation, for the parity test of THIS force routine:
+            forces();                    // once through the full bond lists,
+            __syncthreads();
+            forces();                    // once through the candidates
+            __syncthreads();
+            for (int p = tid; p < np; p += MD2_T) {
+                const uint16_t a = perm[p];
+                if (a != MD2_NONE && V.dbg_forces) {
+                    double* o = V.dbg_forces + 3 * (size_t)(d->atom_off + a);
+                    o[0] = mobile(meta[p]) ? fx[p] : 0.f; o[1] = mobile(meta[p]) ? fy[p] : 0.f; o[2] = mobile(meta[p]) ? fz[p] : 0.f;
+                }
+            }
+            if (tid == 0) B.flags[blockIdx.x] = overflow ? 1 : 0;
+            return;
+        }
         for (int sub = (pr.relax_mdsteps > 0 ? 0 : 1); sub < 2; sub++) {
             const int nsteps = sub == 0 ? pr.relax_mdsteps : pr.mdsteps[st];
             const float t0 = sub == 0 ? (float)pr.relax_temperature : (float)pr.tstart[st];

@@ -88,6 +88,23 @@ def test_cluster_md_kernel_force_loop_matches_oracle(monkeypatch, cl):
             assert np.abs(f - f_ref).max() <= 2e-4 * np.abs(f_ref).max(), np.abs(f - f_ref).max() / np.abs(f_ref).max()
 
 
+def test_global_memory_md_kernel_force_loop_matches_oracle(monkeypatch):
+    """the forces k_md_big itself computes (state in global memory, every bond walked from both ends, full and candidate
+    lists) against the oracle: 3010-atom demo structures, forced onto that kernel, and the 9500-bead system that needs it"""
+    monkeypatch.setenv("IGMK_FORCE_BIG", "1")
+    from helpers import demo_structure
+    ffg = np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "ff_golden.npz"))
+    prot = short_protocol()
+    for systems in ([demo_structure(ffg, k) for k in (2, 7)], [_big_system(seed=6)[2]]):
+        with MStepBatch(0) as b:
+            slots = [b.submit(ps) for ps in systems]
+            b.md_forces(prot, 1)
+            for ps, slot in zip(systems, slots):
+                f_ref, _ = ff.single_point(ps, prot.evfactor[1], prot.envfactor[1], 1.0)
+                f = b.fetch_forces(slot)
+                assert np.abs(f - f_ref).max() <= 2e-4 * np.abs(f_ref).max(), np.abs(f - f_ref).max() / np.abs(f_ref).max()
+
+
 def test_single_point_and_cg_beyond_shared_memory():
     g, rad, ps = _big_system()
     f_ref, e_ref = ff.single_point(ps)
@@ -194,5 +211,15 @@ def test_config4_size_200kb_genome():
         xyz2, res = b.fetch(slot)
         md_ms, cg_ms, _ = b.last_timings()
     assert res.status == 0 and np.isfinite(xyz2).all() and res.final_energy < e_ref["total"]
+    import os
+    os.environ["IGMK_FORCE_BIG"] = "1"             # the same forces from the one-CTA global-memory kernel at full size
+    try:
+        with MStepBatch(0) as b:
+            slot = b.submit(ps)
+            b.md_forces(prot, 0)
+            fb = b.fetch_forces(slot)
+    finally:
+        del os.environ["IGMK_FORCE_BIG"]
+    assert np.abs(fb - f0).max() <= 2e-4 * np.abs(f0).max()
     print("200 kb structure: %.1f ms for %d MD force evaluations, CG %.1f ms for %d evaluations"
           % (md_ms, 4 * (40 + 10 + 2), cg_ms, res.cg_evals))
