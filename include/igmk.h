@@ -218,7 +218,7 @@ int igmk_single_point_f32(igmk_handle_t* h, double ev_scale, double env_scale,
  * lists and hardware approximations): the run-setup evaluation of annealing stage `stage` of `prot` (pair prefactor
  * and envelope scaled as lammps.py:287-303 does for that stage), no time step taken; read them with
  * igmk_fetch_forces.  What a `run 0` with the dump's fx fy fz columns is in the reference (lammps.py:253-256).
- * Structures of at most 8192 atoms (the shared-memory MD path). */
+ * Available for whichever MD kernel the batch takes (one CTA, thread-block cluster, global-memory). */
 int igmk_md_forces(igmk_handle_t* h, const igmk_protocol_t* prot, int32_t stage);
 int igmk_fetch(igmk_handle_t* h, int32_t slot, float* xyz_out /* [n_atoms][3] */,
                igmk_result_t* res);
